@@ -1,0 +1,186 @@
+/*
+ * cudapoa_b200.h -- C ABI of the B200-native batched partial-order-alignment engine.
+ *
+ * This is the drop-in boundary for the cudapoa path of GenomeWorks 0.5.0.  Every entry point
+ * below stands in for one member of the reference's C++ plugin interface, which is what the
+ * reference's own FFI (the pygenomeworks Cython module) binds:
+ *
+ *   reference interface (file:line, relative to the GenomeWorks tree)        C entry point
+ *   ------------------------------------------------------------------------ -----------------------------
+ *   cudapoa::Init()                          cudapoa/include/.../cudapoa.hpp:41    cudapoa_b200_init
+ *   BatchSize(3-arg ctor)                    cudapoa/include/.../batch.hpp:75      cudapoa_b200_batch_size_default
+ *   BatchSize(6-arg ctor)                    cudapoa/include/.../batch.hpp:99      cudapoa_b200_batch_size_explicit
+ *   create_batch(...)                        cudapoa/include/.../batch.hpp:220     cudapoa_b200_create_batch
+ *   Batch::~Batch                            cudapoa/include/.../batch.hpp:137     cudapoa_b200_destroy_batch
+ *   Batch::add_poa_group                     cudapoa/include/.../batch.hpp:153     cudapoa_b200_add_poa_group(_flat)
+ *   Batch::get_total_poas                    cudapoa/include/.../batch.hpp:159     cudapoa_b200_get_total_poas
+ *   Batch::generate_poa                      cudapoa/include/.../batch.hpp:162     cudapoa_b200_generate_poa
+ *   Batch::get_consensus                     cudapoa/include/.../batch.hpp:174     cudapoa_b200_get_consensus + result accessors
+ *   Batch::get_msa                           cudapoa/include/.../batch.hpp:186     cudapoa_b200_get_msa       + result accessors
+ *   Batch::get_graphs                        cudapoa/include/.../batch.hpp:196     cudapoa_b200_get_graphs    + result accessors
+ *   Batch::batch_id                          cudapoa/include/.../batch.hpp:202     cudapoa_b200_batch_id
+ *   Batch::reset                             cudapoa/include/.../batch.hpp:205     cudapoa_b200_reset
+ *   get_multi_batch_sizes                    cudapoa/include/.../utils.hpp:48      cudapoa_b200_get_multi_batch_sizes
+ *   (pygenomeworks CudaPoaBatch binds exactly these: pygenomeworks/genomeworks/cudapoa/cudapoa.pxd:54-90)
+ *
+ * Plain pointers and sizes only; no C++ or torch types cross this boundary.  Status codes are the
+ * numeric values of cudapoa::StatusType (cudapoa.hpp:26-38); a negative return means a C++ exception
+ * was caught at the boundary (-1 std::invalid_argument, -2 std::runtime_error, -3 anything else) and
+ * cudapoa_b200_last_error() holds its what() for the calling thread.
+ *
+ * There is no CPU fallback behind this interface: without a CUDA device create_batch fails.
+ */
+#ifndef CUDAPOA_B200_H
+#define CUDAPOA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Symbol prefix.  The same C-ABI translation unit is also compiled against the reference's own
+ * headers and library on the GPU box (oracle/Makefile) to obtain a bit-exactness oracle with an
+ * identical calling convention; that build sets CUDAPOA_CABI_PREFIX to cudapoa_ref_. */
+#ifndef CUDAPOA_CABI_PREFIX
+#define CUDAPOA_CABI_PREFIX cudapoa_b200_
+#endif
+#define CUDAPOA_CABI_CAT2(a, b) a##b
+#define CUDAPOA_CABI_CAT(a, b) CUDAPOA_CABI_CAT2(a, b)
+#define CUDAPOA_CABI(name) CUDAPOA_CABI_CAT(CUDAPOA_CABI_PREFIX, name)
+
+/* cudapoa::StatusType, same order and values (cudapoa.hpp:26-38). */
+enum
+{
+    CUDAPOA_B200_SUCCESS                                   = 0,
+    CUDAPOA_B200_EXCEEDED_MAXIMUM_POAS                     = 1,
+    CUDAPOA_B200_EXCEEDED_MAXIMUM_SEQUENCE_SIZE            = 2,
+    CUDAPOA_B200_EXCEEDED_MAXIMUM_SEQUENCES_PER_POA        = 3,
+    CUDAPOA_B200_NODE_COUNT_EXCEEDED_MAXIMUM_GRAPH_SIZE    = 4,
+    CUDAPOA_B200_EDGE_COUNT_EXCEEDED_MAXIMUM_GRAPH_SIZE    = 5,
+    CUDAPOA_B200_SEQ_LEN_EXCEEDED_MAXIMUM_NODES_PER_WINDOW = 6,
+    CUDAPOA_B200_LOOP_COUNT_EXCEEDED_UPPER_BOUND           = 7,
+    CUDAPOA_B200_OUTPUT_TYPE_UNAVAILABLE                   = 8,
+    CUDAPOA_B200_GENERIC_ERROR                             = 9
+};
+
+/* cudapoa::OutputType bit mask (cudapoa.hpp:44-48). */
+enum
+{
+    CUDAPOA_B200_OUTPUT_CONSENSUS = 1,
+    CUDAPOA_B200_OUTPUT_MSA       = 2
+};
+
+/* Mirror of cudapoa::BatchSize, fields in declaration order (batch.hpp:53-73). */
+typedef struct cudapoa_b200_batch_size
+{
+    int32_t max_sequence_size;
+    int32_t max_consensus_size;
+    int32_t max_nodes_per_window;
+    int32_t max_nodes_per_window_banded;
+    int32_t max_matrix_graph_dimension;
+    int32_t max_matrix_graph_dimension_banded;
+    int32_t max_matrix_sequence_dimension;
+    int32_t alignment_band_width;
+    int32_t max_sequences_per_poa;
+} cudapoa_b200_batch_size;
+
+/* Opaque batch handle (one cudapoa::Batch). */
+typedef struct cudapoa_b200_batch cudapoa_b200_batch;
+
+/* Per-batch counters of the last generate_poa(); filled only by the native engine. */
+typedef struct cudapoa_b200_stats
+{
+    int64_t windows;        /* windows processed                                             */
+    int64_t reads_aligned;  /* sum over windows of (reads - 1)                               */
+    int64_t dp_cells;       /* sum of N_s * Wc (SURVEY.md 8(d) work unit)                    */
+    int64_t graph_rows;     /* sum of N_s                                                    */
+    int64_t exact_path;     /* alignments that took the exact-arithmetic slow path           */
+    int64_t h2d_bytes;      /* bytes copied host->device by generate_poa                     */
+    int64_t d2h_bytes;      /* bytes copied device->host by the last get_*                   */
+    double kernel_ms;       /* CUDA-event time of the device work of generate_poa            */
+    double graph_kernel_ms; /* the POA graph-build kernel alone                              */
+} cudapoa_b200_stats;
+
+const char* CUDAPOA_CABI(last_error)(void);
+const char* CUDAPOA_CABI(implementation)(void); /* "b200-native" or "genomeworks-reference" */
+
+int32_t CUDAPOA_CABI(init)(void);
+
+int32_t CUDAPOA_CABI(batch_size_default)(cudapoa_b200_batch_size* out, int32_t max_seq_sz, int32_t max_seq_per_poa,
+                                         int32_t band_width);
+int32_t CUDAPOA_CABI(batch_size_explicit)(cudapoa_b200_batch_size* out, int32_t max_seq_sz, int32_t max_consensus_sz,
+                                          int32_t max_nodes_per_w, int32_t max_nodes_per_w_banded, int32_t band_width,
+                                          int32_t max_seq_per_poa);
+
+/* stream is a cudaStream_t passed as void* (NULL = default stream); the caller keeps ownership. */
+cudapoa_b200_batch* CUDAPOA_CABI(create_batch)(int32_t device_id, void* stream, size_t max_mem, int8_t output_mask,
+                                               const cudapoa_b200_batch_size* batch_size, int16_t gap_score,
+                                               int16_t mismatch_score, int16_t match_score,
+                                               int32_t cuda_banded_alignment);
+void CUDAPOA_CABI(destroy_batch)(cudapoa_b200_batch* batch);
+
+/* One group.  weights may be NULL, and any weights[i] may be NULL (= all ones).  per_seq_status has room for
+ * n_entries values; *n_status receives how many were written (0 when the group itself was refused, matching
+ * the reference, which clears the vector only after the score buffer was reserved). */
+int32_t CUDAPOA_CABI(add_poa_group)(cudapoa_b200_batch* batch, const char* const* seqs, const int8_t* const* weights,
+                                    const int32_t* lengths, int32_t n_entries, int32_t* per_seq_status,
+                                    int32_t* n_status);
+
+/* Many groups from flat host buffers: bases/weights are the reads of all windows back to back, read_lengths one
+ * entry per read, window_n_reads one entry per window.  Adds windows in order by calling add_poa_group and stops
+ * at the first group the batch refuses; *n_added = windows accepted.  per_seq_status (optional) gets one value
+ * per read of the accepted windows.  Returns the status of the last add_poa_group call. */
+int32_t CUDAPOA_CABI(add_poa_groups_flat)(cudapoa_b200_batch* batch, const uint8_t* bases, const int8_t* weights,
+                                          const int32_t* read_lengths, const int32_t* window_n_reads,
+                                          int32_t n_windows, int32_t* n_added, int32_t* per_seq_status);
+
+int32_t CUDAPOA_CABI(get_total_poas)(const cudapoa_b200_batch* batch);
+int32_t CUDAPOA_CABI(generate_poa)(cudapoa_b200_batch* batch);
+int32_t CUDAPOA_CABI(batch_id)(const cudapoa_b200_batch* batch);
+int32_t CUDAPOA_CABI(reset)(cudapoa_b200_batch* batch);
+
+/* get_*: run the reference-named call and keep its outputs inside the handle until the next get_* / destroy.
+ * The return value is what the C++ call returned (get_graphs returns void there: always 0 here). */
+int32_t CUDAPOA_CABI(get_consensus)(cudapoa_b200_batch* batch);
+int32_t CUDAPOA_CABI(get_msa)(cudapoa_b200_batch* batch);
+int32_t CUDAPOA_CABI(get_graphs)(cudapoa_b200_batch* batch);
+
+/* Accessors over the outputs of the last get_*.  Pointers stay valid until the next get_* or destroy. */
+int32_t CUDAPOA_CABI(result_count)(const cudapoa_b200_batch* batch);       /* size of the consensus/msa/graphs vector */
+int32_t CUDAPOA_CABI(result_status_count)(const cudapoa_b200_batch* batch); /* size of output_status                  */
+int32_t CUDAPOA_CABI(result_status)(const cudapoa_b200_batch* batch, int32_t i);
+int32_t CUDAPOA_CABI(result_consensus)(const cudapoa_b200_batch* batch, int32_t i, const char** seq,
+                                       const uint16_t** coverage); /* returns length */
+int32_t CUDAPOA_CABI(result_msa_rows)(const cudapoa_b200_batch* batch, int32_t i);
+int32_t CUDAPOA_CABI(result_msa_row)(const cudapoa_b200_batch* batch, int32_t i, int32_t row,
+                                     const char** seq); /* returns length */
+/* Graph i as arrays: node labels (one char per node id 0..n-1; 0 for ids without a label) and an edge list
+ * sorted by (sink, source).  Each call fills up to cap entries and returns the total count. */
+int32_t CUDAPOA_CABI(result_graph_nodes)(const cudapoa_b200_batch* batch, int32_t i, char* labels, int32_t cap);
+int32_t CUDAPOA_CABI(result_graph_edges)(const cudapoa_b200_batch* batch, int32_t i, int32_t* src, int32_t* dst,
+                                         int32_t* weight, int32_t cap);
+/* Whole-batch digest helpers used by the benchmark so that result decoding stays out of Python:
+ * total characters over all consensus strings (or MSA rows), and an FNV-1a 64 hash of
+ * status|length|bytes(|coverage) over all windows in order. */
+int64_t CUDAPOA_CABI(result_total_chars)(const cudapoa_b200_batch* batch);
+uint64_t CUDAPOA_CABI(result_digest)(const cudapoa_b200_batch* batch);
+
+/* get_multi_batch_sizes over flat host buffers (lengths only are needed).  Writes up to cap batch sizes and,
+ * per window, the index of the batch size it was assigned to (-1 if none).  Returns the number of batch sizes. */
+int32_t CUDAPOA_CABI(get_multi_batch_sizes)(const int32_t* read_lengths, const int32_t* window_n_reads,
+                                            int32_t n_windows, int32_t banded_alignment, int32_t msa_flag,
+                                            int32_t band_width, float gpu_memory_usage_quota, int32_t mismatch_score,
+                                            int32_t gap_score, int32_t match_score, cudapoa_b200_batch_size* out,
+                                            int32_t cap, int32_t* window_to_batch);
+
+/* Native-engine extras (absent from the reference build of this ABI). */
+int32_t CUDAPOA_CABI(get_stats)(const cudapoa_b200_batch* batch, cudapoa_b200_stats* out);
+int32_t CUDAPOA_CABI(max_poas)(const cudapoa_b200_batch* batch);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* CUDAPOA_B200_H */
