@@ -1,0 +1,784 @@
+// Host side of the B200 POA engine: the cudapoa::Batch implementation behind create_batch().
+//
+// Observable behaviour follows the reference host code (cudapoa/src/cudapoa_batch.cuh, allocate_block.hpp,
+// batch.cu, cudapoa_limits.hpp, utils.cu, cudapoa.cpp); memory layout, staging and kernels are this engine's own.
+#include "engine_stats.hpp"
+#include "poa_layout.hpp"
+#include "poa_window.cuh"
+
+#include <claraparabricks/genomeworks/cudapoa/batch.hpp>
+#include <claraparabricks/genomeworks/cudapoa/cudapoa.hpp>
+#include <claraparabricks/genomeworks/cudapoa/utils.hpp>
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <iomanip>
+#include <iostream>
+#include <string>
+#include <vector>
+
+namespace claraparabricks
+{
+namespace genomeworks
+{
+namespace cudapoa
+{
+
+using namespace poa_b200;
+
+namespace
+{
+
+// cudapoa_limits.hpp:28-37.  Always uses the NON-banded graph dimension, as the reference does.
+bool use_32bit_score(const BatchSize& b, int32_t gap, int32_t mismatch, int32_t match)
+{
+    const int32_t upper = b.max_sequence_size * match;
+    const int32_t lower = b.max_sequence_size * std::max(gap, mismatch) +
+                          (b.max_matrix_graph_dimension - b.max_sequence_size) * gap;
+    return (upper > INT16_MAX || (-lower) > (INT16_MAX + 1));
+}
+
+// cudapoa_limits.hpp:39-53
+bool use_32bit_size(const BatchSize& b, bool banded)
+{
+    int32_t m = b.max_consensus_size;
+    m         = std::max(m, banded ? b.max_matrix_graph_dimension_banded : b.max_matrix_graph_dimension);
+    m         = std::max(m, b.max_matrix_sequence_dimension);
+    return m > INT16_MAX;
+}
+
+struct MemoryPlan
+{
+    bool score32 = false;
+    bool size32  = false;
+    int32_t M    = 0; // node capacity
+    int32_t G    = 0; // score matrix rows
+    ArenaLayout layout{};
+    int64_t input_per_poa  = 0;
+    int64_t output_per_poa = 0;
+    int64_t fixed_per_poa  = 0; // arena + inputs + outputs
+    int64_t score_per_poa  = 0; // banded: exact; full: for the widest allowed read
+};
+
+MemoryPlan make_plan(const BatchSize& b, bool banded, bool msa, int32_t gap, int32_t mismatch, int32_t match)
+{
+    MemoryPlan p;
+    p.score32 = use_32bit_score(b, gap, mismatch, match);
+    p.size32  = p.score32 && use_32bit_size(b, banded);
+    p.M       = banded ? b.max_nodes_per_window_banded : b.max_nodes_per_window;
+    p.G       = banded ? b.max_matrix_graph_dimension_banded : b.max_matrix_graph_dimension;
+    p.G       = std::max(p.G, p.M + 1); // one score row per node plus row 0
+    const int32_t S = std::max(b.max_sequences_per_poa, 1);
+    const int32_t L = std::max(b.max_sequence_size, 1);
+    p.layout  = make_arena_layout(p.M, p.M + L + 8, S, L, p.size32 ? 4 : 2, msa);
+    p.input_per_poa  = static_cast<int64_t>(S) * L * 2 + static_cast<int64_t>(S) * 4 + sizeof(WindowDesc);
+    p.output_per_poa = 1 + 4 + 8 +
+                       (msa ? static_cast<int64_t>(S) * b.max_consensus_size
+                            : static_cast<int64_t>(b.max_consensus_size) * 3);
+    p.fixed_per_poa = p.layout.stride + align_up64(p.input_per_poa, 16) + align_up64(p.output_per_poa, 16) + 64;
+    const int64_t width = banded ? b.alignment_band_width + kBandPad : b.max_matrix_sequence_dimension + 8;
+    p.score_per_poa     = width * static_cast<int64_t>(p.G) * (p.score32 ? 4 : 2);
+    return p;
+}
+
+std::atomic<int32_t> g_batches_16_16{0}, g_batches_32_16{0}, g_batches_32_32{0};
+
+template <typename T>
+T* carve(uint8_t*& cursor, int64_t count)
+{
+    T* p   = reinterpret_cast<T*>(cursor);
+    cursor += align_up64(count * static_cast<int64_t>(sizeof(T)), 256);
+    return p;
+}
+
+} // namespace
+
+class B200Batch : public Batch, public EngineStatsSource
+{
+public:
+    B200Batch(int32_t device_id, cudaStream_t stream, size_t max_mem, int8_t output_mask, const BatchSize& batch_size,
+              int32_t gap, int32_t mismatch, int32_t match, bool banded)
+        : max_sequences_per_poa_(throw_on_negative(batch_size.max_sequences_per_poa,
+                                                   "Maximum sequences per POA has to be non-negative"))
+        , device_id_(throw_on_negative(device_id, "Device ID has to be non-negative"))
+        , stream_(stream)
+        , output_mask_(output_mask)
+        , batch_size_(batch_size)
+        , gap_(gap)
+        , mismatch_(mismatch)
+        , match_(match)
+        , banded_(banded)
+        , msa_((output_mask & OutputType::msa) != 0)
+    {
+        plan_ = make_plan(batch_size_, banded_, msa_, gap_, mismatch_, match_);
+        // allocate_block.hpp:66-76: refuse budgets that cannot hold a single POA
+        const size_t minimum = static_cast<size_t>(plan_.fixed_per_poa);
+        if (max_mem < minimum + static_cast<size_t>(plan_.score_per_poa))
+        {
+            throw std::runtime_error(std::string("Require at least ")
+                                         .append(std::to_string(minimum + plan_.score_per_poa))
+                                         .append(" bytes of device memory per CUDAPOA batch to process correctly."));
+        }
+        scoped_device_switch dev(device_id_);
+        max_poas_ = static_cast<int32_t>(
+            std::min<int64_t>(max_mem / static_cast<size_t>(plan_.fixed_per_poa + plan_.score_per_poa), INT32_MAX / 4));
+        bid_ = (plan_.score32 ? (plan_.size32 ? g_batches_32_32 : g_batches_32_16) : g_batches_16_16)++;
+        allocate(max_mem);
+        GW_CU_CHECK_ERR(cudaEventCreate(&ev_start_));
+        GW_CU_CHECK_ERR(cudaEventCreate(&ev_stop_));
+        reset();
+    }
+
+    ~B200Batch() override
+    {
+        scoped_device_switch dev(device_id_);
+        cudaEventDestroy(ev_start_);
+        cudaEventDestroy(ev_stop_);
+        cudaFree(block_d_);
+        cudaFreeHost(block_h_);
+        if (weights_h_ != nullptr)
+            cudaFreeHost(weights_h_);
+    }
+
+    StatusType add_poa_group(std::vector<StatusType>& per_seq_status, const Group& poa_group) override;
+    int32_t get_total_poas() const override { return poa_count_; }
+    void generate_poa() override;
+    StatusType get_consensus(std::vector<std::string>& consensus, std::vector<std::vector<uint16_t>>& coverage,
+                             std::vector<StatusType>& output_status) override;
+    StatusType get_msa(std::vector<std::vector<std::string>>& msa, std::vector<StatusType>& output_status) override;
+    void get_graphs(std::vector<DirectedGraph>& graphs, std::vector<StatusType>& output_status) override;
+    int32_t batch_id() const override { return bid_; }
+
+    void reset() override
+    {
+        poa_count_       = 0;
+        num_bases_       = 0;
+        num_reads_       = 0;
+        next_score_off_  = 0;
+        avail_score_mem_ = score_pool_bytes_;
+        has_weights_     = false;
+        launched_        = false;
+        timed_           = false;
+    }
+
+    void fill_stats(cudapoa_b200_stats* out) const override;
+    int32_t max_poas() const override { return max_poas_; }
+
+private:
+    void allocate(size_t max_mem);
+    bool reserve_scores(int32_t max_seq_length);
+    StatusType add_sequence(const Entry& e);
+    void ensure_weights();
+    void launch();
+    void sync_and_collect();
+    void push_status(std::vector<StatusType>& out, int32_t poa) const
+    {
+        out.emplace_back(static_cast<StatusType>(status_h_[poa]));
+    }
+
+    int32_t max_sequences_per_poa_;
+    int32_t device_id_;
+    cudaStream_t stream_;
+    int8_t output_mask_;
+    BatchSize batch_size_;
+    int32_t gap_, mismatch_, match_;
+    bool banded_;
+    bool msa_;
+    MemoryPlan plan_;
+    int32_t max_poas_ = 0;
+    int32_t bid_      = 0;
+
+    // device block and its carve-up
+    uint8_t* block_d_      = nullptr;
+    uint8_t* bases_d_      = nullptr;
+    int8_t* weights_d_     = nullptr;
+    int32_t* read_len_d_   = nullptr;
+    WindowDesc* windows_d_ = nullptr;
+    uint8_t* status_d_     = nullptr;
+    int32_t* node_count_d_ = nullptr;
+    uint32_t* stat_rows_d_ = nullptr;
+    uint32_t* stat_exact_d_ = nullptr;
+    unsigned long long* stat_cells_d_ = nullptr;
+    uint8_t* consensus_d_  = nullptr;
+    uint16_t* coverage_d_  = nullptr;
+    uint8_t* msa_d_        = nullptr;
+    uint8_t* arena_d_      = nullptr;
+    uint8_t* scores_d_     = nullptr;
+    size_t score_pool_bytes_ = 0;
+
+    // pinned host block
+    uint8_t* block_h_       = nullptr;
+    uint8_t* bases_h_       = nullptr;
+    int8_t* weights_h_      = nullptr; // allocated on the first weighted entry
+    int32_t* read_len_h_    = nullptr;
+    WindowDesc* windows_h_  = nullptr;
+    uint8_t* status_h_      = nullptr;
+    int32_t* node_count_h_  = nullptr;
+    uint32_t* stat_rows_h_  = nullptr;
+    uint32_t* stat_exact_h_ = nullptr;
+    unsigned long long* stat_cells_h_ = nullptr;
+    uint8_t* consensus_h_   = nullptr;
+    uint16_t* coverage_h_   = nullptr;
+    uint8_t* msa_h_         = nullptr;
+
+    // staging state
+    int32_t poa_count_      = 0;
+    int64_t num_bases_      = 0;
+    int32_t num_reads_      = 0;
+    int64_t next_score_off_ = 0; // full alignment: score elements handed out so far
+    size_t avail_score_mem_ = 0;
+    bool has_weights_       = false;
+    bool launched_          = false;
+    bool timed_             = false;
+
+    cudaEvent_t ev_start_{}, ev_stop_{};
+    mutable cudapoa_b200_stats stats_{};
+};
+
+void B200Batch::allocate(size_t max_mem)
+{
+    const int64_t S = std::max(max_sequences_per_poa_, 1);
+    const int64_t L = std::max(batch_size_.max_sequence_size, 1);
+    const int64_t C = std::max(batch_size_.max_consensus_size, 2);
+    GW_CU_CHECK_ERR(cudaMalloc(reinterpret_cast<void**>(&block_d_), max_mem));
+
+    // Shrink max_poas_ until the fixed arrays plus one banded score matrix per POA fit (alignment padding).
+    auto fixed_bytes = [&](int64_t n) {
+        int64_t b = 0;
+        auto a    = [&](int64_t x) { b += align_up64(x, 256); };
+        a(n * S * L);                 // bases
+        a(n * S * L);                 // weights
+        a(n * S * 4);                 // read_len
+        a(n * static_cast<int64_t>(sizeof(WindowDesc)));
+        a(n);                         // status
+        a(n * 4);                     // node_count
+        a(n * 4);                     // stat_rows
+        a(n * 4);                     // stat_exact
+        a(n * 8);                     // stat_cells
+        a(msa_ ? 0 : n * C);          // consensus
+        a(msa_ ? 0 : n * C * 2);      // coverage
+        a(msa_ ? n * S * C : 0);      // msa
+        a(n * plan_.layout.stride);   // arena
+        return b;
+    };
+    while (max_poas_ > 1 &&
+           fixed_bytes(max_poas_) + static_cast<int64_t>(max_poas_) * plan_.score_per_poa > static_cast<int64_t>(max_mem))
+        max_poas_--;
+
+    const int64_t n = max_poas_;
+    uint8_t* cur    = block_d_;
+    bases_d_        = carve<uint8_t>(cur, n * S * L);
+    weights_d_      = carve<int8_t>(cur, n * S * L);
+    read_len_d_     = carve<int32_t>(cur, n * S);
+    windows_d_      = carve<WindowDesc>(cur, n);
+    status_d_       = carve<uint8_t>(cur, n);
+    node_count_d_   = carve<int32_t>(cur, n);
+    stat_rows_d_    = carve<uint32_t>(cur, n);
+    stat_exact_d_   = carve<uint32_t>(cur, n);
+    stat_cells_d_   = carve<unsigned long long>(cur, n);
+    consensus_d_    = carve<uint8_t>(cur, msa_ ? 0 : n * C);
+    coverage_d_     = carve<uint16_t>(cur, msa_ ? 0 : n * C);
+    msa_d_          = carve<uint8_t>(cur, msa_ ? n * S * C : 0);
+    arena_d_        = carve<uint8_t>(cur, n * plan_.layout.stride);
+    scores_d_       = cur;
+    const int64_t used = cur - block_d_;
+    score_pool_bytes_  = (static_cast<int64_t>(max_mem) > used) ? max_mem - static_cast<size_t>(used) : 0;
+
+    // pinned staging: inputs (weights are added lazily) and outputs
+    int64_t hb = 0;
+    auto h     = [&](int64_t x) {
+        int64_t at = hb;
+        hb += align_up64(x, 256);
+        return at;
+    };
+    const int64_t o_bases = h(n * S * L), o_len = h(n * S * 4), o_win = h(n * sizeof(WindowDesc)), o_st = h(n),
+                  o_nc = h(n * 4), o_sr = h(n * 4), o_se = h(n * 4), o_sc = h(n * 8), o_cons = h(msa_ ? 0 : n * C),
+                  o_cov = h(msa_ ? 0 : n * C * 2), o_msa = h(msa_ ? n * S * C : 0);
+    GW_CU_CHECK_ERR(cudaHostAlloc(reinterpret_cast<void**>(&block_h_), static_cast<size_t>(hb + 256), cudaHostAllocDefault));
+    bases_h_      = block_h_ + o_bases;
+    read_len_h_   = reinterpret_cast<int32_t*>(block_h_ + o_len);
+    windows_h_    = reinterpret_cast<WindowDesc*>(block_h_ + o_win);
+    status_h_     = block_h_ + o_st;
+    node_count_h_ = reinterpret_cast<int32_t*>(block_h_ + o_nc);
+    stat_rows_h_  = reinterpret_cast<uint32_t*>(block_h_ + o_sr);
+    stat_exact_h_ = reinterpret_cast<uint32_t*>(block_h_ + o_se);
+    stat_cells_h_ = reinterpret_cast<unsigned long long*>(block_h_ + o_sc);
+    consensus_h_  = block_h_ + o_cons;
+    coverage_h_   = reinterpret_cast<uint16_t*>(block_h_ + o_cov);
+    msa_h_        = block_h_ + o_msa;
+}
+
+// reserve_buf, cudapoa_batch.cuh:542-564
+bool B200Batch::reserve_scores(int32_t max_seq_length)
+{
+    const int64_t width = banded_ ? batch_size_.alignment_band_width + kBandPad
+                                  : cudautils::align<int32_t, 4>(max_seq_length + 1 + 4);
+    const size_t bytes  = static_cast<size_t>(width) * static_cast<size_t>(plan_.G) * (plan_.score32 ? 4 : 2);
+    if (bytes > avail_score_mem_)
+    {
+        if (get_total_poas() == 0)
+        {
+            std::cout << "Memory available " << std::fixed << std::setprecision(2)
+                      << static_cast<double>(avail_score_mem_) / 1024. / 1024. / 1024.;
+            std::cout << "GB, Memory required " << static_cast<double>(bytes) / 1024. / 1024. / 1024.;
+            std::cout << "GB (sequence length " << max_seq_length << ", graph length " << plan_.G << ")" << std::endl;
+        }
+        return false;
+    }
+    avail_score_mem_ -= bytes;
+    return true;
+}
+
+void B200Batch::ensure_weights()
+{
+    if (has_weights_)
+        return;
+    if (weights_h_ == nullptr)
+    {
+        const size_t bytes = static_cast<size_t>(max_poas_) * std::max(max_sequences_per_poa_, 1) *
+                             std::max(batch_size_.max_sequence_size, 1);
+        GW_CU_CHECK_ERR(cudaHostAlloc(reinterpret_cast<void**>(&weights_h_), bytes, cudaHostAllocDefault));
+    }
+    std::memset(weights_h_, 1, static_cast<size_t>(num_bases_)); // everything staged so far had weight 1
+    has_weights_ = true;
+}
+
+// add_seq_to_poa, cudapoa_batch.cuh:490-539
+StatusType B200Batch::add_sequence(const Entry& e)
+{
+    if (e.length > batch_size_.max_sequence_size)
+        return StatusType::exceeded_maximum_sequence_size;
+    WindowDesc& wd      = windows_h_[poa_count_ - 1];
+    const int32_t width = cudautils::align<int32_t, 4>(e.length + 1 + 4);
+    if (width > wd.scores_width)
+    {
+        if (!banded_)
+            next_score_off_ += static_cast<int64_t>(width - wd.scores_width) * plan_.G;
+        wd.scores_width = width;
+    }
+    if (wd.n_reads >= max_sequences_per_poa_)
+        return StatusType::exceeded_maximum_sequences_per_poa;
+    if (e.weights != nullptr)
+    {
+        for (int32_t i = 0; i < e.length; i++)
+            throw_on_negative(e.weights[i], "Base weights need to be non-negative");
+        ensure_weights();
+    }
+    if (e.length > 0)
+    {
+        std::memcpy(bases_h_ + num_bases_, e.seq, static_cast<size_t>(e.length));
+        if (has_weights_)
+        {
+            if (e.weights != nullptr)
+                std::memcpy(weights_h_ + num_bases_, e.weights, static_cast<size_t>(e.length));
+            else
+                std::memset(weights_h_ + num_bases_, 1, static_cast<size_t>(e.length));
+        }
+    }
+    read_len_h_[num_reads_] = e.length;
+    wd.n_reads++;
+    num_bases_ += e.length;
+    num_reads_++;
+    return StatusType::success;
+}
+
+// add_poa_group, cudapoa_batch.cuh:103-143
+StatusType B200Batch::add_poa_group(std::vector<StatusType>& per_seq_status, const Group& poa_group)
+{
+    int32_t max_len = 0;
+    for (const Entry& e : poa_group)
+        max_len = std::max(max_len, e.length);
+    if (!reserve_scores(max_len))
+        return StatusType::exceeded_maximum_poas;
+    per_seq_status.clear();
+    if (poa_count_ == max_poas_)
+        return StatusType::exceeded_maximum_poas;
+
+    WindowDesc wd{};
+    wd.base_off     = num_bases_;
+    wd.score_off    = next_score_off_;
+    wd.read_off     = num_reads_;
+    wd.n_reads      = 0;
+    wd.scores_width = 0;
+    windows_h_[poa_count_++] = wd;
+    for (const Entry& e : poa_group)
+        per_seq_status.push_back(add_sequence(e));
+    return StatusType::success;
+}
+
+template <typename ScoreT, typename IdT>
+static void launch_typed(const KernelParams& P, bool banded, bool msa, cudaStream_t stream)
+{
+    const dim3 block(kWarpsPerBlock * 32);
+    const dim3 grid((P.n_windows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    if (banded)
+    {
+        if (msa)
+            poa_window_kernel<ScoreT, IdT, true, true><<<grid, block, 0, stream>>>(P);
+        else
+            poa_window_kernel<ScoreT, IdT, true, false><<<grid, block, 0, stream>>>(P);
+    }
+    else
+    {
+        if (msa)
+            poa_window_kernel<ScoreT, IdT, false, true><<<grid, block, 0, stream>>>(P);
+        else
+            poa_window_kernel<ScoreT, IdT, false, false><<<grid, block, 0, stream>>>(P);
+    }
+}
+
+void B200Batch::launch()
+{
+    KernelParams P{};
+    P.bases               = bases_d_;
+    P.weights             = has_weights_ ? weights_d_ : nullptr;
+    P.read_len            = read_len_d_;
+    P.windows             = windows_d_;
+    P.n_windows           = poa_count_;
+    P.arena               = arena_d_;
+    P.layout              = plan_.layout;
+    P.scores              = scores_d_;
+    P.banded_score_stride = static_cast<int64_t>(batch_size_.alignment_band_width + kBandPad) * plan_.G;
+    P.status              = status_d_;
+    P.node_count          = node_count_d_;
+    P.consensus           = consensus_d_;
+    P.coverage            = coverage_d_;
+    P.msa                 = msa_d_;
+    P.stat_rows           = stat_rows_d_;
+    P.stat_exact          = stat_exact_d_;
+    P.stat_cells          = stat_cells_d_;
+    P.max_nodes           = plan_.M;
+    P.max_consensus       = batch_size_.max_consensus_size;
+    P.max_reads           = std::max(max_sequences_per_poa_, 1);
+    P.band                = batch_size_.alignment_band_width;
+    P.gap                 = gap_;
+    P.mismatch            = mismatch_;
+    P.match               = match_;
+#ifdef SPOA_ACCURATE
+    P.spoa_accurate = 1;
+#else
+    const char* env = std::getenv("CUDAPOA_B200_SPOA_ACCURATE");
+    P.spoa_accurate = (env != nullptr && env[0] == '1') ? 1 : 0;
+#endif
+    if (!plan_.score32)
+        launch_typed<int16_t, int16_t>(P, banded_, msa_, stream_);
+    else if (!plan_.size32)
+        launch_typed<int32_t, int16_t>(P, banded_, msa_, stream_);
+    else
+        launch_typed<int32_t, int32_t>(P, banded_, msa_, stream_);
+    GW_CU_CHECK_ERR(cudaPeekAtLastError());
+}
+
+// generate_poa, cudapoa_batch.cuh:152-193: copies and launch are enqueued, nothing is waited for.
+void B200Batch::generate_poa()
+{
+    scoped_device_switch dev(device_id_);
+    if (poa_count_ == 0)
+        return;
+    stats_           = cudapoa_b200_stats{};
+    stats_.windows   = poa_count_;
+    stats_.reads_aligned = num_reads_ - poa_count_;
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(bases_d_, bases_h_, static_cast<size_t>(num_bases_), cudaMemcpyHostToDevice, stream_));
+    stats_.h2d_bytes += num_bases_;
+    if (has_weights_)
+    {
+        GW_CU_CHECK_ERR(cudaMemcpyAsync(weights_d_, weights_h_, static_cast<size_t>(num_bases_), cudaMemcpyHostToDevice, stream_));
+        stats_.h2d_bytes += num_bases_;
+    }
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(read_len_d_, read_len_h_, sizeof(int32_t) * num_reads_, cudaMemcpyHostToDevice, stream_));
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(windows_d_, windows_h_, sizeof(WindowDesc) * poa_count_, cudaMemcpyHostToDevice, stream_));
+    stats_.h2d_bytes += static_cast<int64_t>(sizeof(int32_t)) * num_reads_ + static_cast<int64_t>(sizeof(WindowDesc)) * poa_count_;
+    GW_CU_CHECK_ERR(cudaEventRecord(ev_start_, stream_));
+    launch();
+    GW_CU_CHECK_ERR(cudaEventRecord(ev_stop_, stream_));
+    launched_ = true;
+    timed_    = false;
+}
+
+void B200Batch::sync_and_collect()
+{
+    const size_t n = static_cast<size_t>(poa_count_);
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(status_h_, status_d_, n, cudaMemcpyDeviceToHost, stream_));
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(node_count_h_, node_count_d_, n * 4, cudaMemcpyDeviceToHost, stream_));
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(stat_rows_h_, stat_rows_d_, n * 4, cudaMemcpyDeviceToHost, stream_));
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(stat_exact_h_, stat_exact_d_, n * 4, cudaMemcpyDeviceToHost, stream_));
+    GW_CU_CHECK_ERR(cudaMemcpyAsync(stat_cells_h_, stat_cells_d_, n * 8, cudaMemcpyDeviceToHost, stream_));
+    stats_.d2h_bytes += static_cast<int64_t>(n) * 21;
+    GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
+    if (launched_ && !timed_)
+    {
+        float ms = 0.f;
+        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, ev_start_, ev_stop_));
+        stats_.kernel_ms       = ms;
+        stats_.graph_kernel_ms = ms;
+        int64_t rows = 0, exact = 0, cells = 0;
+        for (size_t i = 0; i < n; i++)
+        {
+            rows += stat_rows_h_[i];
+            exact += stat_exact_h_[i];
+            cells += static_cast<int64_t>(stat_cells_h_[i]);
+        }
+        stats_.graph_rows = rows;
+        stats_.exact_path = exact;
+        stats_.dp_cells   = cells; // sum of N_s * Wc
+        timed_          = true;
+    }
+}
+
+void B200Batch::fill_stats(cudapoa_b200_stats* out) const
+{
+    *out = stats_;
+}
+
+// get_consensus, cudapoa_batch.cuh:196-252: blocking; outputs are appended to the caller's vectors.
+StatusType B200Batch::get_consensus(std::vector<std::string>& consensus, std::vector<std::vector<uint16_t>>& coverage,
+                                    std::vector<StatusType>& output_status)
+{
+    if (!(OutputType::consensus & output_mask_))
+        return StatusType::output_type_unavailable;
+    scoped_device_switch dev(device_id_);
+    const int64_t C = batch_size_.max_consensus_size;
+    if (poa_count_ > 0 && launched_)
+    {
+        const size_t n = static_cast<size_t>(poa_count_) * static_cast<size_t>(C);
+        GW_CU_CHECK_ERR(cudaMemcpyAsync(consensus_h_, consensus_d_, n, cudaMemcpyDeviceToHost, stream_));
+        GW_CU_CHECK_ERR(cudaMemcpyAsync(coverage_h_, coverage_d_, n * 2, cudaMemcpyDeviceToHost, stream_));
+        stats_.d2h_bytes = static_cast<int64_t>(n) * 3;
+        sync_and_collect();
+    }
+    consensus.reserve(consensus.size() + poa_count_);
+    coverage.reserve(coverage.size() + poa_count_);
+    output_status.reserve(output_status.size() + poa_count_);
+    for (int32_t poa = 0; poa < poa_count_; poa++)
+    {
+        push_status(output_status, poa);
+        if (status_h_[poa] != 0)
+        {
+            consensus.emplace_back();
+            coverage.emplace_back();
+            continue;
+        }
+        // the device wrote the path end -> start, NUL terminated
+        const char* c      = reinterpret_cast<const char*>(consensus_h_ + poa * C);
+        const uint16_t* cv = coverage_h_ + poa * C;
+        const size_t len   = strnlen(c, static_cast<size_t>(C));
+        consensus.emplace_back(std::string(std::reverse_iterator<const char*>(c + len),
+                                           std::reverse_iterator<const char*>(c)));
+        coverage.emplace_back(std::vector<uint16_t>(std::reverse_iterator<const uint16_t*>(cv + len),
+                                                    std::reverse_iterator<const uint16_t*>(cv)));
+    }
+    return StatusType::success;
+}
+
+// get_msa, cudapoa_batch.cuh:255-307
+StatusType B200Batch::get_msa(std::vector<std::vector<std::string>>& msa, std::vector<StatusType>& output_status)
+{
+    if (!(OutputType::msa & output_mask_))
+        return StatusType::output_type_unavailable;
+    scoped_device_switch dev(device_id_);
+    const int64_t C = batch_size_.max_consensus_size;
+    const int64_t S = std::max(max_sequences_per_poa_, 1);
+    if (poa_count_ > 0 && launched_)
+    {
+        const size_t n = static_cast<size_t>(poa_count_) * static_cast<size_t>(S * C);
+        GW_CU_CHECK_ERR(cudaMemcpyAsync(msa_h_, msa_d_, n, cudaMemcpyDeviceToHost, stream_));
+        stats_.d2h_bytes = static_cast<int64_t>(n);
+        sync_and_collect();
+    }
+    for (int32_t poa = 0; poa < poa_count_; poa++)
+    {
+        msa.emplace_back();
+        push_status(output_status, poa);
+        if (status_h_[poa] != 0)
+            continue;
+        const int32_t n_reads = windows_h_[poa].n_reads;
+        msa.back().reserve(n_reads);
+        for (int32_t r = 0; r < n_reads; r++)
+            msa.back().emplace_back(reinterpret_cast<const char*>(msa_h_ + (poa * S + r) * C));
+    }
+    return StatusType::success;
+}
+
+// get_graphs, cudapoa_batch.cuh:309-387: node label = base, one edge source -> sink per in-edge slot.
+void B200Batch::get_graphs(std::vector<DirectedGraph>& graphs, std::vector<StatusType>& output_status)
+{
+    scoped_device_switch dev(device_id_);
+    graphs.resize(poa_count_);
+    if (poa_count_ == 0)
+        return;
+    if (launched_)
+        sync_and_collect();
+    const ArenaLayout& L = plan_.layout;
+    const int32_t idb    = plan_.size32 ? 4 : 2;
+    std::vector<uint8_t> nodes, in_cnt, in_edge, in_w;
+    for (int32_t poa = 0; poa < poa_count_; poa++)
+    {
+        push_status(output_status, poa);
+        if (status_h_[poa] != 0)
+            continue;
+        const int32_t n      = node_count_h_[poa];
+        const uint8_t* arena = arena_d_ + static_cast<int64_t>(poa) * L.stride;
+        nodes.resize(n);
+        in_cnt.resize(static_cast<size_t>(n) * 2);
+        GW_CU_CHECK_ERR(cudaMemcpy(nodes.data(), arena + L.nodes, n, cudaMemcpyDeviceToHost));
+        GW_CU_CHECK_ERR(cudaMemcpy(in_cnt.data(), arena + L.in_cnt, static_cast<size_t>(n) * 2, cudaMemcpyDeviceToHost));
+        const uint16_t* cnt = reinterpret_cast<const uint16_t*>(in_cnt.data());
+        int32_t max_slots   = 0;
+        for (int32_t i = 0; i < n; i++)
+            max_slots = std::max<int32_t>(max_slots, cnt[i]);
+        // slot-major planes: copy the first max_slots planes (n entries of each)
+        in_edge.resize(static_cast<size_t>(max_slots) * n * idb);
+        in_w.resize(static_cast<size_t>(max_slots) * n * 2);
+        if (max_slots > 0)
+        {
+            GW_CU_CHECK_ERR(cudaMemcpy2D(in_edge.data(), static_cast<size_t>(n) * idb, arena + L.in_edges,
+                                         static_cast<size_t>(L.M) * idb, static_cast<size_t>(n) * idb, max_slots,
+                                         cudaMemcpyDeviceToHost));
+            GW_CU_CHECK_ERR(cudaMemcpy2D(in_w.data(), static_cast<size_t>(n) * 2, arena + L.in_w,
+                                         static_cast<size_t>(L.M) * 2, static_cast<size_t>(n) * 2, max_slots,
+                                         cudaMemcpyDeviceToHost));
+        }
+        DirectedGraph& graph = graphs[poa];
+        for (int32_t sink = 0; sink < n; sink++)
+        {
+            graph.set_node_label(sink, std::string(1, static_cast<char>(nodes[sink])));
+            for (int32_t e = 0; e < cnt[sink]; e++)
+            {
+                const size_t at = static_cast<size_t>(e) * n + sink;
+                const int32_t src = (idb == 2) ? reinterpret_cast<const int16_t*>(in_edge.data())[at]
+                                               : reinterpret_cast<const int32_t*>(in_edge.data())[at];
+                const int32_t w = reinterpret_cast<const uint16_t*>(in_w.data())[at];
+                graph.add_edge(src, sink, w);
+            }
+        }
+    }
+}
+
+// batch.cu:27-77
+std::unique_ptr<Batch> create_batch(int32_t device_id, cudaStream_t stream, size_t max_mem, int8_t output_mask,
+                                    const BatchSize& batch_size, int16_t gap_score, int16_t mismatch_score,
+                                    int16_t match_score, bool cuda_banded_alignment)
+{
+    return std::unique_ptr<Batch>(new B200Batch(device_id, stream, max_mem, output_mask, batch_size, gap_score,
+                                                mismatch_score, match_score, cuda_banded_alignment));
+}
+
+// cudapoa.cpp:23-29.  The engine has no logger to start; the call stays for source compatibility.
+StatusType Init()
+{
+    return StatusType::success;
+}
+
+// utils.cu:24-138 with estimate_max_poas (allocate_block.hpp:364-401) evaluated with this engine's footprint and
+// cudaMemGetInfo queried once instead of once per group.
+void get_multi_batch_sizes(std::vector<BatchSize>& list_of_batch_sizes,
+                           std::vector<std::vector<int32_t>>& list_of_groups_per_batch,
+                           const std::vector<Group>& poa_groups, bool banded_alignment, bool msa_flag,
+                           int32_t band_width, std::vector<int32_t>* bins_capacity, float gpu_memory_usage_quota,
+                           int32_t mismatch_score, int32_t gap_score, int32_t match_score)
+{
+    size_t total = 0, free_mem = 0;
+    GW_CU_CHECK_ERR(cudaMemGetInfo(&free_mem, &total));
+    const double mem_per_batch = static_cast<double>(gpu_memory_usage_quota) * static_cast<double>(free_mem);
+
+    const int32_t num_groups = get_size<int32_t>(poa_groups);
+    std::vector<int64_t> max_poas(num_groups);
+    std::vector<int32_t> max_lengths(num_groups);
+    for (int32_t i = 0; i < num_groups; i++)
+    {
+        int32_t longest = 0;
+        for (const Entry& e : poa_groups[i])
+            longest = std::max(longest, e.length);
+        const BatchSize bs(longest, get_size<int32_t>(poa_groups[i]), band_width);
+        const MemoryPlan p = make_plan(bs, banded_alignment, msa_flag, gap_score, mismatch_score, match_score);
+        max_poas[i]        = static_cast<int64_t>(mem_per_batch / static_cast<double>(p.fixed_per_poa + p.score_per_poa));
+        max_lengths[i]     = longest;
+    }
+
+    int32_t num_bins = 20;
+    std::vector<int32_t> default_bins;
+    if (bins_capacity == nullptr)
+    {
+        default_bins.assign(num_bins, 1);
+        for (int32_t j = 1; j < num_bins; j++)
+            default_bins[j] = default_bins[j - 1] * 2;
+        bins_capacity = &default_bins;
+    }
+    else
+    {
+        num_bins = get_size<int32_t>(*bins_capacity);
+    }
+    std::vector<int32_t> frequency(num_bins, 0), bin_len(num_bins, 0), bin_reads(num_bins, 0);
+    std::vector<std::vector<int32_t>> members(num_bins);
+    for (int32_t i = 0; i < num_groups; i++)
+    {
+        const int64_t size_i = static_cast<int64_t>(max_lengths[i]) * get_size<int32_t>(poa_groups[i]);
+        for (int32_t j = 0; j < num_bins; j++)
+        {
+            if (max_poas[i] <= bins_capacity->at(j) || j == num_bins - 1)
+            {
+                frequency[j]++;
+                members[j].push_back(i);
+                if (static_cast<int64_t>(bin_len[j]) * bin_reads[j] < size_i)
+                {
+                    bin_len[j]   = max_lengths[i];
+                    bin_reads[j] = get_size<int32_t>(poa_groups[i]);
+                }
+                break;
+            }
+        }
+    }
+    // merge bins of smaller groups into the batch of a larger-group bin while they fit its capacity
+    for (int32_t j = 0; j < num_bins; j++)
+    {
+        if (frequency[j] == 0)
+            continue;
+        list_of_batch_sizes.emplace_back(bin_len[j], bin_reads[j], band_width);
+        list_of_groups_per_batch.push_back(members[j]);
+        for (int32_t k = j + 1; k < num_bins; k++)
+        {
+            if (frequency[k] == 0)
+                continue;
+            if (bins_capacity->at(j) < frequency[k])
+                break;
+            std::vector<int32_t>& current = list_of_groups_per_batch.back();
+            current.insert(current.end(), members[k].begin(), members[k].end());
+            frequency[k] = 0;
+        }
+    }
+}
+
+} // namespace cudapoa
+} // namespace genomeworks
+} // namespace claraparabricks
+
+namespace
+{
+__global__ void rcp_table_kernel(float* out, int32_t n)
+{
+    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+    {
+        float r;
+        float d = static_cast<float>(i);
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+        out[i] = r;
+    }
+}
+} // namespace
+
+extern "C" int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, int32_t n)
+{
+    cudaError_t e = cudaSetDevice(device_id);
+    if (e != cudaSuccess)
+        return static_cast<int32_t>(e);
+    float* d = nullptr;
+    e        = cudaMalloc(reinterpret_cast<void**>(&d), sizeof(float) * static_cast<size_t>(n));
+    if (e != cudaSuccess)
+        return static_cast<int32_t>(e);
+    rcp_table_kernel<<<(n + 255) / 256, 256>>>(d, n);
+    e = cudaMemcpy(out, d, sizeof(float) * static_cast<size_t>(n), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return static_cast<int32_t>(e);
+}

@@ -1,0 +1,25 @@
+// Native-engine extras reachable through the C ABI (cudapoa_b200_get_stats / cudapoa_b200_max_poas).
+#pragma once
+
+#include "cudapoa_b200.h"
+
+#include <cstdint>
+
+namespace claraparabricks
+{
+namespace genomeworks
+{
+namespace cudapoa
+{
+
+class EngineStatsSource
+{
+public:
+    virtual ~EngineStatsSource()                              = default;
+    virtual void fill_stats(cudapoa_b200_stats* out) const    = 0;
+    virtual int32_t max_poas() const                          = 0;
+};
+
+} // namespace cudapoa
+} // namespace genomeworks
+} // namespace claraparabricks

@@ -1,0 +1,833 @@
+// Device functions of the B200 POA engine: exact-arithmetic alignment (all modes), graph update,
+// topological sorts, consensus and MSA.  One warp owns one window.
+//
+// "Exact" = same stored values, comparisons and tie-breaks as the reference kernels
+// (cudapoa_nw.cuh, cudapoa_nw_banded.cuh, cudapoa_add_alignment.cuh, cudapoa_topsort.cuh,
+// cudapoa_generate_consensus.cuh, cudapoa_generate_msa.cuh), re-formulated: slot-major graph arrays,
+// prefix-max scans instead of the data-dependent fix-point loop, band geometry cached per row,
+// per-read node paths instead of per-edge read lists for the MSA.
+#pragma once
+
+#include "poa_layout.hpp"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace poa_b200
+{
+
+constexpr unsigned kFull = 0xffffffffu;
+
+enum : int32_t
+{
+    kStSuccess           = 0,
+    kStSeqSizeExceeded   = 2,
+    kStNodeCountExceeded = 4,
+    kStEdgeCountExceeded = 5,
+    kStLoopCountExceeded = 7,
+    kStGenericError      = 9
+};
+
+// Per-window view of the arena (pointers into global memory).
+template <typename IdT>
+struct Graph
+{
+    uint8_t* nodes;
+    uint16_t *in_cnt, *out_cnt, *aln_cnt, *cov, *kahn;
+    IdT *sorted, *pos;
+    IdT *in_edges, *out_edges, *aligned;
+    uint16_t* in_w;
+    IdT *aln_graph, *aln_read;
+    int32_t* row_bs;
+    int32_t* cscore;
+    IdT* cpred;
+    uint8_t *marks, *check;
+    IdT* msa_pos;
+    IdT* stack;
+    IdT* path;
+    int32_t M;
+
+    __device__ __forceinline__ IdT& in_edge(int32_t node, int32_t slot) const { return in_edges[slot * M + node]; }
+    __device__ __forceinline__ IdT& out_edge(int32_t node, int32_t slot) const { return out_edges[slot * M + node]; }
+    __device__ __forceinline__ IdT& aln(int32_t node, int32_t slot) const { return aligned[slot * M + node]; }
+    __device__ __forceinline__ uint16_t& weight(int32_t node, int32_t slot) const { return in_w[slot * M + node]; }
+};
+
+template <typename IdT>
+__device__ __forceinline__ Graph<IdT> make_graph(uint8_t* a, const ArenaLayout& L)
+{
+    Graph<IdT> g;
+    g.nodes     = a + L.nodes;
+    g.in_cnt    = reinterpret_cast<uint16_t*>(a + L.in_cnt);
+    g.out_cnt   = reinterpret_cast<uint16_t*>(a + L.out_cnt);
+    g.aln_cnt   = reinterpret_cast<uint16_t*>(a + L.aln_cnt);
+    g.cov       = reinterpret_cast<uint16_t*>(a + L.cov);
+    g.kahn      = reinterpret_cast<uint16_t*>(a + L.kahn);
+    g.sorted    = reinterpret_cast<IdT*>(a + L.sorted);
+    g.pos       = reinterpret_cast<IdT*>(a + L.pos);
+    g.in_edges  = reinterpret_cast<IdT*>(a + L.in_edges);
+    g.out_edges = reinterpret_cast<IdT*>(a + L.out_edges);
+    g.aligned   = reinterpret_cast<IdT*>(a + L.aligned);
+    g.in_w      = reinterpret_cast<uint16_t*>(a + L.in_w);
+    g.aln_graph = reinterpret_cast<IdT*>(a + L.aln_graph);
+    g.aln_read  = reinterpret_cast<IdT*>(a + L.aln_read);
+    g.row_bs    = reinterpret_cast<int32_t*>(a + L.row_bs);
+    g.cscore    = reinterpret_cast<int32_t*>(a + L.cscore);
+    g.cpred     = reinterpret_cast<IdT*>(a + L.cpred);
+    g.marks     = a + L.marks;
+    g.check     = a + L.check;
+    g.msa_pos   = reinterpret_cast<IdT*>(a + L.msa_pos);
+    g.stack     = reinterpret_cast<IdT*>(a + L.stack);
+    g.path      = reinterpret_cast<IdT*>(a + L.path);
+    g.M         = L.M;
+    return g;
+}
+
+// ---- score arithmetic with the reference's integer semantics -------------------------------------------
+// int16 scores: sums are formed in int and truncated when stored; int32 scores: sums wrap.
+template <typename ScoreT>
+struct ScoreOps;
+
+template <>
+struct ScoreOps<int16_t>
+{
+    static __device__ __forceinline__ int32_t add(int16_t a, int32_t b) { return static_cast<int32_t>(a) + b; }
+    static __device__ __forceinline__ int16_t narrow(int32_t v) { return static_cast<int16_t>(v); }
+    static __device__ __forceinline__ int16_t type_min() { return INT16_MIN; }
+};
+
+template <>
+struct ScoreOps<int32_t>
+{
+    static __device__ __forceinline__ int32_t add(int32_t a, int32_t b)
+    {
+        return static_cast<int32_t>(static_cast<uint32_t>(a) + static_cast<uint32_t>(b));
+    }
+    static __device__ __forceinline__ int32_t narrow(int32_t v) { return v; }
+    static __device__ __forceinline__ int32_t type_min() { return INT32_MIN; }
+};
+
+// Band sentinel, cudapoa_nw_banded.cuh:199-200.
+template <typename ScoreT>
+__device__ __forceinline__ ScoreT band_sentinel(int32_t gap, int32_t mismatch, int32_t match)
+{
+    int32_t m = min(min(gap, mismatch), -match) - 1;
+    return ScoreOps<ScoreT>::narrow(ScoreOps<ScoreT>::add(ScoreOps<ScoreT>::type_min(), 2 * abs(m)));
+}
+
+// Band gradient exactly as the reference's fast-math build computes it (cudapoa_nw_banded.cuh:206):
+// FMUL.FTZ(float(L + 1), MUFU.RCP(float(N + 1))).
+__device__ __forceinline__ float band_gradient(int32_t read_len, int32_t node_count)
+{
+    float r;
+    float d = static_cast<float>(node_count + 1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    float q;
+    float n = static_cast<float>(read_len + 1);
+    asm("mul.ftz.f32 %0, %1, %2;" : "=f"(q) : "f"(n), "f"(r));
+    return q;
+}
+
+// cudapoa_nw_banded.cuh:28-48
+__device__ __forceinline__ int32_t band_start(int32_t row, float gradient, int32_t band, int32_t max_column)
+{
+    float p;
+    float fr = static_cast<float>(row);
+    asm("mul.ftz.f32 %0, %1, %2;" : "=f"(p) : "f"(fr), "f"(gradient));
+    int32_t start = __float2int_rz(p) - band / 2;
+    start         = max(start, 0);
+    if (start + band > max_column)
+        start = max_column - band + 4;
+    start = max(start, 0);
+    return start - (start % 4);
+}
+
+__device__ __forceinline__ int32_t wrap_add(int32_t a, int32_t b)
+{
+    return static_cast<int32_t>(static_cast<uint32_t>(a) + static_cast<uint32_t>(b));
+}
+
+// Inclusive warp prefix maximum.
+__device__ __forceinline__ int32_t warp_prefix_max(int32_t v, int32_t lane)
+{
+#pragma unroll
+    for (int32_t d = 1; d < 32; d <<= 1)
+    {
+        int32_t o = __shfl_up_sync(kFull, v, d);
+        if (lane >= d)
+            v = max(v, o);
+    }
+    return v;
+}
+
+// Horizontal pass over one 128-cell chunk (4 cells per lane): H[j] = max(S[j], H[j-1] + gap) with H[-1] = carry.
+// Computed as a prefix maximum of S[j] - j*gap; equal to the reference's warp fix-point
+// (cudapoa_nw_banded.cuh:301-351, cudapoa_nw.cuh:257-313), which never truncates in this step.
+template <typename ScoreT>
+__device__ __forceinline__ void horizontal_pass(ScoreT (&c)[4], ScoreT& carry, int32_t gap, int32_t lane)
+{
+    using O      = ScoreOps<ScoreT>;
+    int32_t base = lane * 4;
+    int32_t x0   = O::add(c[0], -(base + 0) * gap);
+    int32_t x1   = max(x0, O::add(c[1], -(base + 1) * gap));
+    int32_t x2   = max(x1, O::add(c[2], -(base + 2) * gap));
+    int32_t x3   = max(x2, O::add(c[3], -(base + 3) * gap));
+    int32_t incl = warp_prefix_max(x3, lane);
+    int32_t prev = __shfl_up_sync(kFull, incl, 1);
+    int32_t cin  = O::add(carry, gap); // position -1 of the chunk
+    prev         = (lane == 0) ? cin : max(prev, cin);
+    c[0]         = O::narrow(wrap_add(max(x0, prev), (base + 0) * gap));
+    c[1]         = O::narrow(wrap_add(max(x1, prev), (base + 1) * gap));
+    c[2]         = O::narrow(wrap_add(max(x2, prev), (base + 2) * gap));
+    c[3]         = O::narrow(wrap_add(max(x3, prev), (base + 3) * gap));
+    carry        = __shfl_sync(kFull, c[3], 31);
+}
+
+// Score matrix accessor with the reference's effective semantics.
+//  banded: row stride band + 8; cell [0] is the left boundary (column 0 value while band_start == 0, the
+//          sentinel afterwards), cells [1..band] are columns band_start+1.., cells [band+1..band+7] stay at the
+//          sentinel; row 0 holds j*gap in all band + 8 cells (cudapoa_nw_banded.cuh:208-212).
+//  full:   row stride = the window's scores_width; cell [j] is column j.
+template <typename ScoreT, bool BANDED>
+struct ScoreMatrix
+{
+    ScoreT* s;
+    const int32_t* row_bs; // banded only
+    int32_t width;
+    int32_t band;
+    ScoreT sentinel;
+
+    __device__ __forceinline__ ScoreT* row(int32_t r) const { return s + static_cast<int64_t>(r) * width; }
+
+    // get_score (cudapoa_nw_banded.cuh:106-120) / direct read (cudapoa_nw.cuh)
+    __device__ __forceinline__ ScoreT get(int32_t r, int32_t column) const
+    {
+        if (!BANDED)
+            return row(r)[column];
+        if (column == 0)
+            return row(r)[0];
+        int32_t b = row_bs[r];
+        if (column > b + band || column < b)
+            return sentinel;
+        return row(r)[column - b];
+    }
+};
+
+// Needleman-Wunsch of one read against the graph, exact arithmetic.  All 32 lanes of the warp call this.
+// Returns the alignment length (alignment written end -> start into g.aln_graph / g.aln_read), or -1.
+template <typename ScoreT, typename IdT, bool BANDED>
+__device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                               ScoreT* scores, int32_t width, int32_t band, int32_t gap, int32_t mismatch,
+                               int32_t match, int32_t lane)
+{
+    using O = ScoreOps<ScoreT>;
+    ScoreMatrix<ScoreT, BANDED> M;
+    M.s        = scores;
+    M.row_bs   = g.row_bs;
+    M.width    = width;
+    M.band     = band;
+    M.sentinel = BANDED ? band_sentinel<ScoreT>(gap, mismatch, match) : 0;
+
+    const int32_t max_column = read_len + 1;
+    float gradient           = 0.f;
+    if (BANDED)
+    {
+        gradient = band_gradient(read_len, node_count);
+        for (int32_t r = lane; r <= node_count; r += 32)
+            g.row_bs[r] = band_start(r, gradient, band, max_column);
+    }
+    // row 0
+    const int32_t row0_cells = BANDED ? width : read_len + 1;
+    for (int32_t j = lane; j < row0_cells; j += 32)
+        scores[j] = O::narrow(j * gap);
+    __syncwarp();
+
+    const int32_t span = BANDED ? band : ((read_len + 127) / 128) * 128;
+    for (int32_t r = 1; r <= node_count; r++)
+    {
+        const int32_t node = g.sorted[r - 1];
+        const int32_t pc   = g.in_cnt[node];
+        const uint8_t base = g.nodes[node];
+        const int32_t bs   = BANDED ? g.row_bs[r] : 0;
+        ScoreT* out        = M.row(r);
+
+        // left boundary (cudapoa_nw_banded.cuh:214-249 / cudapoa_nw.cuh:181-210)
+        ScoreT left;
+        if (BANDED && bs != 0)
+        {
+            left = M.sentinel;
+        }
+        else if (pc == 0)
+        {
+            left = O::narrow(gap);
+        }
+        else
+        {
+            ScoreT best = O::type_min();
+            for (int32_t p = 0; p < pc; p++)
+            {
+                int32_t prow = g.pos[g.in_edge(node, p)] + 1;
+                best         = max(best, M.row(prow)[0]);
+            }
+            left = O::narrow(O::add(best, gap));
+        }
+        if (lane == 0)
+            out[0] = left;
+        if (BANDED && lane < kBandPad - 1)
+            out[band + 1 + lane] = M.sentinel;
+
+        ScoreT carry = left;
+        for (int32_t c0 = 0; c0 < span; c0 += 128)
+        {
+            const int32_t col_idx0 = c0 + lane * 4;   // cells col_idx0+1 .. col_idx0+4 of this row
+            const int32_t read_pos = bs + col_idx0;   // 0-based read position of the first cell
+            int32_t prof[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                prof[k] = (read_pos + k < read_len && read[read_pos + k] == base) ? match : mismatch;
+
+            ScoreT cell[4];
+            const bool active = BANDED || (read_pos < read_len);
+            if (active)
+            {
+                for (int32_t p = 0; p < max(pc, 1); p++)
+                {
+                    const int32_t prow = (pc == 0) ? 0 : g.pos[g.in_edge(node, p)] + 1;
+                    ScoreT cand[4];
+                    bool in_band = true;
+                    int32_t off  = read_pos;
+                    if (BANDED)
+                    {
+                        const int32_t pb = g.row_bs[prow];
+                        // get_scores, cudapoa_nw_banded.cuh:122-174
+                        in_band = !((read_pos + 1 > pb + band + 4) || (read_pos + 1 < pb));
+                        off     = read_pos - pb;
+                    }
+                    if (!in_band)
+                    {
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            cand[k] = M.sentinel;
+                    }
+                    else
+                    {
+                        const ScoreT* ps = M.row(prow) + off;
+                        ScoreT pv[5];
+#pragma unroll
+                        for (int k = 0; k < 5; k++)
+                            pv[k] = ps[k];
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            cand[k] = O::narrow(max(O::add(pv[k], prof[k]), O::add(pv[k + 1], gap)));
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        cell[k] = (p == 0) ? cand[k] : max(cell[k], cand[k]);
+                }
+            }
+            else
+            {
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    cell[k] = O::type_min(); // right of the read: never stored, never propagates leftwards
+            }
+            horizontal_pass<ScoreT>(cell, carry, gap, lane);
+            if (active)
+            {
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    out[col_idx0 + 1 + k] = cell[k];
+            }
+        }
+        __syncwarp();
+    }
+
+    // sink selection + traceback on lane 0 (cudapoa_nw_banded.cuh:369-480 / cudapoa_nw.cuh:328-459)
+    int32_t aligned = 0;
+    if (lane == 0)
+    {
+        int32_t i = 0, j = read_len;
+        ScoreT mscore = O::type_min();
+        for (int32_t idx = 1; idx <= node_count; idx++)
+        {
+            if (g.out_cnt[g.sorted[idx - 1]] == 0)
+            {
+                ScoreT s = M.get(idx, j);
+                if (mscore < s)
+                {
+                    mscore = s;
+                    i      = idx;
+                }
+            }
+        }
+        int32_t prev_i = 0, prev_j = 0, loops = 0;
+        const int32_t limit = read_len + node_count + 2;
+        while (!(i == 0 && j == 0) && loops < limit)
+        {
+            loops++;
+            const ScoreT sij = M.get(i, j);
+            bool found       = false;
+            if (i != 0)
+            {
+                const int32_t node = g.sorted[i - 1];
+                const int32_t pc   = g.in_cnt[node];
+                if (j != 0)
+                {
+                    const int32_t cost = (g.nodes[node] == read[j - 1]) ? match : mismatch;
+                    for (int32_t p = 0; p < max(pc, 1) && !found; p++)
+                    {
+                        const int32_t pi = (pc == 0) ? 0 : g.pos[g.in_edge(node, p)] + 1;
+                        if (static_cast<int32_t>(sij) == O::add(M.get(pi, j - 1), cost))
+                        {
+                            prev_i = pi;
+                            prev_j = j - 1;
+                            found  = true;
+                        }
+                    }
+                }
+                for (int32_t p = 0; p < max(pc, 1) && !found; p++)
+                {
+                    const int32_t pi = (pc == 0) ? 0 : g.pos[g.in_edge(node, p)] + 1;
+                    if (static_cast<int32_t>(sij) == O::add(M.get(pi, j), gap))
+                    {
+                        prev_i = pi;
+                        prev_j = j;
+                        found  = true;
+                    }
+                }
+            }
+            if (!found && j > 0 && static_cast<int32_t>(sij) == O::add(M.get(i, j - 1), gap))
+            {
+                prev_i = i;
+                prev_j = j - 1;
+                found  = true;
+            }
+            g.aln_graph[aligned] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
+            g.aln_read[aligned]  = static_cast<IdT>((j == prev_j) ? -1 : j - 1);
+            aligned++;
+            i = prev_i;
+            j = prev_j;
+        }
+        if (loops >= limit)
+            aligned = -1;
+    }
+    return __shfl_sync(kFull, aligned, 0);
+}
+
+// Backbone from read 0 (cudapoa_kernels.cuh:171-209), one node per lane and step.
+template <typename IdT, bool MSA>
+__device__ void init_backbone(const Graph<IdT>& g, const uint8_t* seq, const int8_t* w, int32_t len, int32_t lane)
+{
+    for (int32_t i = lane; i < len; i += 32)
+    {
+        g.nodes[i]   = seq[i];
+        g.sorted[i]  = static_cast<IdT>(i);
+        g.pos[i]     = static_cast<IdT>(i);
+        g.aln_cnt[i] = 0;
+        g.cov[i]     = 1;
+        const int32_t wi = w ? w[i] : 1;
+        if (i == 0)
+        {
+            g.in_cnt[0]    = 0;
+            g.weight(0, 0) = static_cast<uint16_t>(wi);
+        }
+        else
+        {
+            g.in_cnt[i]     = 1;
+            g.in_edge(i, 0) = static_cast<IdT>(i - 1);
+            g.weight(i, 0)  = static_cast<uint16_t>((w ? w[i - 1] : 1) + wi);
+        }
+        if (i + 1 < len)
+        {
+            g.out_cnt[i]     = 1;
+            g.out_edge(i, 0) = static_cast<IdT>(i + 1);
+        }
+        else
+        {
+            g.out_cnt[i] = 0;
+        }
+        if (MSA)
+            g.path[i] = static_cast<IdT>(i); // read 0 visits node i with base i
+    }
+}
+
+// Fuse one alignment into the graph (cudapoa_add_alignment.cuh:59-279).  Lane 0 only.
+// path (MSA only): node visited by each base of this read, replacing the reference's per-edge read lists.
+template <typename IdT, bool MSA>
+__device__ int32_t add_alignment(const Graph<IdT>& g, int32_t& node_count, int32_t aln_len, const uint8_t* read,
+                                 const int8_t* w, IdT* path, int32_t max_nodes)
+{
+    int32_t head         = -1;
+    int32_t curr         = -1;
+    uint16_t prev_weight = 0;
+    int32_t n            = node_count;
+    for (int32_t pos = aln_len - 1; pos >= 0; pos--)
+    {
+        const int32_t read_pos = g.aln_read[pos];
+        if (read_pos == -1)
+            continue;
+        const int32_t bw   = w ? w[read_pos] : 1;
+        const uint8_t base = read[read_pos];
+        const int32_t gn   = g.aln_graph[pos];
+        bool make_new      = false;
+        if (gn == -1)
+        {
+            make_new = true;
+        }
+        else if (g.nodes[gn] == base)
+        {
+            curr = gn;
+        }
+        else
+        {
+            const int32_t na = g.aln_cnt[gn];
+            int32_t hit      = -1;
+            for (int32_t a = 0; a < na; a++)
+            {
+                const int32_t aid = g.aln(gn, a);
+                if (g.nodes[aid] == base)
+                {
+                    hit = aid;
+                    break;
+                }
+            }
+            if (hit != -1)
+                curr = hit;
+            else
+                make_new = true;
+        }
+        if (make_new)
+        {
+            curr = n++;
+            if (n >= max_nodes)
+                return kStNodeCountExceeded;
+            g.nodes[curr]   = base;
+            g.out_cnt[curr] = 0;
+            g.in_cnt[curr]  = 0;
+            g.aln_cnt[curr] = 0;
+            g.cov[curr]     = 0;
+            if (gn != -1)
+            {
+                // cross-link the new node with gn and everything already aligned to gn (:150-170)
+                const int32_t na = g.aln_cnt[gn];
+                int32_t k        = 0;
+                for (int32_t a = 0; a < na; a++)
+                {
+                    const int32_t aid = g.aln(gn, a);
+                    const int32_t c   = g.aln_cnt[aid];
+                    g.aln(aid, c)     = static_cast<IdT>(curr);
+                    g.aln_cnt[aid]    = static_cast<uint16_t>(c + 1);
+                    g.aln(curr, k++)  = static_cast<IdT>(aid);
+                }
+                g.aln(gn, na)   = static_cast<IdT>(curr);
+                g.aln_cnt[gn]   = static_cast<uint16_t>(na + 1);
+                g.aln(curr, k++) = static_cast<IdT>(gn);
+                g.aln_cnt[curr] = static_cast<uint16_t>(k);
+            }
+        }
+        if (MSA)
+            path[read_pos] = static_cast<IdT>(curr);
+
+        if (head != -1)
+        {
+            bool exists       = false;
+            const int32_t inc = g.in_cnt[curr];
+            for (int32_t e = 0; e < inc; e++)
+            {
+                if (g.in_edge(curr, e) == head)
+                {
+                    exists            = true;
+                    g.weight(curr, e) = static_cast<uint16_t>(g.weight(curr, e) + (prev_weight + bw));
+                }
+            }
+            if (!exists)
+            {
+                g.in_edge(curr, inc)    = static_cast<IdT>(head);
+                g.weight(curr, inc)     = static_cast<uint16_t>(prev_weight + bw);
+                g.in_cnt[curr]          = static_cast<uint16_t>(inc + 1);
+                const int32_t outc      = g.out_cnt[head];
+                g.out_edge(head, outc)  = static_cast<IdT>(curr);
+                g.out_cnt[head]         = static_cast<uint16_t>(outc + 1);
+                if (outc + 1 >= kMaxNodeEdges || inc + 1 >= kMaxNodeEdges)
+                    return kStEdgeCountExceeded;
+            }
+        }
+        head = curr;
+        g.cov[head]++;
+        prev_weight = static_cast<uint16_t>(bw);
+    }
+    node_count = n;
+    return kStSuccess;
+}
+
+// Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88).  Lane 0 only.
+template <typename IdT>
+__device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
+{
+    int32_t tail = 0;
+    for (int32_t n = 0; n < node_count; n++)
+    {
+        const uint16_t c = g.in_cnt[n];
+        g.kahn[n]        = c;
+        if (c == 0)
+        {
+            g.pos[n]         = static_cast<IdT>(tail);
+            g.sorted[tail++] = static_cast<IdT>(n);
+        }
+    }
+    for (int32_t head = 0; head < tail; head++)
+    {
+        const int32_t node = g.sorted[head];
+        const int32_t oc   = g.out_cnt[node];
+        for (int32_t e = 0; e < oc; e++)
+        {
+            const int32_t child = g.out_edge(node, e);
+            const uint16_t c    = g.kahn[child] - 1;
+            g.kahn[child]       = c;
+            if (c == 0)
+            {
+                g.pos[child]     = static_cast<IdT>(tail);
+                g.sorted[tail++] = static_cast<IdT>(child);
+            }
+        }
+    }
+}
+
+// SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.
+// Returns false if the explicit stack would overflow its 4*M capacity.
+template <typename IdT>
+__device__ bool topsort_spoa_order(const Graph<IdT>& g, int32_t node_count)
+{
+    for (int32_t i = 0; i < node_count; i++)
+    {
+        g.marks[i] = 0;
+        g.check[i] = 1;
+    }
+    const int32_t cap = 4 * g.M - 2 * (kMaxNodeEdges + kMaxNodeAlignments);
+    int32_t top       = -1;
+    int32_t out       = 0;
+    for (int32_t i = 0; i < node_count; i++)
+    {
+        if (g.marks[i] != 0)
+            continue;
+        g.stack[++top] = static_cast<IdT>(i);
+        while (top != -1)
+        {
+            const int32_t node = g.stack[top];
+            bool valid         = true;
+            if (g.marks[node] != 2)
+            {
+                if (top >= cap)
+                    return false;
+                const int32_t ic = g.in_cnt[node];
+                for (int32_t e = 0; e < ic; e++)
+                {
+                    const int32_t b = g.in_edge(node, e);
+                    if (g.marks[b] != 2)
+                    {
+                        g.stack[++top] = static_cast<IdT>(b);
+                        valid          = false;
+                    }
+                }
+                if (g.check[node])
+                {
+                    const int32_t na = g.aln_cnt[node];
+                    for (int32_t a = 0; a < na; a++)
+                    {
+                        const int32_t aid = g.aln(node, a);
+                        if (g.marks[aid] != 2)
+                        {
+                            g.stack[++top] = static_cast<IdT>(aid);
+                            g.check[aid]   = 0;
+                            valid          = false;
+                        }
+                    }
+                }
+                if (valid)
+                {
+                    g.marks[node] = 2;
+                    if (g.check[node])
+                    {
+                        g.sorted[out] = static_cast<IdT>(node);
+                        g.pos[node]   = static_cast<IdT>(out);
+                        out++;
+                        const int32_t na = g.aln_cnt[node];
+                        for (int32_t a = 0; a < na; a++)
+                        {
+                            const int32_t aid = g.aln(node, a);
+                            g.sorted[out]     = static_cast<IdT>(aid);
+                            g.pos[aid]        = static_cast<IdT>(out);
+                            out++;
+                        }
+                    }
+                }
+                else
+                {
+                    g.marks[node] = 1;
+                }
+            }
+            if (valid)
+                top--;
+        }
+    }
+    return true;
+}
+
+// Re-score the tail of the graph after invalidating the competitors of the current best node
+// (cudapoa_generate_consensus.cuh:28-112).
+template <typename IdT>
+__device__ int32_t branch_completion(const Graph<IdT>& g, int32_t max_pos, int32_t node_count)
+{
+    int32_t node = g.sorted[max_pos];
+    const int32_t oc = g.out_cnt[node];
+    for (int32_t oe = 0; oe < oc; oe++)
+    {
+        const int32_t child = g.out_edge(node, oe);
+        const int32_t ic    = g.in_cnt[child];
+        for (int32_t ie = 0; ie < ic; ie++)
+        {
+            const int32_t id = g.in_edge(child, ie);
+            if (id != node)
+                g.cscore[id] = -1;
+        }
+    }
+    int32_t max_score = 0, max_id = 0;
+    for (int32_t p = max_pos + 1; p < node_count; p++)
+    {
+        node          = g.sorted[p];
+        int32_t pred  = -1;
+        int32_t score = -1;
+        const int32_t ic = g.in_cnt[node];
+        for (int32_t e = 0; e < ic; e++)
+        {
+            const int32_t begin = g.in_edge(node, e);
+            const int32_t bsc   = g.cscore[begin];
+            if (bsc == -1)
+                continue;
+            const int32_t w = g.weight(node, e);
+            if (score < w || (score == w && g.cscore[pred] <= bsc))
+            {
+                score = w;
+                pred  = begin;
+            }
+        }
+        g.cpred[node] = static_cast<IdT>(pred);
+        if (pred != -1)
+            score += g.cscore[pred];
+        if (max_score <= score)
+        {
+            max_score = score;
+            max_id    = node;
+        }
+        g.cscore[node] = score;
+    }
+    return max_id;
+}
+
+// Heaviest-bundle consensus (cudapoa_generate_consensus.cuh:134-276).  Lane 0 only.  Writes the consensus and
+// its coverage end -> start, NUL-terminated; returns a StatusType value.
+template <typename IdT>
+__device__ int32_t generate_consensus(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus,
+                                      uint16_t* coverage, int32_t max_consensus)
+{
+    int32_t max_id = 0, max_score = -1;
+    for (int32_t p = 0; p < node_count; p++)
+    {
+        const int32_t node = g.sorted[p];
+        int32_t pred       = -1;
+        int32_t score      = -1;
+        const int32_t ic   = g.in_cnt[node];
+        for (int32_t e = 0; e < ic; e++)
+        {
+            const int32_t w     = g.weight(node, e);
+            const int32_t begin = g.in_edge(node, e);
+            if (score < w || (score == w && g.cscore[pred] <= g.cscore[begin]))
+            {
+                score = w;
+                pred  = begin;
+            }
+        }
+        g.cpred[node] = static_cast<IdT>(pred);
+        if (pred != -1)
+            score += g.cscore[pred];
+        if (max_score <= score)
+        {
+            max_id    = node;
+            max_score = score;
+        }
+        g.cscore[node] = score;
+    }
+    int32_t loops = 0;
+    while (g.out_cnt[max_id] != 0 && loops < node_count)
+    {
+        max_id = branch_completion<IdT>(g, g.pos[max_id], node_count);
+        loops++;
+    }
+    if (loops >= node_count)
+        return kStLoopCountExceeded;
+
+    int32_t at = 0, count = 0;
+    while (true)
+    {
+        consensus[at] = g.nodes[max_id];
+        uint16_t cov  = g.cov[max_id];
+        const int32_t na = g.aln_cnt[max_id];
+        for (int32_t a = 0; a < na; a++)
+            cov = static_cast<uint16_t>(cov + g.cov[g.aln(max_id, a)]);
+        coverage[at] = cov;
+        const int32_t pred = g.cpred[max_id];
+        if (pred == -1)
+            break;
+        max_id = pred;
+        at     = min(at + 1, max_consensus - 1);
+        count++;
+    }
+    if (count >= max_consensus - 1)
+        return kStSeqSizeExceeded;
+    consensus[at + 1] = 0;
+    return kStSuccess;
+}
+
+// MSA column of every node (cudapoa_generate_msa.cuh:27-46); needs the SPOA-order sort.  Lane 0 only.
+template <typename IdT>
+__device__ int32_t msa_columns(const Graph<IdT>& g, int32_t node_count)
+{
+    int32_t col = 0;
+    for (int32_t rank = 0; rank < node_count; rank++)
+    {
+        const int32_t node = g.sorted[rank];
+        g.msa_pos[node]    = static_cast<IdT>(col);
+        const int32_t na   = g.aln_cnt[node];
+        for (int32_t k = 0; k < na; k++)
+            g.msa_pos[g.sorted[++rank]] = static_cast<IdT>(col);
+        col++;
+    }
+    return col;
+}
+
+// One MSA row per read (cudapoa_generate_msa.cuh:48-118): the whole warp writes row s -- '-' everywhere, then
+// each base into the column of the node it was fused into.
+template <typename IdT>
+__device__ void msa_rows(const Graph<IdT>& g, const uint8_t* bases, const int32_t* read_len, int32_t n_reads,
+                         uint8_t* msa, int32_t msa_len, int32_t max_consensus, int32_t max_seq, int32_t lane)
+{
+    const uint8_t* seq = bases;
+    for (int32_t s = 0; s < n_reads; s++)
+    {
+        uint8_t* row      = msa + static_cast<int64_t>(s) * max_consensus;
+        const int32_t len = read_len[s];
+        const IdT* path   = g.path + static_cast<int64_t>(s) * max_seq;
+        for (int32_t c = lane; c < msa_len; c += 32)
+            row[c] = '-';
+        if (lane == 0)
+            row[msa_len] = 0;
+        __syncwarp();
+        for (int32_t k = lane; k < len; k += 32)
+            row[g.msa_pos[path[k]]] = seq[k];
+        seq += len;
+    }
+}
+
+
+
+} // namespace poa_b200

@@ -1,0 +1,130 @@
+// Device data layout of the B200 POA engine (shared by host and device code).
+//
+// Every window owns one "arena" slice of device memory holding its graph and scratch arrays, plus a slice of
+// the score pool.  Edge-like arrays are SLOT-MAJOR: element (node, slot) lives at [slot * M + node], so that
+// the first few slots of consecutive nodes are contiguous (real POA graphs use 1-3 of the 50 slots the
+// reference semantics require, cudapoa_structs.cuh:18-21) and warp-parallel passes over nodes coalesce.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+
+namespace poa_b200
+{
+
+constexpr int32_t kMaxNodeEdges      = 50; // same limits as the reference: they are observable through
+constexpr int32_t kMaxNodeAlignments = 50; // edge_count_exceeded_maximum_graph_size
+constexpr int32_t kBandPad           = 8;  // cells right of the band kept at the sentinel
+constexpr int32_t kWarp              = 32;
+
+struct WindowDesc
+{
+    int64_t base_off;     // first base of the window in the flat bases/weights buffers
+    int64_t score_off;    // first score cell of the window in the score pool (elements)
+    int32_t read_off;     // first read of the window in read_len[]
+    int32_t n_reads;      // reads accepted into the window
+    int32_t scores_width; // full alignment: row stride of this window's score matrix
+    int32_t reserved;
+};
+
+// Byte offsets of the per-window arrays inside the window's arena slice.
+struct ArenaLayout
+{
+    int64_t stride; // bytes per window
+    int64_t nodes;
+    int64_t in_cnt, out_cnt, aln_cnt, cov, kahn; // uint16[M]
+    int64_t sorted, pos;                         // IdT[M]
+    int64_t in_edges, out_edges, aligned;        // IdT[50][M]
+    int64_t in_w;                                // uint16[50][M]
+    int64_t aln_graph, aln_read;                 // IdT[aln_cap]
+    int64_t row_bs;                              // int32[M + 1]   band start per score row
+    int64_t cscore;                              // int32[M]       consensus scores / racon marks scratch
+    int64_t cpred;                               // IdT[M]         consensus predecessors / racon stack
+    int64_t marks, check;                        // uint8[M]
+    int64_t msa_pos;                             // IdT[M]
+    int64_t stack;                               // IdT[4 * M]     DFS stack of the SPOA-order topological sort
+    int64_t path;                                // IdT[max_reads][max_seq]  node visited by each base (MSA only)
+    int32_t M;                                   // node capacity (max_nodes_per_window[_banded])
+    int32_t aln_cap;                             // alignment capacity
+    int32_t max_reads;
+    int32_t max_seq;
+};
+
+struct KernelParams
+{
+    const uint8_t* bases;
+    const int8_t* weights; // nullptr: every weight is 1
+    const int32_t* read_len;
+    const WindowDesc* windows;
+    int32_t n_windows;
+
+    uint8_t* arena;
+    ArenaLayout layout;
+    void* scores;                 // ScoreT pool
+    int64_t banded_score_stride;  // elements per window in banded mode
+
+    uint8_t* status;       // per window: 0 or a StatusType value
+    int32_t* node_count;   // per window: nodes in the final graph
+    uint8_t* consensus;    // per window max_consensus bytes (written end -> start, NUL terminated)
+    uint16_t* coverage;    // per window max_consensus entries
+    uint8_t* msa;          // per window max_reads * max_consensus bytes
+    uint32_t* stat_rows;   // per window: sum of graph rows over its alignments
+    uint32_t* stat_exact;  // per window: alignments that took the exact path
+    unsigned long long* stat_cells; // per window: sum of N_s * Wc (Wc = band, or the read length in full mode)
+
+    int32_t max_nodes;
+    int32_t max_consensus;
+    int32_t max_reads;
+    int32_t band;
+    int32_t gap, mismatch, match;
+    int32_t spoa_accurate;
+};
+
+inline int64_t align_up64(int64_t v, int64_t a)
+{
+    return (v + a - 1) / a * a;
+}
+
+// id_bytes: sizeof(IdT); msa: whether the per-read node paths are needed.
+inline ArenaLayout make_arena_layout(int32_t M, int32_t aln_cap, int32_t max_reads, int32_t max_seq, int32_t id_bytes,
+                                     bool msa)
+{
+    ArenaLayout L{};
+    L.M         = M;
+    L.aln_cap   = aln_cap;
+    L.max_reads = max_reads;
+    L.max_seq   = max_seq;
+    int64_t off = 0;
+    auto take   = [&](int64_t bytes) {
+        int64_t at = off;
+        off        = align_up64(off + bytes, 16);
+        return at;
+    };
+    const int64_t m = M;
+    L.nodes         = take(m);
+    L.in_cnt        = take(2 * m);
+    L.out_cnt       = take(2 * m);
+    L.aln_cnt       = take(2 * m);
+    L.cov           = take(2 * m);
+    L.kahn          = take(2 * m);
+    L.sorted        = take(id_bytes * m);
+    L.pos           = take(id_bytes * m);
+    L.in_edges      = take(id_bytes * m * kMaxNodeEdges);
+    L.out_edges     = take(id_bytes * m * kMaxNodeEdges);
+    L.aligned       = take(id_bytes * m * kMaxNodeAlignments);
+    L.in_w          = take(2 * m * kMaxNodeEdges);
+    L.aln_graph     = take(static_cast<int64_t>(id_bytes) * aln_cap);
+    L.aln_read      = take(static_cast<int64_t>(id_bytes) * aln_cap);
+    L.row_bs        = take(4 * (m + 1));
+    L.cscore        = take(4 * m);
+    L.cpred         = take(id_bytes * (m + 8));
+    L.marks         = take(m);
+    L.check         = take(m);
+    L.msa_pos       = take(id_bytes * m);
+    L.stack         = take(id_bytes * m * 4);
+    L.path          = take(msa ? static_cast<int64_t>(id_bytes) * max_reads * max_seq : 0);
+    L.stride        = align_up64(off, 256);
+    return L;
+}
+
+} // namespace poa_b200

@@ -1,0 +1,153 @@
+// Per-window driver kernel: backbone -> per read {align, fuse, sort} -> consensus or MSA, one warp per window.
+// Follows the control flow and error protocol of generatePOAKernel + generateConsensusKernel /
+// generateMSAKernel (cudapoa_kernels.cuh:66-359, cudapoa_generate_consensus.cuh:278-347,
+// cudapoa_generate_msa.cuh:120-224), fused into a single launch.
+#pragma once
+
+#include "poa_device.cuh"
+#include "poa_fast.cuh"
+
+namespace poa_b200
+{
+
+constexpr int32_t kWarpsPerBlock = 4;
+
+template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const KernelParams P)
+{
+    const int32_t lane = threadIdx.x & 31;
+    const int32_t w    = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (w >= P.n_windows)
+        return;
+
+    const WindowDesc wd = P.windows[w];
+    const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+    const uint8_t* seq  = P.bases + wd.base_off;
+    const int8_t* wts   = P.weights ? P.weights + wd.base_off : nullptr;
+    const int32_t* rlen = P.read_len + wd.read_off;
+    ScoreT* scores      = static_cast<ScoreT*>(P.scores) +
+                     (BANDED ? static_cast<int64_t>(w) * P.banded_score_stride : wd.score_off);
+    const int32_t width = BANDED ? P.band + kBandPad : wd.scores_width;
+
+    int32_t status     = kStSuccess;
+    int32_t node_count = 0;
+    uint32_t rows      = 0;
+    uint32_t exact     = 0;
+    unsigned long long cells = 0;
+
+    if (wd.n_reads <= 0 || rlen[0] <= 0)
+    {
+        status = kStGenericError; // the reference has no defined behaviour for an empty backbone
+    }
+    else if (rlen[0] > P.layout.M)
+    {
+        status = kStNodeCountExceeded;
+    }
+    else
+    {
+        node_count = rlen[0];
+        init_backbone<IdT, MSA>(g, seq, wts, node_count, lane);
+        __syncwarp();
+
+        for (int32_t s = 1; s < wd.n_reads; s++)
+        {
+            seq += rlen[s - 1];
+            if (wts)
+                wts += rlen[s - 1];
+            const int32_t len = rlen[s];
+            if (node_count >= P.max_nodes) // cudapoa_kernels.cuh:220-226
+            {
+                status = kStNodeCountExceeded;
+                break;
+            }
+            int32_t aln_len = kFastNotTaken;
+            if (BANDED && sizeof(ScoreT) == 2)
+                aln_len = align_fast_banded16<IdT>(g, node_count, seq, len, reinterpret_cast<int16_t*>(scores),
+                                                   P.band, P.gap, P.mismatch, P.match, lane);
+            if (aln_len == kFastNotTaken)
+            {
+                aln_len = align_exact<ScoreT, IdT, BANDED>(g, node_count, seq, len, scores, width, P.band, P.gap,
+                                                           P.mismatch, P.match, lane);
+                exact++;
+            }
+            rows += static_cast<uint32_t>(node_count);
+            cells += static_cast<unsigned long long>(node_count) * static_cast<unsigned long long>(BANDED ? P.band : len);
+            if (aln_len == -1) // cudapoa_kernels.cuh:281-289
+            {
+                status = kStLoopCountExceeded;
+                break;
+            }
+            int32_t rc = kStSuccess;
+            if (lane == 0)
+            {
+                rc = add_alignment<IdT, MSA>(g, node_count, aln_len, seq, wts,
+                                             MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
+                                             P.max_nodes);
+                if (rc == kStSuccess)
+                {
+                    if (P.spoa_accurate)
+                    {
+                        if (!topsort_spoa_order<IdT>(g, node_count))
+                            rc = kStGenericError;
+                    }
+                    else
+                    {
+                        topsort_kahn<IdT>(g, node_count);
+                    }
+                }
+            }
+            rc         = __shfl_sync(kFull, rc, 0);
+            node_count = __shfl_sync(kFull, node_count, 0);
+            __syncwarp();
+            if (rc != kStSuccess) // cudapoa_kernels.cuh:314-319
+            {
+                status = rc;
+                break;
+            }
+        }
+    }
+
+    if (status == kStSuccess)
+    {
+        if (!MSA)
+        {
+            if (lane == 0)
+                status = generate_consensus<IdT>(g, node_count, P.consensus + static_cast<int64_t>(w) * P.max_consensus,
+                                                 P.coverage + static_cast<int64_t>(w) * P.max_consensus,
+                                                 P.max_consensus);
+        }
+        else
+        {
+            int32_t msa_len = 0;
+            if (lane == 0)
+            {
+                if (!topsort_spoa_order<IdT>(g, node_count))
+                    status = kStGenericError;
+                else
+                {
+                    msa_len = msa_columns<IdT>(g, node_count);
+                    if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
+                        status = kStSeqSizeExceeded;
+                }
+            }
+            status  = __shfl_sync(kFull, status, 0);
+            msa_len = __shfl_sync(kFull, msa_len, 0);
+            __syncwarp();
+            if (status == kStSuccess)
+                msa_rows<IdT>(g, P.bases + wd.base_off, rlen, wd.n_reads,
+                              P.msa + static_cast<int64_t>(w) * P.max_reads * P.max_consensus, msa_len,
+                              P.max_consensus, P.layout.max_seq, lane);
+        }
+    }
+
+    if (lane == 0)
+    {
+        P.status[w]     = static_cast<uint8_t>(status);
+        P.node_count[w] = node_count;
+        P.stat_rows[w]  = rows;
+        P.stat_exact[w] = exact;
+        P.stat_cells[w] = cells;
+    }
+}
+
+} // namespace poa_b200

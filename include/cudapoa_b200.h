@@ -179,6 +179,12 @@ int32_t CUDAPOA_CABI(get_multi_batch_sizes)(const int32_t* read_lengths, const i
 int32_t CUDAPOA_CABI(get_stats)(const cudapoa_b200_batch* batch, cudapoa_b200_stats* out);
 int32_t CUDAPOA_CABI(max_poas)(const cudapoa_b200_batch* batch);
 
+/* Native library only (no reference counterpart): out[i] = MUFU.RCP(float(i)) for i < n, evaluated on `device_id`.
+ * The reference is built with -use_fast_math, so its band geometry divides through this instruction
+ * (cudapoa_nw_banded.cuh:206); tests/golden/make_rcp_table.py stores the table so that the CPU oracle can
+ * reproduce the device's band starts bit for bit.  Returns 0, or a cudaError_t value. */
+int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, int32_t n);
+
 #ifdef __cplusplus
 }
 #endif
