@@ -782,3 +782,74 @@ extern "C" int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, i
     cudaFree(d);
     return static_cast<int32_t>(e);
 }
+
+namespace
+{
+template <int KIND>
+__global__ void __launch_bounds__(256) dpx_peak_kernel(uint32_t* out, int32_t iters, uint32_t seed)
+{
+    uint32_t a[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        a[k] = seed + threadIdx.x * 8u + k;
+    const uint32_t b = seed | 0x00010001u;
+    for (int32_t i = 0; i < iters; i++)
+    {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+        {
+            if (KIND == 0)
+                a[k] = __viaddmax_s16x2(a[k], b, a[(k + 1) & 7]);
+            else
+                a[k] = static_cast<uint32_t>(__viaddmax_s32(static_cast<int32_t>(a[k]), static_cast<int32_t>(b),
+                                                            static_cast<int32_t>(a[(k + 1) & 7])));
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        x ^= a[k];
+    if (x == 0x12345678u)
+        out[blockIdx.x] = x;
+}
+} // namespace
+
+extern "C" int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* instr_per_s, double* ms_out)
+{
+    cudaError_t e = cudaSetDevice(device_id);
+    if (e != cudaSuccess)
+        return static_cast<int32_t>(e);
+    cudaDeviceProp prop{};
+    cudaGetDeviceProperties(&prop, device_id);
+    const int32_t blocks = prop.multiProcessorCount * 8; // 8 x 256 threads = 2048 threads per SM
+    const int32_t iters  = 1 << 16;
+    uint32_t* d          = nullptr;
+    cudaMalloc(reinterpret_cast<void**>(&d), sizeof(uint32_t) * blocks);
+    cudaEvent_t t0, t1;
+    cudaEventCreate(&t0);
+    cudaEventCreate(&t1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++)
+    {
+        cudaEventRecord(t0);
+        if (kind == 0)
+            dpx_peak_kernel<0><<<blocks, 256>>>(d, iters, 12345u + rep);
+        else
+            dpx_peak_kernel<1><<<blocks, 256>>>(d, iters, 12345u + rep);
+        cudaEventRecord(t1);
+        e = cudaEventSynchronize(t1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, t0, t1);
+        if (rep > 0 && ms < best)
+            best = ms;
+    }
+    cudaEventDestroy(t0);
+    cudaEventDestroy(t1);
+    cudaFree(d);
+    const double instr = static_cast<double>(blocks) * 256.0 * 8.0 * static_cast<double>(iters);
+    if (instr_per_s != nullptr)
+        *instr_per_s = instr / (static_cast<double>(best) * 1e-3);
+    if (ms_out != nullptr)
+        *ms_out = best;
+    return static_cast<int32_t>(e);
+}

@@ -185,6 +185,11 @@ int32_t CUDAPOA_CABI(max_poas)(const cudapoa_b200_batch* batch);
  * reproduce the device's band starts bit for bit.  Returns 0, or a cudaError_t value. */
 int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, int32_t n);
 
+/* Native library only: DPX issue-rate micro-benchmark used as the roofline denominator.
+ * Runs independent __viaddmax_s16x2 (kind 0) or __viaddmax_s32 (kind 1) chains, 8 accumulators per thread, on every
+ * SM of `device_id` and returns thread-level instructions per second in *instr_per_s and the kernel time in *ms. */
+int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* instr_per_s, double* ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,219 @@
+"""GPU: the native engine, through the C ABI, against (1) the CPU oracle on the same seeded windows, (2) the golden
+outputs of the reference cudapoa, (3) the live reference build when oracle/_ref/libcudapoa_ref.so travelled, and
+(4) size-independent properties at larger sizes.  Bit-exact everywhere: all arithmetic is integer."""
+import random
+
+import numpy as np
+import pytest
+
+import oraclelib
+import parity
+from cases import CASES, case_windows
+from claragenomicsanalysis_b200 import _cabi
+from claragenomicsanalysis_b200.cudapoa import CudaPoaBatch
+from claragenomicsanalysis_b200.windows import WindowSet, generate_windows
+
+pytestmark = pytest.mark.gpu
+
+MEM = 4 << 30
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _cabi.native()  # raises if the CUDA extension is missing: no fallback
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_native_matches_oracle_and_reference_golden(lib, name):
+    case = CASES[name]
+    eng = case["engine"]
+    output = eng["output"]
+    ws = case_windows(name)
+    n = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+    o = parity.run_oracle(ws, want_graphs=True, **eng)
+    assert parity.compare(n, o, output) == []
+    for w in range(len(ws)):
+        if n["status"][w] == 0:
+            assert n["graphs"][w][0] == o["graphs"][w][0]
+            assert n["graphs"][w][1] == o["graphs"][w][1]
+    g = parity.load_golden("reference_%s.json" % name)
+    assert g is not None
+    assert [int(s) for s in n["status"]] == g["status"]
+    assert parity.digests(n, output) == g["digest"]
+    assert n["seq_status"] == g["seq_status"]
+    stats = n["stats"][0]
+    assert stats["dp_cells"] == o["dp_cells"]
+
+
+@pytest.mark.parametrize("name", ["cfg2_banded16_consensus", "cfg3_banded16_msa", "full16_consensus",
+                                  "banded32_consensus"])
+def test_native_matches_live_reference(lib, name):
+    if not oraclelib.have_ref_cudapoa():
+        pytest.skip("reference build not present on this box")
+    case = CASES[name]
+    ws = case_windows(name)
+    n = parity.run_abi(lib, ws, max_mem=MEM, **case["engine"])
+    r = parity.run_abi(parity.ref_lib(), ws, max_mem=MEM, **case["engine"])
+    assert parity.compare(n, r, case["engine"]["output"]) == []
+
+
+# ---- Batch API behaviour, after cudapoa/tests/Test_CudapoaBatch.cu:66-199 -----------------------------------------
+def test_initialize_and_zero_memory(lib):
+    b = CudaPoaBatch(5, 1024, MEM, lib=lib)
+    assert b.total_poas == 0
+    b.close()
+    with pytest.raises(RuntimeError):
+        CudaPoaBatch(5, 1024, 0, lib=lib)
+
+
+def test_add_and_reset_counts(lib):
+    b = CudaPoaBatch(5, 1024, MEM, lib=lib)
+    ws = WindowSet.from_lists([[""]])  # the all-zero Entry{} of Test_CudapoaBatch.cu:80-93
+    rc, added = b.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads)
+    assert rc == 0 and added == 1 and b.total_poas == 1
+    b.reset()
+    assert b.total_poas == 0
+    b.close()
+
+
+def test_per_sequence_status_codes(lib):
+    b = CudaPoaBatch(10, 1024, MEM, lib=lib)
+    rc, st = b.add_poa_group(["A" * 20] * 11)
+    assert rc == 0 and b.total_poas == 1
+    assert st[:10] == [0] * 10 and st[10] == 3  # exceeded_maximum_sequences_per_poa
+    rc, st = b.add_poa_group(["A" * 1024, "A" * 1025])
+    assert rc == 0 and st == [0, 2]  # exceeded_maximum_sequence_size
+    b.close()
+
+
+def test_identical_sequences_give_themselves(lib):
+    b = CudaPoaBatch(10, 1024, MEM, lib=lib)
+    seq = "A" * 1023
+    ws = WindowSet.from_lists([[seq, seq, seq]], weights=[[np.ones(1023, np.int8)] * 3])
+    b.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads, weights=ws.weights)
+    b.generate_poa()
+    cons, cov, st = b.get_consensus()
+    assert st == [0] and cons == [seq] and cov[0] == [3] * 1023
+    b.close()
+
+
+def test_negative_weight_is_invalid_argument(lib):
+    b = CudaPoaBatch(10, 1024, MEM, lib=lib)
+    ws = WindowSet.from_lists([["ACGT", "ACGT"]], weights=[[np.array([1, 1, 1, 1], np.int8),
+                                                              np.array([1, -1, 1, 1], np.int8)]])
+    with pytest.raises(ValueError):
+        b.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads, weights=ws.weights)
+    b.close()
+
+
+def test_output_type_unavailable(lib):
+    b = CudaPoaBatch(10, 256, MEM, output_type="msa", lib=lib)
+    b.add_poa_group(["ACGTACGT", "ACGAACGT"])
+    b.generate_poa()
+    with pytest.raises(RuntimeError):
+        b.get_consensus()
+    msa, st = b.get_msa()
+    assert st == [0] and len(msa[0]) == 2
+    b.close()
+    with pytest.raises(RuntimeError):
+        CudaPoaBatch(10, 256, MEM, output_type="error_input", lib=lib)
+
+
+def test_batch_full_returns_exceeded_maximum_poas(lib):
+    bs_mem = 64 << 20
+    b = CudaPoaBatch(4, 256, bs_mem, cuda_banded_alignment=True, lib=lib)
+    cap = b.max_poas
+    assert cap >= 1
+    ws = generate_windows(cap + 3, template_length=100, n_reads=4)
+    rc, added = b.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads)
+    assert rc == 1 and added == cap and b.total_poas == cap  # exceeded_maximum_poas
+    b.close()
+
+
+# ---- pygenomeworks binding behaviour, after pygenomeworks/test/test_cudapoa_bindings.py ----------------------------
+@pytest.mark.parametrize("banded", [False, True])
+def test_simple_batches(lib, banded):
+    b = CudaPoaBatch(10, 1024, MEM, cuda_banded_alignment=banded, lib=lib)
+    b.add_poa_group(["ACTGACTG", "ACTTACTG", "ACGGACTG", "ATCGACTG"])
+    b.add_poa_group(["ACTGAC", "ACTTAC", "ACGGAC", "ATCGAC"])
+    b.generate_poa()
+    cons, cov, st = b.get_consensus()
+    assert len(cons) == 2 and b.total_poas == 2 and st == [0, 0]
+    b.reset()
+    assert b.total_poas == 0
+    b.close()
+
+
+def test_graph_of_three_reads(lib):
+    b = CudaPoaBatch(10, 1024, MEM, lib=lib)
+    b.add_poa_group(["ACTGACTG", "ACTTACTG", "ACTCACTG"])
+    b.generate_poa()
+    b.get_consensus()
+    graphs, st = b.get_graphs()
+    assert len(graphs) == 1
+    assert graphs[0].number_of_nodes() == 10 and graphs[0].number_of_edges() == 11
+    b.close()
+
+
+def test_complex_batch_recovers_truth(lib):
+    random.seed(2)
+    ref = "".join(random.choice("ACGT") for _ in range(500))
+    reads = ["".join(r if random.random() > 0.02 else random.choice("ACGT") for r in ref) for _ in range(100)]
+    b = CudaPoaBatch(1000, 1024, MEM, lib=lib)
+    b.add_poa_group(reads)
+    b.generate_poa()
+    cons, cov, st = b.get_consensus()
+    assert st == [0] and cons[0] == ref
+    b.close()
+
+
+# ---- MSA, after cudapoa/tests/Test_CudapoaGenerateMSA2.cu ---------------------------------------------------------
+def test_msa_rows_spell_their_reads(lib):
+    ws = generate_windows(1, start_index=31, template_length=50, n_reads=500, read_error=0.2)
+    n = parity.run_abi(lib, ws, max_seq=1024, max_reads=500, banded=False, output="msa", max_mem=8 << 30)
+    assert n["status"] == [0]
+    rows = n["msa"][0]
+    assert len(rows) == 500 and len(set(len(r) for r in rows)) == 1
+    assert [r.replace("-", "") for r in rows] == ws.window(0)
+
+
+def test_msa_overflow_status(lib):
+    # max_consensus_size == max_sequence_size, backbone one short of it (Test_CudapoaGenerateMSA2.cu:127-158)
+    bs = CudaPoaBatch(10, 1024, MEM, output_type="msa", lib=lib).batch_size
+    bs.max_consensus_size = bs.max_sequence_size
+    ws = generate_windows(1, start_index=77, template_length=1010, n_reads=10, backbone_error=0.0, read_error=0.15)
+    n = parity.run_abi(lib, ws, max_seq=1024, max_reads=10, banded=False, output="msa", max_mem=MEM, batch_size_c=bs)
+    o = parity.run_oracle(ws, max_seq=1024, max_reads=10, banded=False, output="msa", batch_size=bs)
+    assert n["status"] == o["status"] == [2]  # exceeded_maximum_sequence_size
+
+
+def test_spoa_accurate_mode_matches_spoa_msa(lib, monkeypatch):
+    if not oraclelib.have_ref_spoa():
+        pytest.skip("reference SPOA not built")
+    monkeypatch.setenv("CUDAPOA_B200_SPOA_ACCURATE", "1")
+    ws = generate_windows(4, start_index=500, template_length=120, n_reads=12)
+    n = parity.run_abi(lib, ws, max_seq=256, max_reads=12, banded=False, output="msa", max_mem=MEM)
+    o = parity.run_oracle(ws, max_seq=256, max_reads=12, banded=False, output="msa", spoa_accurate=True)
+    assert parity.compare(n, o, "msa") == []
+    sp = oraclelib.SpoaRun(ws, msa=True)
+    assert [n["msa"][w] for w in range(4)] == [sp.msa(w) for w in range(4)]
+
+
+# ---- properties at larger sizes ------------------------------------------------------------------------------------
+def test_large_batch_properties(lib):
+    """2048 cfg-2 windows: all succeed, results do not depend on how the windows are split into batches or on
+    where a window sits in the batch, and a second run is identical."""
+    base = generate_windows(256, template_length=500, n_reads=30)
+    ws = base.tile(2048)
+    eng = dict(max_seq=640, max_reads=30, band=256, banded=True, output="consensus")
+    a = parity.run_abi(lib, ws, max_mem=24 << 30, **eng)
+    assert set(a["status"]) == {0}
+    da = parity.digests(a, "consensus")
+    assert da[:256] * 8 == da  # tiled windows give tiled results
+    b = parity.run_abi(lib, ws.slice(0, 600), max_mem=1 << 30, **eng)  # forces several batch rounds
+    assert parity.digests(b, "consensus") == da[:600]
+    o = parity.run_oracle(base.slice(0, 8), **eng)
+    assert parity.digests(o, "consensus") == da[:8]
+    lens = [len(c) for c in a["consensus"][:256]]
+    assert 450 <= min(lens) and max(lens) <= 560
+    assert all(max(cov) <= 30 for cov in a["coverage"][:256])
