@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""Benchmark of the B200 cudapoa engine on BASELINE.json's metric: POA windows/s (+ GCUPS).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference]
+
+Workload at every N: BASELINE.json configs[1] -- Racon-style polishing windows, 500 bp template x 30 ONT-like reads,
+static band 256, int16 scores, consensus output (SURVEY.md 8(d) "cfg 2").  One "step" = one batch of `--windows`
+such windows per GPU through the hot path.  Windows are independent: each rank owns its own windows (weak scaling),
+no collective on the data path; torch.distributed is used for the barrier and the max-over-ranks only.
+
+Native arm, three numbers per run:
+  value      windows/s with the batch's inputs already resident in HBM: K launches of the POA kernel timed with CUDA
+             events on the batch's stream (cudapoa_b200_bench_relaunch), max over ranks.
+  e2e        windows/s through the reference-facing C ABI with HOST buffers every step: reset -> add_poa_group (host
+             staging) -> generate_poa (H2D + kernel) -> get_consensus (D2H + decode), wall clock between device syncs.
+  roofline   HBM view (algorithmic bytes of SURVEY.md 8(d) / kernel time vs MEASURED_PEAKS.json) and, in
+             `roofline_dpx`, the binding DPX view: achieved GCUPS vs the s16x2 DPX issue rate measured in this run.
+  cpu_baseline  the reference repository's CPU implementation of the same job (SPOA, 3rdparty/spoa, built unmodified
+             into oracle/_ref/libspoa_ref.so) on all host cores over a bounded sample, plus consensus agreement rate.
+
+Reference arm (--impl reference): SPOA on the host cores, same metric/config/unit, bounded sample per step.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "poa_windows_per_second"
+UNIT = "windows/s"
+WORKLOAD = "cfg2: 500 bp x 30 ONT-like reads, banded(256) int16 consensus, scores 8/-6/-8"
+ENGINE = dict(max_seq=640, max_reads=30, band=256)
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.rows = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 8:
+                self.rows.append(parts)
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        pw = [float(r[3]) for r in self.rows if r[3].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def make_windows(n_windows, distinct, start_index):
+    from claragenomicsanalysis_b200.windows import config_windows
+
+    base = config_windows("cfg2", min(distinct, n_windows), start_index=start_index)
+    return base.tile(n_windows), base
+
+
+def algorithmic_bytes(ws, total_consensus_chars):
+    """bases + 32 B descriptor per window + 2 B per read length + consensus (1 B) and coverage (2 B)
+    per consensus base.  Weights are not transferred when every weight is 1."""
+    return int(ws.n_bases + 32 * len(ws) + 2 * ws.n_reads + 3 * total_consensus_chars)
+
+
+def spoa_run(ws, threads=0):
+    import oraclelib
+
+    return oraclelib.SpoaRun(ws, match=8, mismatch=-6, gap=-8, msa=False, threads=threads)
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args, rank, world):
+    """SPOA (the reference repository's CPU POA) on all host cores; rank 0 only."""
+    if rank != 0:
+        return
+    import oraclelib
+
+    if not oraclelib.have_ref_spoa():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libspoa_ref.so was not built"}))
+        return
+    cores = host_cores()
+    probe, _ = make_windows(max(2 * cores, 8), 4096, 0)
+    r = spoa_run(probe, cores)
+    rate = len(probe) / max(r.seconds, 1e-6)
+    budget = min(10.0, 150.0 / max(args.steps + args.warmup, 1))
+    n = max(cores, int(rate * budget))
+    ws, _ = make_windows(n, 4096, 0)
+    for _ in range(args.warmup):
+        spoa_run(ws, cores)
+    t = 0.0
+    cells = 0
+    for _ in range(args.steps):
+        r = spoa_run(ws, cores)
+        t += r.seconds
+        cells += r.cells
+    value = n * args.steps / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32 (SPOA AVX2 engine, full alignment)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "windows_per_step": n, "engine": "SPOA v3.0.0 kNW linear gaps, full (unbanded)"},
+        "gcups": cells / t / 1e9,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": "%d cfg2 windows per step x %d steps, SPOA on %d threads" % (n, args.steps, cores)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_native(args, rank, world, local_rank):
+    import torch  # device sync + torch.distributed plumbing only
+
+    from claragenomicsanalysis_b200 import _cabi, build
+    from claragenomicsanalysis_b200.cudapoa import CudaPoaBatch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the POA path has no CPU fallback")
+    build.build()
+    lib = _cabi.native()
+    dll = ctypes.CDLL(_cabi.NATIVE_LIB_PATH)
+    dll.cudapoa_b200_bench_relaunch.restype = ctypes.c_double
+    dll.cudapoa_b200_bench_relaunch.argtypes = [ctypes.c_void_p, ctypes.c_int32]
+    dll.cudapoa_b200_debug_dpx_peak.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_double),
+                                                ctypes.POINTER(ctypes.c_double)]
+
+    device = local_rank
+    torch.cuda.set_device(device)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    ws, base = make_windows(args.windows, args.distinct, rank * args.distinct)
+    free_b, total_b = torch.cuda.mem_get_info(device)
+    max_mem = int(min(free_b * 0.85, args.max_mem_gb * (1 << 30)))
+    batch = CudaPoaBatch(ENGINE["max_reads"], ENGINE["max_seq"], max_mem, output_type="consensus", device_id=device,
+                         cuda_banded_alignment=True, alignment_band_width=ENGINE["band"], lib=lib)
+    if batch.max_poas < len(ws):
+        ws = ws.slice(0, batch.max_poas)
+    n_win = len(ws)
+
+    def e2e_step():
+        batch.reset()
+        rc, added = batch.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads)
+        if added != n_win:
+            raise RuntimeError("batch accepted %d of %d windows (status %d)" % (added, n_win, rc))
+        batch.generate_poa()
+        batch.fetch("consensus")
+
+    # first pass: stage, run, fetch -- also the correctness gate of this run
+    e2e_step()
+    statuses = batch.result_statuses()
+    n_ok = sum(1 for s in statuses if s == 0)
+    digest0 = batch.result_digest()
+    cons_chars = batch.result_total_chars()
+    stats = batch.stats()
+    if n_ok != n_win:
+        raise RuntimeError("only %d of %d windows succeeded" % (n_ok, n_win))
+
+    sampler = ClockSampler(device)
+    # ---- resident leg: inputs already in HBM, K launches timed with CUDA events on the batch's stream ----
+    for _ in range(max(args.warmup, 3)):
+        dll.cudapoa_b200_bench_relaunch(batch._handle, 1)
+    barrier()
+    sampler.start()
+    ms_total = dll.cudapoa_b200_bench_relaunch(batch._handle, args.steps)
+    barrier()
+    clocks = sampler.stop()
+    if ms_total <= 0:
+        raise RuntimeError("relaunch failed: " + lib.error())
+    ms_step = max_over_ranks(ms_total / args.steps)
+    batch.fetch("consensus")
+    if batch.result_digest() != digest0:
+        raise RuntimeError("results changed between launches")
+    total_windows = sum_over_ranks(float(n_win))
+    total_cells = sum_over_ranks(float(stats["dp_cells"]))
+    value = total_windows / (ms_step * 1e-3)
+    gcups = total_cells / (ms_step * 1e-3) / 1e9
+
+    # ---- end-to-end leg: host buffers -> C ABI -> host results every step ----
+    for _ in range(max(args.warmup, 3)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    e2e_s = max_over_ranks((t1 - t0) / args.steps)
+    barrier()
+    st2 = batch.stats()
+    e2e_value = total_windows / e2e_s
+    if batch.result_digest() != digest0:
+        raise RuntimeError("end-to-end results differ from the first pass")
+
+    # ---- rooflines ----
+    hbm_peak, hbm_src = measured_peaks()
+    alg_bytes = algorithmic_bytes(ws, cons_chars)
+    achieved_gbs = alg_bytes / (ms_step * 1e-3) / 1e9 if world == 1 else sum_over_ranks(float(alg_bytes)) / (ms_step * 1e-3) / 1e9 / world
+    r16 = ctypes.c_double(0)
+    r16ms = ctypes.c_double(0)
+    dll.cudapoa_b200_debug_dpx_peak(device, 0, ctypes.byref(r16), ctypes.byref(r16ms))
+    dpx_peak_gcups = r16.value / 1e9  # >= 1 s16x2 DPX instruction per cell
+    per_gpu_gcups = gcups / world
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "windows_per_step_per_gpu": n_win, "distinct_windows_per_gpu": len(base),
+                   "batch_size": "BatchSize(640, 30, 256)", "l2": "inputs + per-window state larger than L2 (%.1f GB "
+                   "touched per step)" % (n_win * 2.7e-3), "sharding": "windows split across ranks, no collective"},
+        "gcups": gcups,
+        "dp_cells_per_window": stats["dp_cells"] / n_win,
+        "exact_path_alignments": stats["exact_path"], "alignments": stats["reads_aligned"],
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(st2["h2d_bytes"]),
+                "d2h_bytes_per_step": int(st2["d2h_bytes"]), "ms_per_step": e2e_s * 1e3,
+                "path": "add_poa_groups_flat(host numpy) -> generate_poa -> get_consensus via C ABI"},
+        "gpu_launches": 2 * args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                     "algorithmic_bytes_per_launch": alg_bytes,
+                     "note": "integer DP: the binding roofline is the DPX issue rate, see roofline_dpx"},
+        "roofline_dpx": {"bound": "dpx-int16", "achieved": per_gpu_gcups, "peak": dpx_peak_gcups, "unit": "GCUPS",
+                         "frac": per_gpu_gcups / dpx_peak_gcups if dpx_peak_gcups > 0 else None,
+                         "peak_source": "VIADDMNMX.S16x2 thread-instructions/s measured in this run "
+                                        "(cudapoa_b200_debug_dpx_peak, %.2f ms)" % r16ms.value},
+        "clocks": clocks,
+    }
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args, base, batch, lib)
+        ref_gpu = reference_cudapoa(args, base)
+        if ref_gpu is not None:
+            line["reference_cudapoa_gpu"] = ref_gpu
+    batch.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, base, batch, lib):
+    """SPOA on all host cores over a bounded sample of the same windows + consensus agreement with the engine."""
+    import oraclelib
+
+    if not oraclelib.have_ref_spoa():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "libspoa_ref.so not built"}
+    cores = host_cores()
+    probe = base.slice(0, max(2 * cores, 8))
+    r = spoa_run(probe, cores)
+    rate = len(probe) / max(r.seconds, 1e-6)
+    n = int(min(len(base), max(cores, rate * args.cpu_seconds)))
+    sample = base.slice(0, n)
+    r = spoa_run(sample, cores)
+    # agreement: the engine's consensus for the same windows
+    batch.reset()
+    batch.add_poa_groups_flat(sample.bases, sample.read_lengths, sample.window_n_reads)
+    batch.generate_poa()
+    cons, _, _ = batch.get_consensus()
+    agree = sum(1 for w in range(n) if cons[w] == r.consensus(w))
+    return {"value": n / r.seconds, "unit": UNIT, "cores": cores, "kind": "reference",
+            "gcups": r.cells / r.seconds / 1e9,
+            "sample": "%d cfg2 windows, SPOA v3.0.0 (AVX2, full alignment) on %d threads, %.1f s" % (n, cores, r.seconds),
+            "consensus_agreement_with_engine": agree / n}
+
+
+def reference_cudapoa(args, base):
+    """The reference cudapoa kernels (GenomeWorks 0.5.0, built unmodified for sm_100a) on the same GPU: the kernel
+    to beat.  Reported only; not part of any timed region of the native arm."""
+    import oraclelib
+
+    if not oraclelib.have_ref_cudapoa():
+        return None
+    try:
+        import parity
+
+        from claragenomicsanalysis_b200.cudapoa import CudaPoaBatch
+
+        n = min(len(base), 1024)
+        ws = base.slice(0, n)
+        b = CudaPoaBatch(ENGINE["max_reads"], ENGINE["max_seq"], 8 << 30, output_type="consensus",
+                         cuda_banded_alignment=True, alignment_band_width=ENGINE["band"], lib=parity.ref_lib())
+        best = None
+        for _ in range(3):
+            b.reset()
+            t0 = time.perf_counter()
+            rc, added = b.add_poa_groups_flat(ws.bases, ws.read_lengths, ws.window_n_reads)
+            b.generate_poa()
+            b.fetch("consensus")
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        b.close()
+        return {"value": added / best, "unit": UNIT, "windows": added,
+                "note": "end-to-end through the same C ABI, best of 3, one batch on one stream"}
+    except Exception as e:  # the comparison is optional
+        return {"error": str(e)[:200]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--windows", type=int, default=16384, help="windows per step per GPU")
+    ap.add_argument("--distinct", type=int, default=1024, help="distinct generated windows (tiled to --windows)")
+    ap.add_argument("--max-mem-gb", type=float, default=120.0)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = env_int("RANK", 0)
+    world = env_int("WORLD_SIZE", 1)
+    local_rank = env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_native(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -531,4 +531,19 @@ int32_t CUDAPOA_CABI(max_poas)(const cudapoa_b200_batch* batch)
 #endif
 }
 
+#ifdef CUDAPOA_B200_NATIVE
+double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations)
+{
+    double ms  = -1.0;
+    int32_t rc = guarded([&]() {
+        auto* src = dynamic_cast<poa::EngineStatsSource*>(batch->impl.get());
+        if (src == nullptr)
+            return -1;
+        ms = src->relaunch(iterations);
+        return 0;
+    });
+    return rc == 0 ? ms : -1.0;
+}
+#endif
+
 } // extern "C"

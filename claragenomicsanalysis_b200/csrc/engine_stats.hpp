@@ -18,6 +18,9 @@ public:
     virtual ~EngineStatsSource()                              = default;
     virtual void fill_stats(cudapoa_b200_stats* out) const    = 0;
     virtual int32_t max_poas() const                          = 0;
+    // Benchmark hook: re-run the device work of the last generate_poa() `iterations` times on inputs that are
+    // already resident in device memory; returns the CUDA-event time of all iterations in ms (< 0: nothing staged).
+    virtual double relaunch(int32_t iterations) = 0;
 };
 
 } // namespace cudapoa

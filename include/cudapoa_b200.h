@@ -190,6 +190,11 @@ int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, int32_t n);
  * SM of `device_id` and returns thread-level instructions per second in *instr_per_s and the kernel time in *ms. */
 int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* instr_per_s, double* ms);
 
+/* Native library only: benchmark hook.  Re-runs the device work of the last generate_poa() `iterations` times on
+ * the inputs already resident in device memory (no host<->device copies) and returns the CUDA-event time of all
+ * iterations in milliseconds, measured on the batch's own stream; negative if nothing has been staged. */
+double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations);
+
 #ifdef __cplusplus
 }
 #endif
