@@ -409,24 +409,34 @@ StatusType B200Batch::add_poa_group(std::vector<StatusType>& per_seq_status, con
     return StatusType::success;
 }
 
-template <typename ScoreT, typename IdT>
-static void launch_typed(const KernelParams& P, bool banded, bool msa, cudaStream_t stream)
+template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
+static void launch_one(const KernelParams& P, cudaStream_t stream)
 {
     const dim3 block(kWarpsPerBlock * 32);
     const dim3 grid((P.n_windows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    const size_t smem = static_cast<size_t>(kWarpsPerBlock) * static_cast<size_t>(P.smem_per_warp);
+    auto kernel       = poa_window_kernel<ScoreT, IdT, BANDED, MSA>;
+    // per device and cheap; batches on several devices share this code
+    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    kernel<<<grid, block, smem, stream>>>(P);
+}
+
+template <typename ScoreT, typename IdT>
+static void launch_typed(const KernelParams& P, bool banded, bool msa, cudaStream_t stream)
+{
     if (banded)
     {
         if (msa)
-            poa_window_kernel<ScoreT, IdT, true, true><<<grid, block, 0, stream>>>(P);
+            launch_one<ScoreT, IdT, true, true>(P, stream);
         else
-            poa_window_kernel<ScoreT, IdT, true, false><<<grid, block, 0, stream>>>(P);
+            launch_one<ScoreT, IdT, true, false>(P, stream);
     }
     else
     {
         if (msa)
-            poa_window_kernel<ScoreT, IdT, false, true><<<grid, block, 0, stream>>>(P);
+            launch_one<ScoreT, IdT, false, true>(P, stream);
         else
-            poa_window_kernel<ScoreT, IdT, false, false><<<grid, block, 0, stream>>>(P);
+            launch_one<ScoreT, IdT, false, false>(P, stream);
     }
 }
 
@@ -457,6 +467,7 @@ void B200Batch::launch()
     P.gap                 = gap_;
     P.mismatch            = mismatch_;
     P.match               = match_;
+    P.smem_per_warp       = kSmemPerWarp;
 #ifdef SPOA_ACCURATE
     P.spoa_accurate = 1;
 #else

@@ -37,7 +37,7 @@ struct Graph
     IdT *sorted, *pos;
     IdT *in_edges, *out_edges, *aligned;
     uint16_t* in_w;
-    IdT *aln_graph, *aln_read;
+    IdT* aln_node; // per read position: graph node the base pairs with, or -1 (the alignment, see align_exact)
     int32_t* row_bs;
     int32_t* cscore;
     IdT* cpred;
@@ -69,8 +69,7 @@ __device__ __forceinline__ Graph<IdT> make_graph(uint8_t* a, const ArenaLayout& 
     g.out_edges = reinterpret_cast<IdT*>(a + L.out_edges);
     g.aligned   = reinterpret_cast<IdT*>(a + L.aligned);
     g.in_w      = reinterpret_cast<uint16_t*>(a + L.in_w);
-    g.aln_graph = reinterpret_cast<IdT*>(a + L.aln_graph);
-    g.aln_read  = reinterpret_cast<IdT*>(a + L.aln_read);
+    g.aln_node  = reinterpret_cast<IdT*>(a + L.aln_node);
     g.row_bs    = reinterpret_cast<int32_t*>(a + L.row_bs);
     g.cscore    = reinterpret_cast<int32_t*>(a + L.cscore);
     g.cpred     = reinterpret_cast<IdT*>(a + L.cpred);
@@ -214,7 +213,11 @@ struct ScoreMatrix
 };
 
 // Needleman-Wunsch of one read against the graph, exact arithmetic.  All 32 lanes of the warp call this.
-// Returns the alignment length (alignment written end -> start into g.aln_graph / g.aln_read), or -1.
+// Returns the alignment length, or -1.  The alignment itself is left in g.aln_node[0 .. read_len): the node each
+// read base pairs with, or -1 for an inserted base.  (The reference's traceback emits (node, read position) pairs
+// end -> start, cudapoa_nw_banded.cuh:386-474; the pairs without a read position are never looked at by
+// addAlignmentToGraph, cudapoa_add_alignment.cuh:84-90, and the others carry read positions len-1 .. 0 in order, so
+// this array holds the same information.)
 template <typename ScoreT, typename IdT, bool BANDED>
 __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                                ScoreT* scores, int32_t width, int32_t band, int32_t gap, int32_t mismatch,
@@ -402,8 +405,8 @@ __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const ui
                 prev_j = j - 1;
                 found  = true;
             }
-            g.aln_graph[aligned] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
-            g.aln_read[aligned]  = static_cast<IdT>((j == prev_j) ? -1 : j - 1);
+            if (j != prev_j) // a read base was consumed: remember the node it pairs with (-1: inserted base)
+                g.aln_node[j - 1] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
             aligned++;
             i = prev_i;
             j = prev_j;
@@ -451,116 +454,143 @@ __device__ void init_backbone(const Graph<IdT>& g, const uint8_t* seq, const int
     }
 }
 
-// Fuse one alignment into the graph (cudapoa_add_alignment.cuh:59-279).  Lane 0 only.
+// Fuse one alignment into the graph (cudapoa_add_alignment.cuh:59-279), 32 read positions per step.
+//
+// The reference walks the alignment serially.  Its per-position work only touches (a) the node the base pairs
+// with and that node's aligned set, (b) the in-edge list of the position's node and (c) the out-edge list of the
+// previous position's node.  An alignment path visits a node at most once and never visits two nodes of one
+// aligned set (aligned nodes are mutually unreachable: every edge the fusion adds either shortcuts an existing
+// path or attaches a new node beside the one it is aligned to), so distinct positions touch disjoint state and
+// the lanes can proceed independently.  Order-dependent pieces are reproduced explicitly: new node ids are handed
+// out in position order (ballot + popc), and the first failing position decides the status.
 // path (MSA only): node visited by each base of this read, replacing the reference's per-edge read lists.
 template <typename IdT, bool MSA>
-__device__ int32_t add_alignment(const Graph<IdT>& g, int32_t& node_count, int32_t aln_len, const uint8_t* read,
-                                 const int8_t* w, IdT* path, int32_t max_nodes)
+__device__ int32_t add_alignment(const Graph<IdT>& g, int32_t& node_count, const uint8_t* read, int32_t read_len,
+                                 const int8_t* w, IdT* path, int32_t max_nodes, int32_t lane)
 {
-    int32_t head         = -1;
-    int32_t curr         = -1;
-    uint16_t prev_weight = 0;
-    int32_t n            = node_count;
-    for (int32_t pos = aln_len - 1; pos >= 0; pos--)
+    int32_t n          = node_count;
+    int32_t carry_curr = -1; // node of read position k0 - 1
+    const unsigned lt  = (1u << lane) - 1u;
+    for (int32_t k0 = 0; k0 < read_len; k0 += 32)
     {
-        const int32_t read_pos = g.aln_read[pos];
-        if (read_pos == -1)
-            continue;
-        const int32_t bw   = w ? w[read_pos] : 1;
-        const uint8_t base = read[read_pos];
-        const int32_t gn   = g.aln_graph[pos];
-        bool make_new      = false;
-        if (gn == -1)
+        const int32_t k = k0 + lane;
+        bool active     = k < read_len;
+        int32_t curr    = -1;
+        int32_t gn      = -1;
+        int32_t bw      = 1;
+        uint8_t base    = 0;
+        bool make_new   = false;
+        if (active)
         {
-            make_new = true;
-        }
-        else if (g.nodes[gn] == base)
-        {
-            curr = gn;
-        }
-        else
-        {
-            const int32_t na = g.aln_cnt[gn];
-            int32_t hit      = -1;
-            for (int32_t a = 0; a < na; a++)
+            base = read[k];
+            bw   = w ? w[k] : 1;
+            gn   = g.aln_node[k];
+            if (gn == -1)
             {
-                const int32_t aid = g.aln(gn, a);
-                if (g.nodes[aid] == base)
-                {
-                    hit = aid;
-                    break;
-                }
-            }
-            if (hit != -1)
-                curr = hit;
-            else
                 make_new = true;
+            }
+            else if (g.nodes[gn] == base)
+            {
+                curr = gn;
+            }
+            else
+            {
+                const int32_t na = g.aln_cnt[gn];
+                for (int32_t a = 0; a < na; a++)
+                {
+                    const int32_t aid = g.aln(gn, a);
+                    if (g.nodes[aid] == base)
+                    {
+                        curr = aid;
+                        break;
+                    }
+                }
+                make_new = (curr == -1);
+            }
         }
+        const unsigned new_mask = __ballot_sync(kFull, make_new);
         if (make_new)
+            curr = n + __popc(new_mask & lt);
+        // `curr = n++; if (n >= max_nodes) return error` (:113-117, :169-173): the first creation that fills the graph
+        const unsigned node_err = __ballot_sync(kFull, make_new && (curr + 1 >= max_nodes));
+        const int32_t node_err_lane = node_err ? (__ffs(node_err) - 1) : 32;
+        if (lane >= node_err_lane)
+            active = false;
+        n += __popc(new_mask);
+        if (active && make_new)
         {
-            curr = n++;
-            if (n >= max_nodes)
-                return kStNodeCountExceeded;
             g.nodes[curr]   = base;
             g.out_cnt[curr] = 0;
             g.in_cnt[curr]  = 0;
-            g.aln_cnt[curr] = 0;
             g.cov[curr]     = 0;
+            int32_t k2      = 0;
             if (gn != -1)
             {
                 // cross-link the new node with gn and everything already aligned to gn (:150-170)
                 const int32_t na = g.aln_cnt[gn];
-                int32_t k        = 0;
                 for (int32_t a = 0; a < na; a++)
                 {
                     const int32_t aid = g.aln(gn, a);
                     const int32_t c   = g.aln_cnt[aid];
                     g.aln(aid, c)     = static_cast<IdT>(curr);
                     g.aln_cnt[aid]    = static_cast<uint16_t>(c + 1);
-                    g.aln(curr, k++)  = static_cast<IdT>(aid);
+                    g.aln(curr, k2++) = static_cast<IdT>(aid);
                 }
-                g.aln(gn, na)   = static_cast<IdT>(curr);
-                g.aln_cnt[gn]   = static_cast<uint16_t>(na + 1);
-                g.aln(curr, k++) = static_cast<IdT>(gn);
-                g.aln_cnt[curr] = static_cast<uint16_t>(k);
+                g.aln(gn, na)     = static_cast<IdT>(curr);
+                g.aln_cnt[gn]     = static_cast<uint16_t>(na + 1);
+                g.aln(curr, k2++) = static_cast<IdT>(gn);
             }
+            g.aln_cnt[curr] = static_cast<uint16_t>(k2);
         }
-        if (MSA)
-            path[read_pos] = static_cast<IdT>(curr);
+        if (MSA && active)
+            path[k] = static_cast<IdT>(curr);
 
-        if (head != -1)
+        int32_t head = __shfl_up_sync(kFull, curr, 1);
+        if (lane == 0)
+            head = carry_curr;
+        bool edge_err = false;
+        if (active)
         {
-            bool exists       = false;
-            const int32_t inc = g.in_cnt[curr];
-            for (int32_t e = 0; e < inc; e++)
+            if (head != -1)
             {
-                if (g.in_edge(curr, e) == head)
+                const int32_t prev_weight = w ? w[k - 1] : 1;
+                const uint16_t add        = static_cast<uint16_t>(prev_weight + bw);
+                bool exists               = false;
+                const int32_t inc         = g.in_cnt[curr];
+                for (int32_t e = 0; e < inc; e++)
                 {
-                    exists            = true;
-                    g.weight(curr, e) = static_cast<uint16_t>(g.weight(curr, e) + (prev_weight + bw));
+                    if (g.in_edge(curr, e) == head)
+                    {
+                        exists            = true;
+                        g.weight(curr, e) = static_cast<uint16_t>(g.weight(curr, e) + add);
+                    }
+                }
+                if (!exists)
+                {
+                    g.in_edge(curr, inc)   = static_cast<IdT>(head);
+                    g.weight(curr, inc)    = add;
+                    g.in_cnt[curr]         = static_cast<uint16_t>(inc + 1);
+                    const int32_t outc     = g.out_cnt[head];
+                    g.out_edge(head, outc) = static_cast<IdT>(curr);
+                    g.out_cnt[head]        = static_cast<uint16_t>(outc + 1);
+                    edge_err               = (outc + 1 >= kMaxNodeEdges || inc + 1 >= kMaxNodeEdges); // :245-249
                 }
             }
-            if (!exists)
-            {
-                g.in_edge(curr, inc)    = static_cast<IdT>(head);
-                g.weight(curr, inc)     = static_cast<uint16_t>(prev_weight + bw);
-                g.in_cnt[curr]          = static_cast<uint16_t>(inc + 1);
-                const int32_t outc      = g.out_cnt[head];
-                g.out_edge(head, outc)  = static_cast<IdT>(curr);
-                g.out_cnt[head]         = static_cast<uint16_t>(outc + 1);
-                if (outc + 1 >= kMaxNodeEdges || inc + 1 >= kMaxNodeEdges)
-                    return kStEdgeCountExceeded;
-            }
+            g.cov[curr]++;
         }
-        head = curr;
-        g.cov[head]++;
-        prev_weight = static_cast<uint16_t>(bw);
+        const unsigned edge_mask = __ballot_sync(kFull, edge_err);
+        if (edge_mask != 0) // an edge failure sits at an earlier position than any node failure of this step
+            return kStEdgeCountExceeded;
+        if (node_err != 0)
+            return kStNodeCountExceeded;
+        carry_curr = __shfl_sync(kFull, curr, 31);
+        __syncwarp();
     }
     node_count = n;
     return kStSuccess;
 }
 
-// Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88).  Lane 0 only.
+// Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88).  Lane 0 only, global memory.
 template <typename IdT>
 __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 {
@@ -591,6 +621,80 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
             }
         }
     }
+}
+
+// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first three
+// out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
+// node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
+// uses topsort_kahn.  All 32 lanes call this.
+constexpr int32_t kKahnBytesPerNode = 11; // 8 (out-degree + 3 edges) + 2 (queue) + 1 (remaining in-degree)
+
+template <typename IdT>
+__device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* smem, int32_t smem_bytes,
+                                  int32_t lane)
+{
+    if (sizeof(IdT) != 2)
+        return false;
+    const int32_t cap = (smem_bytes / kKahnBytesPerNode) & ~7;
+    if (node_count > cap)
+        return false;
+    uint64_t* info  = reinterpret_cast<uint64_t*>(smem);
+    uint16_t* queue = reinterpret_cast<uint16_t*>(smem + 8 * cap);
+    uint8_t* deg    = smem + 10 * cap;
+    const unsigned lt = (1u << lane) - 1u;
+    int32_t tail      = 0;
+    for (int32_t n0 = 0; n0 < node_count; n0 += 32)
+    {
+        const int32_t n = n0 + lane;
+        bool source     = false;
+        if (n < node_count)
+        {
+            const uint32_t ic = g.in_cnt[n];
+            const uint32_t oc = g.out_cnt[n];
+            uint64_t v        = oc;
+            if (oc > 0)
+                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 0))) << 16;
+            if (oc > 1)
+                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 1))) << 32;
+            if (oc > 2)
+                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 2))) << 48;
+            info[n] = v;
+            deg[n]  = static_cast<uint8_t>(ic);
+            source  = (ic == 0);
+        }
+        const unsigned mask = __ballot_sync(kFull, source);
+        if (source)
+            queue[tail + __popc(mask & lt)] = static_cast<uint16_t>(n);
+        tail += __popc(mask);
+    }
+    __syncwarp();
+    if (lane == 0)
+    {
+        for (int32_t head = 0; head < tail; head++)
+        {
+            const int32_t node = queue[head];
+            const uint64_t v   = info[node];
+            const int32_t oc   = static_cast<int32_t>(v & 0xffffu);
+            for (int32_t e = 0; e < oc; e++)
+            {
+                const int32_t child = (e < 3) ? static_cast<int32_t>((v >> (16 * (e + 1))) & 0xffffu)
+                                              : static_cast<int32_t>(g.out_edge(node, e));
+                const uint8_t c = deg[child] - 1;
+                deg[child]      = c;
+                if (c == 0)
+                    queue[tail++] = static_cast<uint16_t>(child);
+            }
+        }
+    }
+    __syncwarp();
+    for (int32_t i = lane; i < node_count; i += 32)
+    {
+        const int32_t n = queue[i];
+        g.sorted[i]     = static_cast<IdT>(n);
+        g.pos[n]        = static_cast<IdT>(i);
+    }
+    __syncwarp();
+    return true;
 }
 
 // SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.

@@ -354,8 +354,8 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 prev_j = j - 1;
                 found  = true;
             }
-            g.aln_graph[aligned] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
-            g.aln_read[aligned]  = static_cast<IdT>((j == prev_j) ? -1 : j - 1);
+            if (j != prev_j) // a read base was consumed: remember the node it pairs with (-1: inserted base)
+                g.aln_node[j - 1] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
             aligned++;
             i = prev_i;
             j = prev_j;

@@ -36,7 +36,7 @@ struct ArenaLayout
     int64_t sorted, pos;                         // IdT[M]
     int64_t in_edges, out_edges, aligned;        // IdT[50][M]
     int64_t in_w;                                // uint16[50][M]
-    int64_t aln_graph, aln_read;                 // IdT[aln_cap]
+    int64_t aln_node;                            // IdT[max_seq + 32]  the alignment: node per read position
     int64_t row_bs;                              // int32[M + 1]   band start per score row
     int64_t cscore;                              // int32[M]       consensus scores / racon marks scratch
     int64_t cpred;                               // IdT[M]         consensus predecessors / racon stack
@@ -78,6 +78,7 @@ struct KernelParams
     int32_t band;
     int32_t gap, mismatch, match;
     int32_t spoa_accurate;
+    int32_t smem_per_warp; // bytes of shared-memory scratch each warp (= window) owns
 };
 
 inline int64_t align_up64(int64_t v, int64_t a)
@@ -113,8 +114,7 @@ inline ArenaLayout make_arena_layout(int32_t M, int32_t aln_cap, int32_t max_rea
     L.out_edges     = take(id_bytes * m * kMaxNodeEdges);
     L.aligned       = take(id_bytes * m * kMaxNodeAlignments);
     L.in_w          = take(2 * m * kMaxNodeEdges);
-    L.aln_graph     = take(static_cast<int64_t>(id_bytes) * aln_cap);
-    L.aln_read      = take(static_cast<int64_t>(id_bytes) * aln_cap);
+    L.aln_node      = take(static_cast<int64_t>(id_bytes) * (max_seq + 32));
     L.row_bs        = take(4 * (m + 1));
     L.cscore        = take(4 * m);
     L.cpred         = take(id_bytes * (m + 8));

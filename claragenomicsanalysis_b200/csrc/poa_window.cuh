@@ -11,14 +11,17 @@ namespace poa_b200
 {
 
 constexpr int32_t kWarpsPerBlock = 4;
+constexpr int32_t kSmemPerWarp   = 24 * 1024; // 2 blocks x 4 warps x 24 KB per SM
 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const KernelParams P)
 {
+    extern __shared__ __align__(16) uint8_t smem_block[];
     const int32_t lane = threadIdx.x & 31;
     const int32_t w    = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     if (w >= P.n_windows)
         return;
+    uint8_t* smem = smem_block + static_cast<size_t>(threadIdx.x >> 5) * P.smem_per_warp; // this warp's scratch
 
     const WindowDesc wd = P.windows[w];
     const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
@@ -77,27 +80,25 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const K
                 status = kStLoopCountExceeded;
                 break;
             }
-            int32_t rc = kStSuccess;
-            if (lane == 0)
+            __syncwarp(); // lane 0's traceback output becomes visible to the warp
+            int32_t rc = add_alignment<IdT, MSA>(g, node_count, seq, len, wts,
+                                                 MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
+                                                 P.max_nodes, lane);
+            __syncwarp();
+            if (rc == kStSuccess)
             {
-                rc = add_alignment<IdT, MSA>(g, node_count, aln_len, seq, wts,
-                                             MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
-                                             P.max_nodes);
-                if (rc == kStSuccess)
+                if (P.spoa_accurate)
                 {
-                    if (P.spoa_accurate)
-                    {
-                        if (!topsort_spoa_order<IdT>(g, node_count))
-                            rc = kStGenericError;
-                    }
-                    else
-                    {
+                    if (lane == 0 && !topsort_spoa_order<IdT>(g, node_count))
+                        rc = kStGenericError;
+                    rc = __shfl_sync(kFull, rc, 0);
+                }
+                else if (!topsort_kahn_smem<IdT>(g, node_count, smem, P.smem_per_warp, lane))
+                {
+                    if (lane == 0)
                         topsort_kahn<IdT>(g, node_count);
-                    }
                 }
             }
-            rc         = __shfl_sync(kFull, rc, 0);
-            node_count = __shfl_sync(kFull, node_count, 0);
             __syncwarp();
             if (rc != kStSuccess) // cudapoa_kernels.cuh:314-319
             {
