@@ -39,6 +39,7 @@ struct Graph
     uint16_t* in_w;
     IdT* aln_node; // per read position: graph node the base pairs with, or -1 (the alignment, see align_exact)
     int32_t* row_bs;
+    uint32_t* rowinfo;
     int32_t* cscore;
     IdT* cpred;
     uint8_t *marks, *check;
@@ -71,6 +72,7 @@ __device__ __forceinline__ Graph<IdT> make_graph(uint8_t* a, const ArenaLayout& 
     g.in_w      = reinterpret_cast<uint16_t*>(a + L.in_w);
     g.aln_node  = reinterpret_cast<IdT*>(a + L.aln_node);
     g.row_bs    = reinterpret_cast<int32_t*>(a + L.row_bs);
+    g.rowinfo   = reinterpret_cast<uint32_t*>(a + L.rowinfo);
     g.cscore    = reinterpret_cast<int32_t*>(a + L.cscore);
     g.cpred     = reinterpret_cast<IdT*>(a + L.cpred);
     g.marks     = a + L.marks;

@@ -18,6 +18,13 @@
 //     byte-permutes when the shift is an odd multiple of 4.
 //   * cell update: two DPX instructions per register and predecessor,
 //       S = __viaddmax_s16x2(D, Q, __viaddmax_s16x2(V, gap, S))   (VIADDMNMX.S16x2 on sm_100a).
+//   * memory: every row goes to the window's score matrix in global memory (the traceback needs all of them), and
+//     the most recent kRingRows rows also stay in a shared-memory ring, which is where predecessor rows are read
+//     from (graph predecessors are almost always a few ranks back).  Per-row descriptors (base, in-degree,
+//     predecessor rows, band start, left boundary) are built by a warp-parallel pre-pass into shared memory, so the
+//     serial row loop and the traceback never chase graph pointers through global memory.
+//   * traceback: score re-derivation as in the reference, on lane 0, out of shared-memory tiles of the score
+//     matrix that the whole warp loads around the current cell.
 #pragma once
 
 #include "poa_device.cuh"
@@ -30,6 +37,11 @@ constexpr int32_t kFastBand     = 256;
 constexpr int32_t kFastRowWords = 132;    // 128 cell words + 4 pad words
 constexpr int32_t kNegT         = -30000; // tilted-domain stand-in for the reference's sentinel class
 constexpr int32_t kNegThreshold = -25000; // anything at or below is sentinel class
+constexpr int32_t kRingRows     = 16;     // power of two
+constexpr int32_t kRingBytes    = kRingRows * kFastRowWords * 4;
+constexpr int32_t kTileRows     = 64;     // traceback tile: rows x 16-byte blocks (8 cells each)
+constexpr int32_t kTileBlocks   = 6;
+static_assert(kTileRows * kTileBlocks * 16 + kTileRows * 4 <= kRingBytes, "the tile reuses the ring's memory");
 
 __device__ __forceinline__ uint32_t pack2(int32_t lo, int32_t hi)
 {
@@ -57,32 +69,61 @@ __device__ __forceinline__ bool fast_path_eligible(int32_t node_count, int32_t r
         return false;
     if ((match - gap) * (read_len + 2) > 30000)
         return false;
+    if (node_count + 1 >= 65536)
+        return false;
     return true;
 }
 
+// Per-row descriptor, three 32-bit words kept as three arrays (shared memory when the graph fits, else global):
+//   w0 = base | in-degree << 8 | sink << 14 | row of predecessor 0 << 16
+//   w1 = band start | left-boundary value (tilted, int16) << 16
+//   w2 = row of predecessor 1 | row of predecessor 2 << 16
+struct RowInfo
+{
+    uint32_t* w0;
+    uint32_t* w1;
+    uint32_t* w2;
+};
+
 // Reads of the tilted score matrix with the reference's get_score semantics (cudapoa_nw_banded.cuh:106-120),
-// returning un-tilted H values; sentinel-class cells come back as the reference's sentinel.
+// returning un-tilted H values; sentinel-class cells come back as the reference's sentinel.  Cells are taken from
+// the shared-memory tile when it holds them, else from the global score matrix.
 struct FastMatrix
 {
-    const uint32_t* rows;  // row r at rows + r * kFastRowWords (row 0 is implicit: H = j * gap)
-    const int32_t* row_bs;
-    const uint16_t* left;  // tilted left-boundary value per row (as int16)
+    const uint32_t* rows;   // row r at rows + r * kFastRowWords (row 0 is implicit: H = j * gap)
+    RowInfo ri;
+    const uint4* tile;      // [kTileRows][kTileBlocks]
+    const int32_t* tile_b0; // first block held for each tile row
+    int32_t tile_r0;        // first row of the tile (tile rows are tile_r0 .. tile_r0 + kTileRows - 1)
     int32_t gap;
     int32_t sentinel;
 
     __device__ __forceinline__ int32_t cell_t(int32_t r, int32_t c) const // c: 0-based cell of the band
     {
-        const uint32_t w = rows[static_cast<int64_t>(r) * kFastRowWords + ((c >> 3) << 2) + (c & 3)];
+        const int32_t blk = c >> 3;
+        const int32_t tr  = r - tile_r0;
+        uint32_t w;
+        if (tr >= 0 && tr < kTileRows)
+        {
+            const int32_t tb = blk - tile_b0[tr];
+            if (tb >= 0 && tb < kTileBlocks)
+            {
+                w = reinterpret_cast<const uint32_t*>(tile + tr * kTileBlocks + tb)[c & 3];
+                return (c & 4) ? hi16(w) : lo16(w);
+            }
+        }
+        w = __ldcg(rows + static_cast<int64_t>(r) * kFastRowWords + (blk << 2) + (c & 3));
         return (c & 4) ? hi16(w) : lo16(w);
     }
     __device__ __forceinline__ int32_t get(int32_t r, int32_t column) const
     {
         if (r == 0)
             return (column >= 0 && column <= kFastBand) ? column * gap : sentinel;
-        const int32_t b = row_bs[r];
+        const uint32_t w1 = ri.w1[r];
+        const int32_t b   = static_cast<int32_t>(w1 & 0xffffu);
         int32_t t;
         if (column == 0 || column == b)
-            t = static_cast<int16_t>(left[r]);
+            t = hi16(w1);
         else if (column > b + kFastBand || column < b)
             return sentinel;
         else
@@ -91,41 +132,89 @@ struct FastMatrix
     }
 };
 
-// Row descriptor packed by the pre-pass: base | in-degree << 8 | sink << 14 | first-predecessor row << 16.
-__device__ __forceinline__ uint32_t make_row_meta(uint32_t base, uint32_t pc, bool sink, uint32_t pred0_row)
+// Load the tile of the score matrix that ends at (row tile_r0 + kTileRows - 1, column j): for every row the
+// kTileBlocks blocks ending with the block that holds column j.  All lanes.
+__device__ __forceinline__ void load_tile(const uint32_t* rows, const RowInfo& ri, uint4* tile, int32_t* tile_b0,
+                                          int32_t tile_r0, int32_t j, int32_t lane)
 {
-    return base | (pc << 8) | (sink ? (1u << 14) : 0u) | (pred0_row << 16);
+    for (int32_t tr = lane; tr < kTileRows; tr += 32)
+    {
+        const int32_t r = tile_r0 + tr;
+        int32_t b0      = 0;
+        if (r >= 1)
+        {
+            const int32_t b  = static_cast<int32_t>(ri.w1[r] & 0xffffu);
+            const int32_t hi = min(max((j - b - 1) >> 3, 0), 32); // block of column j, clamped to the row
+            b0               = max(hi - (kTileBlocks - 1), 0);
+        }
+        tile_b0[tr] = b0;
+    }
+    __syncwarp();
+    for (int32_t idx = lane; idx < kTileRows * kTileBlocks; idx += 32)
+    {
+        const int32_t tr  = idx / kTileBlocks;
+        const int32_t tb  = idx - tr * kTileBlocks;
+        const int32_t r   = tile_r0 + tr;
+        const int32_t blk = tile_b0[tr] + tb;
+        if (r >= 1 && blk <= 32)
+            tile[idx] = __ldcg(reinterpret_cast<const uint4*>(rows + static_cast<int64_t>(r) * kFastRowWords) + blk);
+    }
+    __syncwarp();
 }
 
 template <typename IdT>
 __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
                                        int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
-                                       int32_t mismatch, int32_t match, int32_t lane)
+                                       int32_t mismatch, int32_t match, uint8_t* smem, int32_t smem_bytes,
+                                       int32_t lane)
 {
-    if (!fast_path_eligible(node_count, read_len, band, gap, mismatch, match))
+    if (!fast_path_eligible(node_count, read_len, band, gap, mismatch, match) || smem_bytes < kRingBytes)
         return kFastNotTaken;
 
-    uint32_t* rows       = reinterpret_cast<uint32_t*>(scores);
-    uint32_t* row_meta   = reinterpret_cast<uint32_t*>(g.cscore); // free until the consensus stage
-    uint16_t* left       = g.kahn;                                // free until the next topological sort
+    uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
+    // shared-memory scratch: [ring of recent rows | row descriptors]; descriptors spill to global when they do not fit
+    uint32_t* ring = reinterpret_cast<uint32_t*>(smem);
+    RowInfo ri;
+    {
+        const int32_t cap = ((smem_bytes - kRingBytes) / 12) & ~3;
+        if (node_count + 1 <= cap)
+        {
+            ri.w0 = reinterpret_cast<uint32_t*>(smem + kRingBytes);
+            ri.w1 = ri.w0 + cap;
+            ri.w2 = ri.w1 + cap;
+        }
+        else
+        {
+            ri.w0 = g.rowinfo;
+            ri.w1 = ri.w0 + (g.M + 8);
+            ri.w2 = ri.w1 + (g.M + 8);
+        }
+    }
     const int32_t max_column = read_len + 1;
     const float gradient     = band_gradient(read_len, node_count);
     const int32_t sentinel   = band_sentinel<int16_t>(gap, mismatch, match);
 
-    // pre-pass, one row per lane: band start and row descriptor (32 independent gather chains in flight)
+    // pre-pass, one row per lane: band start and row descriptor (independent gather chains in flight)
+#pragma unroll 2
     for (int32_t r = lane; r <= node_count; r += 32)
     {
-        g.row_bs[r] = band_start(r, gradient, kFastBand, max_column);
+        const uint32_t bs = static_cast<uint32_t>(band_start(r, gradient, kFastBand, max_column));
+        uint32_t w0 = 0, w2 = 0;
         if (r > 0)
         {
             const int32_t node = g.sorted[r - 1];
             const uint32_t pc  = g.in_cnt[node];
             const uint32_t p0  = (pc == 0) ? 0u : static_cast<uint32_t>(g.pos[g.in_edge(node, 0)] + 1);
-            row_meta[r]        = make_row_meta(g.nodes[node], pc, g.out_cnt[node] == 0, p0);
+            const uint32_t p1  = (pc > 1) ? static_cast<uint32_t>(g.pos[g.in_edge(node, 1)] + 1) : 0u;
+            const uint32_t p2  = (pc > 2) ? static_cast<uint32_t>(g.pos[g.in_edge(node, 2)] + 1) : 0u;
+            w0 = static_cast<uint32_t>(g.nodes[node]) | (pc << 8) | ((g.out_cnt[node] == 0) ? (1u << 14) : 0u) |
+                 (p0 << 16);
+            w2 = p1 | (p2 << 16);
         }
+        ri.w0[r] = w0;
+        ri.w1[r] = bs; // row 0: left boundary T = 0
+        ri.w2[r] = w2;
     }
-    if (lane == 0)
-        left[0] = 0;
     __syncwarp();
 
     const uint32_t NEG2  = pack2(kNegT, kNegT);
@@ -137,12 +226,21 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
 
     int32_t cached_bs = -1;
     uint32_t rb_lo = 0, rb_hi = 0;
+    uint32_t w0n = ri.w0[1], w1n = ri.w1[1], w2n = ri.w2[1];
     for (int32_t r = 1; r <= node_count; r++)
     {
-        const uint32_t meta = row_meta[r];
-        const int32_t bs    = g.row_bs[r];
-        const int32_t pc    = (meta >> 8) & 0x3f;
-        const uint32_t base = meta & 0xff;
+        const uint32_t meta   = w0n;
+        const int32_t bs      = static_cast<int32_t>(w1n & 0xffffu);
+        const uint32_t pred12 = w2n;
+        const int32_t pc      = (meta >> 8) & 0x3f;
+        const uint32_t base   = meta & 0xff;
+        {
+            // descriptor of the next row: issued now, consumed an iteration later
+            const int32_t rn = min(r + 1, node_count);
+            w0n = ri.w0[rn];
+            w1n = ri.w1[rn];
+            w2n = ri.w2[rn];
+        }
 
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)); the lane's 8 read bases (positions bs + 8*lane ..)
         // are re-read only when the band start moves
@@ -172,15 +270,24 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         }
 
         uint32_t S[4] = {NEG2, NEG2, NEG2, NEG2};
-        bool any_in_band = false;
+        bool any_in_band  = false;
         int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
-        const int32_t node = (pc > 1) ? static_cast<int32_t>(g.sorted[r - 1]) : 0;
         for (int32_t p = 0; p < max(pc, 1); p++)
         {
-            const int32_t prow = (p == 0) ? static_cast<int32_t>(meta >> 16) : g.pos[g.in_edge(node, p)] + 1;
-            const int32_t d    = bs - g.row_bs[prow];
+            int32_t prow;
+            if (p == 0)
+                prow = static_cast<int32_t>(meta >> 16);
+            else if (p == 1)
+                prow = static_cast<int32_t>(pred12 & 0xffffu);
+            else if (p == 2)
+                prow = static_cast<int32_t>(pred12 >> 16);
+            else
+                prow = g.pos[g.in_edge(g.sorted[r - 1], p)] + 1;
+            const uint32_t pw1  = ri.w1[prow];
+            const int32_t d     = bs - static_cast<int32_t>(pw1 & 0xffffu);
+            const int32_t pleft = hi16(pw1);
             if (bs == 0)
-                left_best = max(left_best, static_cast<int32_t>(static_cast<int16_t>(left[prow])));
+                left_best = max(left_best, pleft);
             if (d > kFastBand)
                 continue; // wholly outside this predecessor's band: raw sentinel, contributes nothing
             any_in_band = true;
@@ -199,45 +306,45 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 }
                 continue;
             }
-            const uint32_t* prev_row = rows + static_cast<int64_t>(prow) * kFastRowWords;
-            const int32_t sl         = lane + (d >> 3);
-            uint32_t V[4];
-            if (sl <= 32)
+            // the predecessor row: shared-memory ring when recent, else the global score matrix (through L2)
+            const int32_t sl = lane + (d >> 3);     // block of this lane's first vertical operand
+            const int32_t c  = 8 * lane + d - 1;    // cell before this lane's first one (the diagonal corner)
+            uint4 a          = make_uint4(NEG2, NEG2, NEG2, NEG2);
+            uint4 b          = a;
+            uint32_t wv      = NEG2;
+            if (r - prow < kRingRows)
             {
-                const uint4 a = *reinterpret_cast<const uint4*>(prev_row + 4 * sl);
-                V[0] = a.x; V[1] = a.y; V[2] = a.z; V[3] = a.w;
+                const uint32_t* prev_row = ring + (prow & (kRingRows - 1)) * kFastRowWords;
+                if (sl <= 32)
+                    a = *reinterpret_cast<const uint4*>(prev_row + 4 * sl);
+                if ((d & 4) && sl + 1 <= 32)
+                    b = *reinterpret_cast<const uint4*>(prev_row + 4 * (sl + 1));
+                if (c >= 0 && (c >> 3) <= 32)
+                    wv = prev_row[((c >> 3) << 2) + 3];
             }
             else
             {
-                V[0] = V[1] = V[2] = V[3] = NEG2;
+                const uint32_t* prev_row = rows + static_cast<int64_t>(prow) * kFastRowWords;
+                if (sl <= 32)
+                    a = __ldcg(reinterpret_cast<const uint4*>(prev_row + 4 * sl));
+                if ((d & 4) && sl + 1 <= 32)
+                    b = __ldcg(reinterpret_cast<const uint4*>(prev_row + 4 * (sl + 1)));
+                if (c >= 0 && (c >> 3) <= 32)
+                    wv = __ldcg(prev_row + ((c >> 3) << 2) + 3);
             }
+            uint32_t V[4] = {a.x, a.y, a.z, a.w};
             if (d & 4)
             {
-                uint32_t W[4] = {NEG2, NEG2, NEG2, NEG2};
-                if (sl + 1 <= 32)
-                {
-                    const uint4 b = *reinterpret_cast<const uint4*>(prev_row + 4 * (sl + 1));
-                    W[0] = b.x; W[1] = b.y; W[2] = b.z; W[3] = b.w;
-                }
-#pragma unroll
-                for (int i = 0; i < 4; i++)
-                    V[i] = __byte_perm(V[i], W[i], 0x5432); // (hi of this block, lo of the next)
+                V[0] = __byte_perm(a.x, b.x, 0x5432); // (hi of this block, lo of the next)
+                V[1] = __byte_perm(a.y, b.y, 0x5432);
+                V[2] = __byte_perm(a.z, b.z, 0x5432);
+                V[3] = __byte_perm(a.w, b.w, 0x5432);
             }
+            // corner value wanted in the high half of `before`
+            uint32_t before = (d & 4) ? (wv << 16) : wv;
+            if (c < 0)
+                before = static_cast<uint32_t>(pleft) << 16;
             // diagonal operands: D_i = V_{i-1}; D_0 = (cell before this lane's first, V_3.lo)
-            uint32_t before = __shfl_up_sync(kFull, V[3], 1);
-            if (lane == 0)
-            {
-                int32_t t;
-                if (d == 0)
-                    t = static_cast<int16_t>(left[prow]);
-                else
-                {
-                    const int32_t c = d - 1;
-                    const uint32_t w = prev_row[((c >> 3) << 2) + (c & 3)];
-                    t = (c & 4) ? hi16(w) : lo16(w);
-                }
-                before = static_cast<uint32_t>(t) << 16;
-            }
             const uint32_t D0 = __byte_perm(before, V[3], 0x5432);
             S[0] = __viaddmax_s16x2(D0, Q[0], __viaddmax_s16x2(V[0], gapv, S[0]));
             S[1] = __viaddmax_s16x2(V[0], Q[1], __viaddmax_s16x2(V[1], gapv, S[1]));
@@ -271,20 +378,27 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         out.z = __vimax3_s16x2(S[2], cb, tl);
         out.w = __vimax3_s16x2(S[3], cb, tl);
         uint32_t* this_row = rows + static_cast<int64_t>(r) * kFastRowWords;
-        *reinterpret_cast<uint4*>(this_row + 4 * lane) = out;
+        uint32_t* ring_row = ring + (r & (kRingRows - 1)) * kFastRowWords;
+        __stcg(reinterpret_cast<uint4*>(this_row + 4 * lane), out);
+        *reinterpret_cast<uint4*>(ring_row + 4 * lane) = out;
         if (lane < 4)
-            this_row[128 + lane] = NEG2;
+        {
+            __stcg(this_row + 128 + lane, NEG2);
+            ring_row[128 + lane] = NEG2;
+        }
         if (lane == 0)
-            left[r] = static_cast<uint16_t>(left_t);
+            ri.w1[r] = static_cast<uint32_t>(bs) | (static_cast<uint32_t>(left_t) << 16);
         __syncwarp();
     }
 
     // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len
-    FastMatrix M{rows, g.row_bs, left, gap, sentinel};
+    uint4* tile      = reinterpret_cast<uint4*>(smem);
+    int32_t* tile_b0 = reinterpret_cast<int32_t*>(smem + kTileRows * kTileBlocks * 16);
+    FastMatrix M{rows, ri, tile, tile_b0, -(1 << 30), gap, sentinel}; // no tile yet
     int32_t best = INT16_MIN, best_row = 0;
     for (int32_t r = 1 + lane; r <= node_count; r += 32)
     {
-        if (row_meta[r] & (1u << 14))
+        if (ri.w0[r] & (1u << 14))
         {
             const int32_t s = M.get(r, read_len);
             if (s > best)
@@ -297,7 +411,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
 #pragma unroll
     for (int32_t k = 16; k > 0; k >>= 1)
     {
-        const int32_t ob = __shfl_xor_sync(kFull, best, k);
+        const int32_t ob   = __shfl_xor_sync(kFull, best, k);
         const int32_t orow = __shfl_xor_sync(kFull, best_row, k);
         // keep the larger score; on ties the smaller (non-zero) row
         if (ob > best || (ob == best && orow != 0 && (best_row == 0 || orow < best_row)))
@@ -307,63 +421,82 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         }
     }
 
-    int32_t aligned = 0;
-    if (lane == 0)
+    // traceback (cudapoa_nw_banded.cuh:386-480): lane 0 walks, the warp reloads the tile when the walk leaves it
+    int32_t i = (best > INT16_MIN) ? best_row : 0, j = read_len;
+    int32_t aligned = 0, loops = 0;
+    int32_t prev_i = 0, prev_j = 0; // lane 0's copies carry over between tiles, as in the reference's single loop
+    const int32_t limit = read_len + node_count + 2;
+    while (!(i == 0 && j == 0) && loops < limit) // uniform: i, j, loops are broadcast at the end of every round
     {
-        int32_t i = (best > INT16_MIN) ? best_row : 0, j = read_len;
-        int32_t prev_i = 0, prev_j = 0, loops = 0;
-        const int32_t limit = read_len + node_count + 2;
-        while (!(i == 0 && j == 0) && loops < limit)
+        const int32_t tile_r0 = i - (kTileRows - 1);
+        load_tile(rows, ri, tile, tile_b0, tile_r0, j, lane);
+        M.tile_r0 = tile_r0;
+        if (lane == 0)
         {
-            loops++;
-            const int32_t sij = M.get(i, j);
-            bool found        = false;
-            if (i != 0)
+            const int32_t row_floor = (tile_r0 <= 1) ? 0 : tile_r0 + 12; // leave before predecessors fall out
+            const int32_t col_floor = j - 8 * (kTileBlocks - 2);         // ... or column j - 1 does
+            while (!(i == 0 && j == 0) && loops < limit && i >= row_floor && j > col_floor)
             {
-                const uint32_t meta = row_meta[i];
-                const int32_t pc    = (meta >> 8) & 0x3f;
-                const int32_t node  = (pc > 1) ? static_cast<int32_t>(g.sorted[i - 1]) : 0;
-                if (j != 0)
+                loops++;
+                const int32_t sij = M.get(i, j);
+                bool found        = false;
+                if (i != 0)
                 {
-                    const int32_t cost = ((meta & 0xff) == read[j - 1]) ? match : mismatch;
+                    const uint32_t meta = ri.w0[i];
+                    const uint32_t p12  = ri.w2[i];
+                    const int32_t pc    = (meta >> 8) & 0x3f;
+                    if (j != 0)
+                    {
+                        const int32_t cost = ((meta & 0xff) == read[j - 1]) ? match : mismatch;
+                        for (int32_t p = 0; p < max(pc, 1) && !found; p++)
+                        {
+                            const int32_t pi = (p == 0)   ? static_cast<int32_t>(meta >> 16)
+                                               : (p == 1) ? static_cast<int32_t>(p12 & 0xffffu)
+                                               : (p == 2) ? static_cast<int32_t>(p12 >> 16)
+                                                          : g.pos[g.in_edge(g.sorted[i - 1], p)] + 1;
+                            if (sij == M.get(pi, j - 1) + cost)
+                            {
+                                prev_i = pi;
+                                prev_j = j - 1;
+                                found  = true;
+                            }
+                        }
+                    }
                     for (int32_t p = 0; p < max(pc, 1) && !found; p++)
                     {
-                        const int32_t pi = (p == 0) ? static_cast<int32_t>(meta >> 16) : g.pos[g.in_edge(node, p)] + 1;
-                        if (sij == M.get(pi, j - 1) + cost)
+                        const int32_t pi = (p == 0)   ? static_cast<int32_t>(meta >> 16)
+                                           : (p == 1) ? static_cast<int32_t>(p12 & 0xffffu)
+                                           : (p == 2) ? static_cast<int32_t>(p12 >> 16)
+                                                      : g.pos[g.in_edge(g.sorted[i - 1], p)] + 1;
+                        if (sij == M.get(pi, j) + gap)
                         {
                             prev_i = pi;
-                            prev_j = j - 1;
+                            prev_j = j;
                             found  = true;
                         }
                     }
                 }
-                for (int32_t p = 0; p < max(pc, 1) && !found; p++)
+                if (!found && j > 0 && sij == M.get(i, j - 1) + gap)
                 {
-                    const int32_t pi = (p == 0) ? static_cast<int32_t>(meta >> 16) : g.pos[g.in_edge(node, p)] + 1;
-                    if (sij == M.get(pi, j) + gap)
-                    {
-                        prev_i = pi;
-                        prev_j = j;
-                        found  = true;
-                    }
+                    prev_i = i;
+                    prev_j = j - 1;
+                    found  = true;
                 }
+                if (j != prev_j) // a read base was consumed: remember the node it pairs with (-1: inserted base)
+                    g.aln_node[j - 1] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
+                aligned++;
+                i = prev_i;
+                j = prev_j;
             }
-            if (!found && j > 0 && sij == M.get(i, j - 1) + gap)
-            {
-                prev_i = i;
-                prev_j = j - 1;
-                found  = true;
-            }
-            if (j != prev_j) // a read base was consumed: remember the node it pairs with (-1: inserted base)
-                g.aln_node[j - 1] = static_cast<IdT>((i == prev_i) ? -1 : g.sorted[i - 1]);
-            aligned++;
-            i = prev_i;
-            j = prev_j;
         }
-        if (loops >= limit)
-            aligned = -1;
+        i       = __shfl_sync(kFull, i, 0);
+        j       = __shfl_sync(kFull, j, 0);
+        loops   = __shfl_sync(kFull, loops, 0);
+        aligned = __shfl_sync(kFull, aligned, 0);
     }
-    return __shfl_sync(kFull, aligned, 0);
+    if (loops >= limit)
+        aligned = -1;
+    return aligned;
 }
 
 } // namespace poa_b200

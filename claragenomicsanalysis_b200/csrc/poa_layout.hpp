@@ -38,6 +38,7 @@ struct ArenaLayout
     int64_t in_w;                                // uint16[50][M]
     int64_t aln_node;                            // IdT[max_seq + 32]  the alignment: node per read position
     int64_t row_bs;                              // int32[M + 1]   band start per score row
+    int64_t rowinfo;                             // uint32[3][M + 8] per-row descriptors of the fast fill when they do not fit shared memory
     int64_t cscore;                              // int32[M]       consensus scores / racon marks scratch
     int64_t cpred;                               // IdT[M]         consensus predecessors / racon stack
     int64_t marks, check;                        // uint8[M]
@@ -116,6 +117,7 @@ inline ArenaLayout make_arena_layout(int32_t M, int32_t aln_cap, int32_t max_rea
     L.in_w          = take(2 * m * kMaxNodeEdges);
     L.aln_node      = take(static_cast<int64_t>(id_bytes) * (max_seq + 32));
     L.row_bs        = take(4 * (m + 1));
+    L.rowinfo       = take(12 * (m + 8));
     L.cscore        = take(4 * m);
     L.cpred         = take(id_bytes * (m + 8));
     L.marks         = take(m);

@@ -11,7 +11,7 @@ namespace poa_b200
 {
 
 constexpr int32_t kWarpsPerBlock = 4;
-constexpr int32_t kSmemPerWarp   = 24 * 1024; // 2 blocks x 4 warps x 24 KB per SM
+constexpr int32_t kSmemPerWarp   = 28 * 1024; // 2 blocks x 4 warps x 28 KB per SM
 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const KernelParams P)
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const K
             int32_t aln_len = kFastNotTaken;
             if (BANDED && sizeof(ScoreT) == 2)
                 aln_len = align_fast_banded16<IdT>(g, node_count, seq, len, reinterpret_cast<int16_t*>(scores),
-                                                   P.band, P.gap, P.mismatch, P.match, lane);
+                                                   P.band, P.gap, P.mismatch, P.match, smem, P.smem_per_warp, lane);
             if (aln_len == kFastNotTaken)
             {
                 aln_len = align_exact<ScoreT, IdT, BANDED>(g, node_count, seq, len, scores, width, P.band, P.gap,
