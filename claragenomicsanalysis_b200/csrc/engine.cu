@@ -77,7 +77,7 @@ MemoryPlan make_plan(const BatchSize& b, bool banded, bool msa, int32_t gap, int
                        (msa ? static_cast<int64_t>(S) * b.max_consensus_size
                             : static_cast<int64_t>(b.max_consensus_size) * 3);
     p.fixed_per_poa = p.layout.stride + align_up64(p.input_per_poa, 16) + align_up64(p.output_per_poa, 16) + 64;
-    const int64_t width = banded ? b.alignment_band_width + kBandPad : b.max_matrix_sequence_dimension + 8;
+    const int64_t width = banded ? b.alignment_band_width + kBandRowPad : b.max_matrix_sequence_dimension + 8;
     p.score_per_poa     = width * static_cast<int64_t>(p.G) * (p.score32 ? 4 : 2);
     return p;
 }
@@ -314,7 +314,7 @@ void B200Batch::allocate(size_t max_mem)
 // reserve_buf, cudapoa_batch.cuh:542-564
 bool B200Batch::reserve_scores(int32_t max_seq_length)
 {
-    const int64_t width = banded_ ? batch_size_.alignment_band_width + kBandPad
+    const int64_t width = banded_ ? batch_size_.alignment_band_width + kBandRowPad
                                   : cudautils::align<int32_t, 4>(max_seq_length + 1 + 4);
     const size_t bytes  = static_cast<size_t>(width) * static_cast<size_t>(plan_.G) * (plan_.score32 ? 4 : 2);
     if (bytes > avail_score_mem_)
@@ -451,7 +451,7 @@ void B200Batch::launch()
     P.arena               = arena_d_;
     P.layout              = plan_.layout;
     P.scores              = scores_d_;
-    P.banded_score_stride = static_cast<int64_t>(batch_size_.alignment_band_width + kBandPad) * plan_.G;
+    P.banded_score_stride = static_cast<int64_t>(batch_size_.alignment_band_width + kBandRowPad) * plan_.G;
     P.status              = status_d_;
     P.node_count          = node_count_d_;
     P.consensus           = consensus_d_;

@@ -14,7 +14,8 @@ namespace poa_b200
 
 constexpr int32_t kMaxNodeEdges      = 50; // same limits as the reference: they are observable through
 constexpr int32_t kMaxNodeAlignments = 50; // edge_count_exceeded_maximum_graph_size
-constexpr int32_t kBandPad           = 8;  // cells right of the band kept at the sentinel
+constexpr int32_t kBandPad           = 8;  // cells right of the band kept at the sentinel (reference layout)
+constexpr int32_t kBandRowPad        = 16; // cells of padding in this engine's banded row stride (two 16-byte blocks)
 constexpr int32_t kWarp              = 32;
 
 struct WindowDesc

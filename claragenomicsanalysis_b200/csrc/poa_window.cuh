@@ -14,7 +14,7 @@ constexpr int32_t kWarpsPerBlock = 4;
 constexpr int32_t kSmemPerWarp   = 28 * 1024; // 2 blocks x 4 warps x 28 KB per SM
 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const KernelParams P)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 2) poa_window_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
     const int32_t lane = threadIdx.x & 31;
@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) poa_window_kernel(const K
     const int32_t* rlen = P.read_len + wd.read_off;
     ScoreT* scores      = static_cast<ScoreT*>(P.scores) +
                      (BANDED ? static_cast<int64_t>(w) * P.banded_score_stride : wd.score_off);
-    const int32_t width = BANDED ? P.band + kBandPad : wd.scores_width;
+    const int32_t width = BANDED ? P.band + kBandRowPad : wd.scores_width;
 
     int32_t status     = kStSuccess;
     int32_t node_count = 0;
