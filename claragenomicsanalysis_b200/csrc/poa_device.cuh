@@ -625,11 +625,11 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
     }
 }
 
-// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first three
+// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first two
 // out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
 // node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
 // uses topsort_kahn.  All 32 lanes call this.
-constexpr int32_t kKahnBytesPerNode = 11; // 8 (out-degree + 3 edges) + 2 (queue) + 1 (remaining in-degree)
+constexpr int32_t kKahnBytesPerNode = 8; // 4 (two out-edges) + 2 (queue) + 1 (out-degree) + 1 (remaining in-degree)
 
 template <typename IdT>
 __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* smem, int32_t smem_bytes,
@@ -640,11 +640,13 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
     const int32_t cap = (smem_bytes / kKahnBytesPerNode) & ~7;
     if (node_count > cap)
         return false;
-    uint64_t* info  = reinterpret_cast<uint64_t*>(smem);
-    uint16_t* queue = reinterpret_cast<uint16_t*>(smem + 8 * cap);
-    uint8_t* deg    = smem + 10 * cap;
+    uint32_t* edges = reinterpret_cast<uint32_t*>(smem);            // out-edge 0 | out-edge 1 << 16
+    uint16_t* queue = reinterpret_cast<uint16_t*>(smem + 4 * cap);
+    uint8_t* outdeg = smem + 6 * cap;
+    uint8_t* deg    = smem + 7 * cap;
     const unsigned lt = (1u << lane) - 1u;
     int32_t tail      = 0;
+#pragma unroll 2
     for (int32_t n0 = 0; n0 < node_count; n0 += 32)
     {
         const int32_t n = n0 + lane;
@@ -653,16 +655,15 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
         {
             const uint32_t ic = g.in_cnt[n];
             const uint32_t oc = g.out_cnt[n];
-            uint64_t v        = oc;
+            uint32_t v        = 0;
             if (oc > 0)
-                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 0))) << 16;
+                v = static_cast<uint16_t>(g.out_edge(n, 0));
             if (oc > 1)
-                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 1))) << 32;
-            if (oc > 2)
-                v |= static_cast<uint64_t>(static_cast<uint16_t>(g.out_edge(n, 2))) << 48;
-            info[n] = v;
-            deg[n]  = static_cast<uint8_t>(ic);
-            source  = (ic == 0);
+                v |= static_cast<uint32_t>(static_cast<uint16_t>(g.out_edge(n, 1))) << 16;
+            edges[n]  = v;
+            outdeg[n] = static_cast<uint8_t>(oc);
+            deg[n]    = static_cast<uint8_t>(ic);
+            source    = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
         if (source)
@@ -672,20 +673,51 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
     __syncwarp();
     if (lane == 0)
     {
-        for (int32_t head = 0; head < tail; head++)
+        int32_t head = 0;
+        int32_t node = queue[0]; // a graph always has a source
+        while (true)
         {
-            const int32_t node = queue[head];
-            const uint64_t v   = info[node];
-            const int32_t oc   = static_cast<int32_t>(v & 0xffffu);
-            for (int32_t e = 0; e < oc; e++)
+            const uint32_t v  = edges[node];
+            const int32_t oc  = outdeg[node];
+            int32_t last      = -1;
+            if (oc > 0)
             {
-                const int32_t child = (e < 3) ? static_cast<int32_t>((v >> (16 * (e + 1))) & 0xffffu)
-                                              : static_cast<int32_t>(g.out_edge(node, e));
-                const uint8_t c = deg[child] - 1;
-                deg[child]      = c;
+                const int32_t child = static_cast<int32_t>(v & 0xffffu);
+                const uint8_t c     = deg[child] - 1;
+                deg[child]          = c;
                 if (c == 0)
+                {
                     queue[tail++] = static_cast<uint16_t>(child);
+                    last          = child;
+                }
             }
+            if (oc > 1)
+            {
+                const int32_t child = static_cast<int32_t>(v >> 16);
+                const uint8_t c     = deg[child] - 1;
+                deg[child]          = c;
+                if (c == 0)
+                {
+                    queue[tail++] = static_cast<uint16_t>(child);
+                    last          = child;
+                }
+            }
+            for (int32_t e = 2; e < oc; e++)
+            {
+                const int32_t child = static_cast<int32_t>(g.out_edge(node, e));
+                const uint8_t c     = deg[child] - 1;
+                deg[child]          = c;
+                if (c == 0)
+                {
+                    queue[tail++] = static_cast<uint16_t>(child);
+                    last          = child;
+                }
+            }
+            head++;
+            if (head >= tail)
+                break;
+            // the next node is the one just queued when the queue held nothing else (the common chain case)
+            node = (head == tail - 1 && last >= 0) ? last : static_cast<int32_t>(queue[head]);
         }
     }
     __syncwarp();

@@ -15,7 +15,7 @@ namespace poa_b200
 constexpr int32_t kMaxNodeEdges      = 50; // same limits as the reference: they are observable through
 constexpr int32_t kMaxNodeAlignments = 50; // edge_count_exceeded_maximum_graph_size
 constexpr int32_t kBandPad           = 8;  // cells right of the band kept at the sentinel (reference layout)
-constexpr int32_t kBandRowPad        = 16; // cells of padding in this engine's banded row stride (two 16-byte blocks)
+constexpr int32_t kBandRowPad        = 24; // cells of padding in this engine's banded row stride (three 16-byte blocks)
 constexpr int32_t kWarp              = 32;
 
 struct WindowDesc
@@ -39,7 +39,7 @@ struct ArenaLayout
     int64_t in_w;                                // uint16[50][M]
     int64_t aln_node;                            // IdT[max_seq + 32]  the alignment: node per read position
     int64_t row_bs;                              // int32[M + 1]   band start per score row
-    int64_t rowinfo;                             // uint32[3][M + 8] per-row descriptors of the fast fill when they do not fit shared memory
+    int64_t rowinfo;                             // uint32[3][M + 40] per-row descriptors of the fast fill
     int64_t cscore;                              // int32[M]       consensus scores / racon marks scratch
     int64_t cpred;                               // IdT[M]         consensus predecessors / racon stack
     int64_t marks, check;                        // uint8[M]
@@ -118,7 +118,7 @@ inline ArenaLayout make_arena_layout(int32_t M, int32_t aln_cap, int32_t max_rea
     L.in_w          = take(2 * m * kMaxNodeEdges);
     L.aln_node      = take(static_cast<int64_t>(id_bytes) * (max_seq + 32));
     L.row_bs        = take(4 * (m + 1));
-    L.rowinfo       = take(12 * (m + 8));
+    L.rowinfo       = take(12 * (m + 40));
     L.cscore        = take(4 * m);
     L.cpred         = take(id_bytes * (m + 8));
     L.marks         = take(m);

@@ -11,10 +11,10 @@ namespace poa_b200
 {
 
 constexpr int32_t kWarpsPerBlock = 4;
-constexpr int32_t kSmemPerWarp   = 28 * 1024; // 2 blocks x 4 warps x 28 KB per SM
+constexpr int32_t kSmemPerWarp   = 14 * 1024; // 4 blocks x 4 warps x 14 KB per SM
 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 2) poa_window_kernel(const KernelParams P)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
     const int32_t lane = threadIdx.x & 31;
