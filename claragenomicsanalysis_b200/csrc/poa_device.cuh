@@ -18,6 +18,64 @@ namespace poa_b200
 
 constexpr unsigned kFull = 0xffffffffu;
 
+// ---- explicit shared-memory accessors -----------------------------------------------------------------------
+// The per-warp scratch is reached through a pointer computed at run time, which the compiler treats as a generic
+// 64-bit address; these wrappers keep shared-memory traffic on 32-bit shared addresses (LDS/STS).
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a)
+{
+    uint16_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint2 lds_v2(uint32_t a)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t a)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v));
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v)
+{
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"(static_cast<uint16_t>(v)));
+}
+__device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v)
+{
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v));
+}
+__device__ __forceinline__ void sts_v2(uint32_t a, uint2 v)
+{
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y));
+}
+__device__ __forceinline__ void sts_v4(uint32_t a, uint4 v)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w));
+}
+
 enum : int32_t
 {
     kStSuccess           = 0,
@@ -640,12 +698,12 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
     const int32_t cap = (smem_bytes / kKahnBytesPerNode) & ~7;
     if (node_count > cap)
         return false;
-    uint32_t* edges = reinterpret_cast<uint32_t*>(smem);            // out-edge 0 | out-edge 1 << 16
-    uint16_t* queue = reinterpret_cast<uint16_t*>(smem + 4 * cap);
-    uint8_t* outdeg = smem + 6 * cap;
-    uint8_t* deg    = smem + 7 * cap;
-    const unsigned lt = (1u << lane) - 1u;
-    int32_t tail      = 0;
+    const uint32_t edges  = smem_u32(smem);   // u32[cap]: out-edge 0 | out-edge 1 << 16
+    const uint32_t queue  = edges + 4 * cap;  // u16[cap]
+    const uint32_t outdeg = edges + 6 * cap;  // u8[cap]
+    const uint32_t deg    = edges + 7 * cap;  // u8[cap]
+    const unsigned lt     = (1u << lane) - 1u;
+    int32_t tail          = 0;
 #pragma unroll 2
     for (int32_t n0 = 0; n0 < node_count; n0 += 32)
     {
@@ -660,70 +718,69 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
                 v = static_cast<uint16_t>(g.out_edge(n, 0));
             if (oc > 1)
                 v |= static_cast<uint32_t>(static_cast<uint16_t>(g.out_edge(n, 1))) << 16;
-            edges[n]  = v;
-            outdeg[n] = static_cast<uint8_t>(oc);
-            deg[n]    = static_cast<uint8_t>(ic);
-            source    = (ic == 0);
+            sts_u32(edges + 4 * n, v);
+            sts_u8(outdeg + n, oc);
+            sts_u8(deg + n, ic);
+            source = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
         if (source)
-            queue[tail + __popc(mask & lt)] = static_cast<uint16_t>(n);
+            sts_u16(queue + 2 * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
         tail += __popc(mask);
     }
     __syncwarp();
     if (lane == 0)
     {
-        int32_t head = 0;
-        int32_t node = queue[0]; // a graph always has a source
+        uint32_t head_a = queue;            // address of the queue head
+        uint32_t tail_a = queue + 2 * tail; // address one past the queue tail
+        uint32_t node   = lds_u16(head_a);  // a graph always has a source
         while (true)
         {
-            const uint32_t v  = edges[node];
-            const int32_t oc  = outdeg[node];
-            int32_t last      = -1;
+            const uint32_t v  = lds_u32(edges + 4 * node);
+            const uint32_t oc = lds_u8(outdeg + node);
             if (oc > 0)
             {
-                const int32_t child = static_cast<int32_t>(v & 0xffffu);
-                const uint8_t c     = deg[child] - 1;
-                deg[child]          = c;
+                const uint32_t child = v & 0xffffu;
+                const uint32_t c     = lds_u8(deg + child) - 1;
+                sts_u8(deg + child, c);
                 if (c == 0)
                 {
-                    queue[tail++] = static_cast<uint16_t>(child);
-                    last          = child;
+                    sts_u16(tail_a, child);
+                    tail_a += 2;
                 }
             }
             if (oc > 1)
             {
-                const int32_t child = static_cast<int32_t>(v >> 16);
-                const uint8_t c     = deg[child] - 1;
-                deg[child]          = c;
+                const uint32_t child = v >> 16;
+                const uint32_t c     = lds_u8(deg + child) - 1;
+                sts_u8(deg + child, c);
                 if (c == 0)
                 {
-                    queue[tail++] = static_cast<uint16_t>(child);
-                    last          = child;
+                    sts_u16(tail_a, child);
+                    tail_a += 2;
                 }
             }
-            for (int32_t e = 2; e < oc; e++)
+            for (uint32_t e = 2; e < oc; e++)
             {
-                const int32_t child = static_cast<int32_t>(g.out_edge(node, e));
-                const uint8_t c     = deg[child] - 1;
-                deg[child]          = c;
+                const uint32_t child = static_cast<uint16_t>(g.out_edge(node, e));
+                const uint32_t c     = lds_u8(deg + child) - 1;
+                sts_u8(deg + child, c);
                 if (c == 0)
                 {
-                    queue[tail++] = static_cast<uint16_t>(child);
-                    last          = child;
+                    sts_u16(tail_a, child);
+                    tail_a += 2;
                 }
             }
-            head++;
-            if (head >= tail)
+            head_a += 2;
+            if (head_a >= tail_a)
                 break;
-            // the next node is the one just queued when the queue held nothing else (the common chain case)
-            node = (head == tail - 1 && last >= 0) ? last : static_cast<int32_t>(queue[head]);
+            node = lds_u16(head_a);
         }
     }
     __syncwarp();
     for (int32_t i = lane; i < node_count; i += 32)
     {
-        const int32_t n = queue[i];
+        const int32_t n = static_cast<int32_t>(lds_u16(queue + 2 * i));
         g.sorted[i]     = static_cast<IdT>(n);
         g.pos[n]        = static_cast<IdT>(i);
     }

@@ -114,7 +114,7 @@ __device__ __forceinline__ int32_t pred_row(const Graph<IdT>& g, uint32_t d0, ui
 struct FastMatrix
 {
     const uint32_t* rows; // row r at rows + r * kFastRowWords
-    const uint32_t* tile; // [kTileRows][kTileStride]
+    uint32_t tile;        // shared address of [kTileRows][kTileStride] words
     int32_t tile_r0;      // first row of the tile
     int32_t tile_j;
     int32_t gap;
@@ -129,25 +129,19 @@ struct FastMatrix
     {
         const int32_t tr     = r - tile_r0;
         const bool in_tile   = (tr >= 0);
-        const uint32_t* trow = tile + tr * kTileStride;
+        const uint32_t trow  = tile + static_cast<uint32_t>(tr * (kTileStride * 4));
         const uint32_t* grow = rows + r * kFastRowWords;
-        int32_t b;
-        uint32_t lw;
+        uint4 lead;
         if (in_tile)
-        {
-            b  = static_cast<int32_t>(trow[0]);
-            lw = trow[3];
-        }
+            lead = lds_v4(trow);
         else
-        {
-            b  = static_cast<int32_t>(__ldcg(grow));
-            lw = __ldcg(grow + 3);
-        }
+            lead = __ldcg(reinterpret_cast<const uint4*>(grow));
+        const int32_t b = static_cast<int32_t>(lead.x);
         const int32_t c = column - b - 1; // 0-based cell of the band
         int32_t t;
         if (column == 0 || c == -1)
         {
-            t = hi16(lw);
+            t = hi16(lead.w);
         }
         else if (static_cast<uint32_t>(c) >= static_cast<uint32_t>(kFastBand))
         {
@@ -159,7 +153,7 @@ struct FastMatrix
             const int32_t tb  = blk - first_block(tile_j, b);
             uint32_t w;
             if (in_tile && static_cast<uint32_t>(tb) < static_cast<uint32_t>(kTileBlocks))
-                w = trow[((tb + 1) << 2) + (c & 3)];
+                w = lds_u32(trow + static_cast<uint32_t>((((tb + 1) << 2) + (c & 3)) << 2));
             else
                 w = __ldcg(grow + ((blk + 1) << 2) + (c & 3));
             t = (c & 4) ? hi16(w) : lo16(w);
@@ -169,7 +163,7 @@ struct FastMatrix
 };
 
 // Load the tile that ends at (row tile_r0 + kTileRows - 1, column j): score blocks and descriptors.  All lanes.
-__device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& rd, uint4* tile, uint2* tile_desc,
+__device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& rd, uint32_t tile, uint32_t tile_desc,
                                           int32_t tile_r0, int32_t j, float gradient, int32_t max_column,
                                           int32_t lane)
 {
@@ -183,14 +177,14 @@ __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& r
         {
             const int32_t b   = band_start(r, gradient, kFastBand, max_column);
             const int32_t blk = (tb == 0) ? 0 : FastMatrix::first_block(j, b) + tb;
-            tile[idx] = __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk);
+            sts_v4(tile + 16u * idx, __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk));
         }
     }
     for (int32_t tr = lane; tr < kTileRows; tr += 32)
     {
         const int32_t r = tile_r0 + tr;
         if (r >= 1)
-            tile_desc[tr] = make_uint2(rd.d0[r], rd.d1[r]);
+            sts_v2(tile_desc + 8u * tr, make_uint2(rd.d0[r], rd.d1[r]));
     }
     __syncwarp();
 }
@@ -205,11 +199,11 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     const int32_t rd_bytes = (read_len + kFastBand + 8 + 15) & ~15;
     if (!fast_path_eligible(node_count, read_len, band, gap, mismatch, match) || smem_bytes < kRingBytes + rd_bytes)
         return kFastNotTaken;
-    uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
-    uint32_t* ring = reinterpret_cast<uint32_t*>(smem);
-    uint8_t* rd    = smem + kRingBytes;
+    uint32_t* rows      = reinterpret_cast<uint32_t*>(scores);
+    const uint32_t ring = smem_u32(smem);  // shared addresses from here on
+    const uint32_t rd   = ring + kRingBytes;
     for (int32_t k = lane; k < rd_bytes; k += 32)
-        rd[k] = (k < read_len) ? read[k] : static_cast<uint8_t>(0);
+        sts_u8(rd + k, (k < read_len) ? read[k] : 0u);
     RowDesc desc;
     desc.d0 = g.rowinfo;
     desc.d1 = desc.d0 + (g.M + 40);
@@ -219,6 +213,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     const float gradient     = band_gradient(read_len, node_count);
     const int32_t sentinel   = band_sentinel<int16_t>(gap, mismatch, match);
     const uint32_t NEG2      = pack2(kNegT, kNegT);
+    const uint4 NEG4         = make_uint4(NEG2, NEG2, NEG2, NEG2);
 
     // pre-pass, one row per lane: row descriptors (independent gather chains in flight)
 #pragma unroll 2
@@ -235,17 +230,25 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         desc.d1[r] = pr[1] | (pr[2] << 16);
         desc.d2[r] = pr[3] | (pr[4] << 16);
     }
-    // row 0: T == 0 in columns 0 .. band + 3, sentinel beyond (cudapoa_nw_banded.cuh:138-143, :208-212);
-    // lead block {band start 0, -, -, left boundary 0}
+    // Row 0: T == 0 in columns 0 .. band + 3, sentinel beyond (cudapoa_nw_banded.cuh:138-143, :208-212); lead block
+    // {band start 0, -, -, left boundary 0}.  Pad blocks exist in the ring only: of row 0 in slot 0 (first pad block
+    // (0, sentinel)) and at the sentinel in the other slots; global rows are never read beyond their cell blocks.
     {
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         __stcg(reinterpret_cast<uint4*>(rows) + lane, z);
-        reinterpret_cast<uint4*>(ring)[lane] = z;
-        if (lane < 12)
+        sts_v4(ring + 16u * lane, z);
+        if (lane == 0)
         {
-            const uint32_t v = (lane < 4) ? 0u : (lane < 8) ? pack2(0, kNegT) : NEG2;
-            __stcg(rows + 128 + lane, v);
-            ring[128 + lane] = v;
+            __stcg(reinterpret_cast<uint4*>(rows) + 32, z);
+            sts_v4(ring + 16u * 32, z);
+            const uint32_t zn = pack2(0, kNegT);
+            sts_v4(ring + 16u * 33, make_uint4(zn, zn, zn, zn));
+            sts_v4(ring + 16u * 34, NEG4);
+        }
+        else if (lane < kRingRows)
+        {
+            sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 33, NEG4);
+            sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 34, NEG4);
         }
     }
     __syncwarp();
@@ -281,22 +284,18 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         {
             const int32_t r     = r0 + k;
             const uint32_t meta = __shfl_sync(kFull, c0, k);
-            const uint32_t p12  = __shfl_sync(kFull, c1, k);
             const int32_t bs    = __shfl_sync(kFull, cbs, k);
             const int32_t pc    = (meta >> 8) & 0x3f;
             const uint32_t base = meta & 0xff;
-            uint32_t p34        = 0;
-            if (pc > 3)
-                p34 = __shfl_sync(kFull, c2, k);
 
             // profile registers Q_i = (pd(cell i), pd(cell i + 4)); the lane's 8 read bases (positions
             // bs + 8*lane .., zero beyond the read) are re-read only when the band start moves
             if (bs != cached_bs)
             {
-                const uint32_t* src = reinterpret_cast<const uint32_t*>(rd + bs + 8 * lane);
-                rb_lo     = src[0];
-                rb_hi     = src[1];
-                cached_bs = bs;
+                const uint32_t ra = rd + bs + 8 * lane; // bs is a multiple of 4: 4-byte aligned, not always 8
+                rb_lo             = lds_u32(ra);
+                rb_hi             = lds_u32(ra + 4);
+                cached_bs         = bs;
             }
             uint32_t Q[4];
             {
@@ -310,48 +309,52 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
             }
 
             uint32_t S[4]     = {NEG2, NEG2, NEG2, NEG2};
-            bool any_in_band  = false;
+            int32_t min_d     = 1 << 20;   // smallest band shift over the predecessors
             int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
-            const int32_t np  = max(pc, 1);
-            for (int32_t p = 0; p < np; p++)
-            {
-                const int32_t prow = pred_row<IdT>(g, meta, p12, p34, r, p);
-                // the predecessor row: shared-memory ring when recent, else the global score matrix (through L2)
-                const bool recent        = (r - prow < kRingRows);
-                const uint32_t* prev_row = recent ? ring + (prow & (kRingRows - 1)) * kFastRowWords
-                                                  : rows + prow * kFastRowWords;
-                uint32_t pbs, plw;
-                if (recent)
-                {
-                    pbs = prev_row[0];
-                    plw = prev_row[3];
-                }
-                else
-                {
-                    pbs = __ldcg(prev_row);
-                    plw = __ldcg(prev_row + 3);
-                }
-                const int32_t d = bs - static_cast<int32_t>(pbs); // >= 0, multiple of 4
-                left_best       = max(left_best, hi16(plw));
-                // d > band: wholly outside this predecessor's band; every operand below then comes from a pad block
-                any_in_band |= (d <= kFastBand);
-                const int32_t sl = min(lane + (d >> 3) + 1, kPadBlock);     // block of the first vertical operand
-                const int32_t sn = min(sl + 1, kPadBlock);
-                const int32_t sc = min((8 * lane + d + 7) >> 3, kPadBlock); // block of the cell before it (lead = 0)
-                uint4 a, b;
+
+            // one predecessor row: S = max(S, diagonal and vertical candidates)
+            auto step = [&](int32_t prow) {
+                const int32_t sl0 = lane + 1;     // block of this lane's cells
+                uint4 lead, a, b;
                 uint32_t wv;
-                if (recent)
+                int32_t d;
+                if (r - prow < kRingRows) // shared-memory ring
                 {
-                    a  = *reinterpret_cast<const uint4*>(prev_row + 4 * sl);
-                    b  = *reinterpret_cast<const uint4*>(prev_row + 4 * sn);
-                    wv = prev_row[4 * sc + 3];
+                    const uint32_t pa = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
+                    lead              = lds_v4(pa);
+                    d                 = bs - static_cast<int32_t>(lead.x); // >= 0, multiple of 4
+                    const int32_t sl  = min(sl0 + (d >> 3), kPadBlock);    // block of the first vertical operand
+                    const int32_t sn  = min(sl + 1, kPadBlock);
+                    const int32_t sc  = min((8 * lane + d + 7) >> 3, kPadBlock); // block of the cell before it
+                    a                 = lds_v4(pa + 16u * sl);
+                    b                 = lds_v4(pa + 16u * sn);
+                    wv                = lds_u32(pa + 16u * sc + 12u);
                 }
-                else
+                else // far predecessor: the global score matrix (through L2); pad blocks are implied
                 {
-                    a  = __ldcg(reinterpret_cast<const uint4*>(prev_row + 4 * sl));
-                    b  = __ldcg(reinterpret_cast<const uint4*>(prev_row + 4 * sn));
-                    wv = __ldcg(prev_row + 4 * sc + 3);
+                    const uint4* prow4 = reinterpret_cast<const uint4*>(rows + prow * kFastRowWords);
+                    lead               = __ldcg(prow4);
+                    d                  = bs - static_cast<int32_t>(lead.x);
+                    const int32_t sl   = sl0 + (d >> 3);
+                    const int32_t sc   = (8 * lane + d + 7) >> 3;
+                    const uint32_t p33 = (prow == 0) ? pack2(0, kNegT) : NEG2; // row 0's first pad block
+                    a = b    = NEG4;
+                    wv       = NEG2;
+                    if (sl <= 32)
+                        a = __ldcg(prow4 + sl);
+                    else if (sl == 33)
+                        a = make_uint4(p33, p33, p33, p33);
+                    if (sl + 1 <= 32)
+                        b = __ldcg(prow4 + sl + 1);
+                    else if (sl + 1 == 33)
+                        b = make_uint4(p33, p33, p33, p33);
+                    if (sc <= 32)
+                        wv = __ldcg(reinterpret_cast<const uint32_t*>(prow4 + sc) + 3);
+                    else if (sc == 33)
+                        wv = p33;
                 }
+                left_best = max(left_best, hi16(lead.w));
+                min_d     = min(min_d, d);
                 // shift by an odd multiple of 4: operands straddle two blocks -> (hi of this block, lo of the
                 // next); the corner is then the low half of this block's last word, else the high half of the
                 // previous block's (the lead block for lane 0: the predecessor's left boundary)
@@ -369,9 +372,18 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 S[1] = __viaddmax_s16x2(V0, Q[1], __viaddmax_s16x2(V1, gapv, S[1]));
                 S[2] = __viaddmax_s16x2(V1, Q[2], __viaddmax_s16x2(V2, gapv, S[2]));
                 S[3] = __viaddmax_s16x2(V2, Q[3], __viaddmax_s16x2(V3, gapv, S[3]));
+            };
+            step(static_cast<int32_t>(meta >> 16)); // predecessor 0 (row 0 for a node without in-edges)
+            if (pc > 1)
+            {
+                const uint32_t p12 = __shfl_sync(kFull, c1, k);
+                const uint32_t p34 = (pc > 3) ? __shfl_sync(kFull, c2, k) : 0u;
+                for (int32_t p = 1; p < pc; p++)
+                    step(pred_row<IdT>(g, meta, p12, p34, r, p));
             }
-            if (!any_in_band)
-                return kFastNotTaken; // sentinel arithmetic would decide this row: let the exact path do it
+            // every predecessor wholly left of this row's band: sentinel arithmetic would decide the row
+            if (min_d > kFastBand)
+                return kFastNotTaken;
 
             // left boundary of this row in the tilted domain
             int32_t left_t = kNegT;
@@ -396,31 +408,25 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
             out.y = __vimax3_s16x2(S[1], cb, tl);
             out.z = __vimax3_s16x2(S[2], cb, tl);
             out.w = __vimax3_s16x2(S[3], cb, tl);
-            uint32_t* this_row = rows + r * kFastRowWords;
-            uint32_t* ring_row = ring + (r & (kRingRows - 1)) * kFastRowWords;
-            __stcg(reinterpret_cast<uint4*>(this_row) + 1 + lane, out);
-            reinterpret_cast<uint4*>(ring_row)[1 + lane] = out;
-            if (lane < 12)
+            uint4* this_row      = reinterpret_cast<uint4*>(rows + r * kFastRowWords);
+            const uint32_t rrow  = ring + static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
+            __stcg(this_row + 1 + lane, out);
+            sts_v4(rrow + 16u + 16u * lane, out);
+            if (lane == 0)
             {
-                // lanes 0..3: lead block {band start, 0, 0, left << 16}; lanes 4..11: the two pad blocks
-                uint32_t v   = NEG2;
-                int32_t word = 128 + lane;
-                if (lane < 4)
-                {
-                    v    = (lane == 0) ? static_cast<uint32_t>(bs)
-                                       : (lane == 3) ? (static_cast<uint32_t>(left_t) << 16) : 0u;
-                    word = lane;
-                }
-                __stcg(this_row + word, v);
-                ring_row[word] = v;
+                const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, static_cast<uint32_t>(left_t) << 16);
+                __stcg(this_row, lead);
+                sts_v4(rrow, lead);
+                if (r == kRingRows) // row 0 leaves ring slot 0: its special pad block goes with it
+                    sts_v4(rrow + 16u * 33, NEG4);
             }
             __syncwarp();
         }
     }
 
     // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len
-    uint32_t* tile   = ring;
-    uint2* tile_desc = reinterpret_cast<uint2*>(ring + kTileRows * kTileStride);
+    const uint32_t tile      = ring;
+    const uint32_t tile_desc = ring + kTileRows * kTileStride * 4;
     FastMatrix M{rows, tile, 1 << 30, 0, gap, sentinel}; // no tile yet: every cell comes from global memory
     int32_t best = INT16_MIN, best_row = 0;
     for (int32_t r = 1 + lane; r <= node_count; r += 32)
@@ -457,7 +463,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     while (!(i == 0 && j == 0) && loops < limit) // uniform: i, j, loops are broadcast at the end of every round
     {
         const int32_t tile_r0 = i - (kTileRows - 1);
-        load_tile(rows, desc, reinterpret_cast<uint4*>(tile), tile_desc, tile_r0, j, gradient, max_column, lane);
+        load_tile(rows, desc, tile, tile_desc, tile_r0, j, gradient, max_column, lane);
         M.tile_r0 = tile_r0;
         M.tile_j  = j;
         if (lane == 0)
@@ -472,7 +478,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 int32_t h  = 0;
                 if (i != 0)
                 {
-                    const uint2 dd      = tile_desc[i - tile_r0];
+                    const uint2 dd      = lds_v2(tile_desc + 8u * static_cast<uint32_t>(i - tile_r0));
                     const uint32_t meta = dd.x;
                     const uint32_t p12  = dd.y;
                     const int32_t pc    = (meta >> 8) & 0x3f;
@@ -480,7 +486,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                     const int32_t np    = max(pc, 1);
                     if (j != 0)
                     {
-                        const int32_t cost = ((meta & 0xff) == rd[j - 1]) ? match : mismatch;
+                        const int32_t cost = ((meta & 0xff) == lds_u8(rd + j - 1)) ? match : mismatch;
                         for (int32_t p = 0; p < np && !found; p++)
                         {
                             const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
