@@ -11,8 +11,9 @@ no collective on the data path; torch.distributed is used for the barrier and th
 Native arm, three numbers per run:
   value      windows/s with the batch's inputs already resident in HBM: K launches of the POA kernel timed with CUDA
              events on the batch's stream (cudapoa_b200_bench_relaunch), max over ranks.
-  e2e        windows/s through the reference-facing C ABI with HOST buffers every step: reset -> add_poa_group (host
-             staging) -> generate_poa (H2D + kernel) -> get_consensus (D2H + decode), wall clock between device syncs.
+  e2e        windows/s through the C ABI with HOST buffers every step: the window pipeline (cudapoa_b200_pipeline_run)
+             drives `--workers` Batch objects, each reset -> add_poa_group (host staging) -> generate_poa (H2D + kernel)
+             -> get_consensus (D2H + decode) per chunk of windows; wall clock between device syncs.
   roofline   HBM view (algorithmic bytes of SURVEY.md 8(d) / kernel time vs MEASURED_PEAKS.json) and, in
              `roofline_dpx`, the binding DPX view: achieved GCUPS vs the s16x2 DPX issue rate measured in this run.
   cpu_baseline  the reference repository's CPU implementation of the same job (SPOA, 3rdparty/spoa, built unmodified
@@ -161,7 +162,7 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "int32 (SPOA AVX2 engine, full alignment)", "data": "synthetic",
+        "vs_baseline": None, "dtype": "int16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "windows_per_step": n, "engine": "SPOA v3.0.0 kNW linear gaps, full (unbanded)"},
         "gcups": cells / t / 1e9,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
@@ -190,31 +191,16 @@ def run_native(args, rank, world, local_rank):
 
     device = local_rank
     torch.cuda.set_device(device)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist_mod
+    from claragenomicsanalysis_b200.distributed import Ranks
 
-        dist = dist_mod
-        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
+    ranks = Ranks(backend="nccl" if world > 1 else None)
 
     def barrier():
-        if dist is not None:
-            dist.barrier()
+        ranks.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    max_over_ranks = ranks.max
+    sum_over_ranks = ranks.sum
 
     ws, base = make_windows(args.windows, args.distinct, rank * args.distinct)
     free_b, total_b = torch.cuda.mem_get_info(device)
@@ -264,20 +250,36 @@ def run_native(args, rank, world, local_rank):
     gcups = total_cells / (ms_step * 1e-3) / 1e9
 
     # ---- end-to-end leg: host buffers -> C ABI -> host results every step ----
+    # The window pipeline (stream scheduler above the Batch interface): `--workers` host threads, each with its own
+    # stream and Batch, stage / launch / collect chunks of one wave of windows; staging overlaps other chunks' kernels.
+    from claragenomicsanalysis_b200.pipeline import WindowPipeline
+
+    batch.reset()
+    chunk = min(args.chunk, n_win)
+    pipe = WindowPipeline(ENGINE["max_reads"], ENGINE["max_seq"], int(args.worker_mem_gb * (1 << 30)),
+                          devices=(device,), workers_per_device=args.workers, output_type="consensus",
+                          cuda_banded_alignment=True, alignment_band_width=ENGINE["band"])
     for _ in range(max(args.warmup, 3)):
-        e2e_step()
+        pipe.run(ws, chunk)
+    if pipe.digest() != digest0:
+        raise RuntimeError("end-to-end results differ from the first pass")
     barrier()
     t0 = time.perf_counter()
+    h2d = d2h = 0
     for _ in range(args.steps):
-        e2e_step()
+        pipe.run(ws, chunk)
+        st2 = pipe.stats()
+        h2d += st2["h2d_bytes"]
+        d2h += st2["d2h_bytes"]
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     e2e_s = max_over_ranks((t1 - t0) / args.steps)
     barrier()
-    st2 = batch.stats()
     e2e_value = total_windows / e2e_s
-    if batch.result_digest() != digest0:
+    if pipe.digest() != digest0:
         raise RuntimeError("end-to-end results differ from the first pass")
+    e2e_launches = args.steps * ((n_win + chunk - 1) // chunk)
+    pipe.close()
 
     # ---- rooflines ----
     hbm_peak, hbm_src = measured_peaks()
@@ -299,10 +301,11 @@ def run_native(args, rank, world, local_rank):
         "gcups": gcups,
         "dp_cells_per_window": stats["dp_cells"] / n_win,
         "exact_path_alignments": stats["exact_path"], "alignments": stats["reads_aligned"],
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(st2["h2d_bytes"]),
-                "d2h_bytes_per_step": int(st2["d2h_bytes"]), "ms_per_step": e2e_s * 1e3,
-                "path": "add_poa_groups_flat(host numpy) -> generate_poa -> get_consensus via C ABI"},
-        "gpu_launches": 2 * args.steps,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d // args.steps),
+                "d2h_bytes_per_step": int(d2h // args.steps), "ms_per_step": e2e_s * 1e3,
+                "path": "cudapoa_b200_pipeline_run(host buffers): %d workers x (add_poa_group -> generate_poa -> "
+                        "get_consensus), chunks of %d windows" % (args.workers, chunk)},
+        "gpu_launches": args.steps + e2e_launches,
         "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
                      "algorithmic_bytes_per_launch": alg_bytes,
@@ -322,8 +325,7 @@ def run_native(args, rank, world, local_rank):
     batch.close()
     if rank == 0:
         print(json.dumps(line))
-    if dist is not None:
-        dist.destroy_process_group()
+    ranks.close()
 
 
 def cpu_baseline(args, base, batch, lib):
@@ -336,8 +338,8 @@ def cpu_baseline(args, base, batch, lib):
     probe = base.slice(0, max(2 * cores, 8))
     r = spoa_run(probe, cores)
     rate = len(probe) / max(r.seconds, 1e-6)
-    n = int(min(len(base), max(cores, rate * args.cpu_seconds)))
-    sample = base.slice(0, n)
+    n = int(max(cores, rate * args.cpu_seconds))
+    sample = base.tile(n)
     r = spoa_run(sample, cores)
     # agreement: the engine's consensus for the same windows
     batch.reset()
@@ -363,8 +365,8 @@ def reference_cudapoa(args, base):
 
         from claragenomicsanalysis_b200.cudapoa import CudaPoaBatch
 
-        n = min(len(base), 1024)
-        ws = base.slice(0, n)
+        n = 4736
+        ws = base.tile(n)
         b = CudaPoaBatch(ENGINE["max_reads"], ENGINE["max_seq"], 8 << 30, output_type="consensus",
                          cuda_banded_alignment=True, alignment_band_width=ENGINE["band"], lib=parity.ref_lib())
         best = None
@@ -389,9 +391,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--windows", type=int, default=16384, help="windows per step per GPU")
+    ap.add_argument("--windows", type=int, default=18944, help="windows per step per GPU (8 waves of 148 x 16)")
+    ap.add_argument("--chunk", type=int, default=2368, help="end-to-end leg: windows per batch round")
+    ap.add_argument("--workers", type=int, default=3, help="end-to-end leg: host threads / streams / batches")
+    ap.add_argument("--worker-mem-gb", type=float, default=8.0)
     ap.add_argument("--distinct", type=int, default=1024, help="distinct generated windows (tiled to --windows)")
-    ap.add_argument("--max-mem-gb", type=float, default=120.0)
+    ap.add_argument("--max-mem-gb", type=float, default=64.0)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -10,7 +10,7 @@ LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libcudapoa_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-SOURCES = ["engine.cu", "c_api.cpp"]
+SOURCES = ["engine.cu", "c_api.cpp", "pipeline.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-DCUDAPOA_B200_NATIVE", "-Xptxas", "-v",

@@ -195,6 +195,37 @@ int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* ins
  * iterations in milliseconds, measured on the batch's own stream; negative if nothing has been staged. */
 double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations);
 
+/* ---- Window pipeline (native library only; no reference counterpart) ------------------------------------------
+ * The stream scheduler / sharding layer above the Batch interface (the reference drives several Batch objects from
+ * std::async tasks in cudapoa/benchmarks/multi_batch.hpp:157-170; it has no multi-GPU code).  Each worker thread owns
+ * one stream and one Batch on one device and pulls chunks of windows from a shared queue; results land in slots
+ * indexed by window, so output order is deterministic.  devices may name the same device several times. */
+typedef struct cudapoa_b200_pipeline cudapoa_b200_pipeline;
+const char* cudapoa_b200_pipeline_last_error(void);
+cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int32_t n_devices,
+                                                    int32_t workers_per_device, size_t mem_per_worker,
+                                                    int8_t output_mask, const cudapoa_b200_batch_size* batch_size,
+                                                    int16_t gap_score, int16_t mismatch_score, int16_t match_score,
+                                                    int32_t cuda_banded_alignment);
+void cudapoa_b200_pipeline_destroy(cudapoa_b200_pipeline* p);
+/* Blocking: all windows (flat host buffers as in add_poa_groups_flat) through the workers.  chunk_windows = windows per
+ * batch round (0: automatic).  Returns 0 or a negative exception code (see last_error). */
+int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases, const int8_t* weights,
+                                  const int32_t* read_lengths, const int32_t* window_n_reads, int32_t n_windows,
+                                  int32_t chunk_windows);
+int32_t cudapoa_b200_pipeline_workers(const cudapoa_b200_pipeline* p);
+int32_t cudapoa_b200_pipeline_capacity(const cudapoa_b200_pipeline* p); /* smallest max_poas over the workers */
+double cudapoa_b200_pipeline_wall_ms(const cudapoa_b200_pipeline* p);   /* wall time of the last run            */
+int32_t cudapoa_b200_pipeline_stats(const cudapoa_b200_pipeline* p, cudapoa_b200_stats* out); /* summed over rounds */
+int32_t cudapoa_b200_pipeline_status(const cudapoa_b200_pipeline* p, int32_t window);
+int32_t cudapoa_b200_pipeline_consensus(const cudapoa_b200_pipeline* p, int32_t window, const char** seq,
+                                        const uint16_t** coverage); /* returns length */
+int32_t cudapoa_b200_pipeline_msa_rows(const cudapoa_b200_pipeline* p, int32_t window);
+int32_t cudapoa_b200_pipeline_msa_row(const cudapoa_b200_pipeline* p, int32_t window, int32_t row, const char** seq);
+int64_t cudapoa_b200_pipeline_total_chars(const cudapoa_b200_pipeline* p);
+/* Same hash as cudapoa_b200_result_digest of one batch holding windows [first, first + count). */
+uint64_t cudapoa_b200_pipeline_digest(const cudapoa_b200_pipeline* p, int32_t first, int32_t count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -217,3 +217,35 @@ def test_large_batch_properties(lib):
     lens = [len(c) for c in a["consensus"][:256]]
     assert 450 <= min(lens) and max(lens) <= 560
     assert all(max(cov) <= 30 for cov in a["coverage"][:256])
+
+
+# ---- window pipeline (stream scheduler / sharding layer) ------------------------------------------------------------
+@pytest.mark.parametrize("output", ["consensus", "msa"])
+def test_pipeline_matches_single_batch_and_oracle(lib, output):
+    from claragenomicsanalysis_b200.pipeline import WindowPipeline
+
+    ws = generate_windows(96, start_index=12000, template_length=(150, 400), n_reads=9)
+    eng = dict(max_seq=512, max_reads=9, band=256, banded=True, output=output)
+    single = parity.run_abi(lib, ws, max_mem=MEM, **eng)
+    o = parity.run_oracle(ws.slice(0, 12), **eng)
+    # two "devices" (the same GPU twice) x two workers, chunks of 7 windows: many rounds, every worker busy
+    p = WindowPipeline(9, 512, 1 << 30, devices=(0, 0), workers_per_device=2, output_type=output)
+    assert p.workers == 4
+    p.run(ws, chunk_windows=7)
+    assert p.statuses() == [int(s) for s in single["status"]]
+    for w in range(len(ws)):
+        if output == "consensus":
+            assert p.consensus(w) == (single["consensus"][w], list(single["coverage"][w]))
+        else:
+            assert p.msa(w) == list(single["msa"][w])
+    for w in range(12):
+        if output == "consensus":
+            assert p.consensus(w) == (o["consensus"][w], list(o["coverage"][w]))
+        else:
+            assert p.msa(w) == o["msa"][w]
+    st = p.stats()
+    assert st["windows"] == 96 and st["reads_aligned"] == 96 * 8
+    d1 = p.digest()
+    p.run(ws, chunk_windows=0)  # automatic chunking, second run on the same pipeline
+    assert p.digest() == d1
+    p.close()
