@@ -616,14 +616,26 @@ __device__ int32_t add_alignment(const Graph<IdT>& g, int32_t& node_count, const
                 const int32_t prev_weight = w ? w[k - 1] : 1;
                 const uint16_t add        = static_cast<uint16_t>(prev_weight + bw);
                 bool exists               = false;
-                const int32_t inc         = g.in_cnt[curr];
-                for (int32_t e = 0; e < inc; e++)
+                const int32_t inc         = make_new ? 0 : static_cast<int32_t>(g.in_cnt[curr]);
+                // the first three slots are fetched together (independent loads), the rest one by one; an edge
+                // occurs at most once per list, so "update every match" (:221-229) is "update the match"
+                const int32_t s0 = g.in_edge(curr, 0), s1 = g.in_edge(curr, 1), s2 = g.in_edge(curr, 2);
+                int32_t hit      = -1;
+                if (inc > 0 && s0 == head)
+                    hit = 0;
+                else if (inc > 1 && s1 == head)
+                    hit = 1;
+                else if (inc > 2 && s2 == head)
+                    hit = 2;
+                for (int32_t e = 3; e < inc && hit < 0; e++)
                 {
                     if (g.in_edge(curr, e) == head)
-                    {
-                        exists            = true;
-                        g.weight(curr, e) = static_cast<uint16_t>(g.weight(curr, e) + add);
-                    }
+                        hit = e;
+                }
+                if (hit >= 0)
+                {
+                    exists              = true;
+                    g.weight(curr, hit) = static_cast<uint16_t>(g.weight(curr, hit) + add);
                 }
                 if (!exists)
                 {
@@ -683,11 +695,11 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
     }
 }
 
-// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first two
+// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first three
 // out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
 // node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
 // uses topsort_kahn.  All 32 lanes call this.
-constexpr int32_t kKahnBytesPerNode = 8; // 4 (two out-edges) + 2 (queue) + 1 (out-degree) + 1 (remaining in-degree)
+constexpr int32_t kKahnBytesPerNode = 10; // 6 (three out-edges) + 2 (queue) + 1 (out-degree) + 1 (remaining in-degree)
 
 template <typename IdT>
 __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* smem, int32_t smem_bytes,
@@ -699,9 +711,10 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
     if (node_count > cap)
         return false;
     const uint32_t edges  = smem_u32(smem);   // u32[cap]: out-edge 0 | out-edge 1 << 16
-    const uint32_t queue  = edges + 4 * cap;  // u16[cap]
-    const uint32_t outdeg = edges + 6 * cap;  // u8[cap]
-    const uint32_t deg    = edges + 7 * cap;  // u8[cap]
+    const uint32_t edge2  = edges + 4 * cap;  // u16[cap]: out-edge 2
+    const uint32_t queue  = edges + 6 * cap;  // u16[cap]
+    const uint32_t outdeg = edges + 8 * cap;  // u8[cap]
+    const uint32_t deg    = edges + 9 * cap;  // u8[cap]
     const unsigned lt     = (1u << lane) - 1u;
     int32_t tail          = 0;
 #pragma unroll 2
@@ -713,12 +726,12 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
         {
             const uint32_t ic = g.in_cnt[n];
             const uint32_t oc = g.out_cnt[n];
-            uint32_t v        = 0;
-            if (oc > 0)
-                v = static_cast<uint16_t>(g.out_edge(n, 0));
-            if (oc > 1)
-                v |= static_cast<uint32_t>(static_cast<uint16_t>(g.out_edge(n, 1))) << 16;
-            sts_u32(edges + 4 * n, v);
+            // slots beyond the out-degree hold stale but readable values: load unconditionally, mask afterwards
+            const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0));
+            const uint32_t e1 = static_cast<uint16_t>(g.out_edge(n, 1));
+            const uint32_t e2 = static_cast<uint16_t>(g.out_edge(n, 2));
+            sts_u32(edges + 4 * n, e0 | (e1 << 16));
+            sts_u16(edge2 + 2 * n, e2);
             sts_u8(outdeg + n, oc);
             sts_u8(deg + n, ic);
             source = (ic == 0);
@@ -760,15 +773,26 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
                     tail_a += 2;
                 }
             }
-            for (uint32_t e = 2; e < oc; e++)
+            if (oc > 2)
             {
-                const uint32_t child = static_cast<uint16_t>(g.out_edge(node, e));
+                const uint32_t child = lds_u16(edge2 + 2 * node);
                 const uint32_t c     = lds_u8(deg + child) - 1;
                 sts_u8(deg + child, c);
                 if (c == 0)
                 {
                     sts_u16(tail_a, child);
                     tail_a += 2;
+                }
+                for (uint32_t e = 3; e < oc; e++)
+                {
+                    const uint32_t child2 = static_cast<uint16_t>(g.out_edge(node, e));
+                    const uint32_t c2     = lds_u8(deg + child2) - 1;
+                    sts_u8(deg + child2, c2);
+                    if (c2 == 0)
+                    {
+                        sts_u16(tail_a, child2);
+                        tail_a += 2;
+                    }
                 }
             }
             head_a += 2;

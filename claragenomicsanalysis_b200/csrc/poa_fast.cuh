@@ -163,29 +163,44 @@ struct FastMatrix
 };
 
 // Load the tile that ends at (row tile_r0 + kTileRows - 1, column j): score blocks and descriptors.  All lanes.
+// Loads are issued in groups of seven per lane before any of them is consumed, so a tile costs two or three
+// round trips to L2/HBM instead of one per block.
 __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& rd, uint32_t tile, uint32_t tile_desc,
                                           int32_t tile_r0, int32_t j, float gradient, int32_t max_column,
                                           int32_t lane)
 {
-#pragma unroll 2
-    for (int32_t idx = lane; idx < kTileRows * (kTileBlocks + 1); idx += 32)
+    constexpr int32_t kPerLane = kTileRows * (kTileBlocks + 1) / 32; // 14
+    constexpr int32_t kGroup   = 7;
+    static_assert(kPerLane % kGroup == 0 && kTileRows % 32 == 0, "tile shape");
+    uint2 dsc[kTileRows / 32];
+#pragma unroll
+    for (int32_t u = 0; u < kTileRows / 32; u++)
     {
-        const int32_t tr = idx / (kTileBlocks + 1);
-        const int32_t tb = idx - tr * (kTileBlocks + 1);
-        const int32_t r  = tile_r0 + tr;
-        if (r >= 0)
+        const int32_t r = tile_r0 + lane + 32 * u;
+        dsc[u]          = (r >= 1) ? make_uint2(rd.d0[r], rd.d1[r]) : make_uint2(0u, 0u);
+    }
+#pragma unroll
+    for (int32_t g0 = 0; g0 < kPerLane; g0 += kGroup)
+    {
+        uint4 v[kGroup];
+#pragma unroll
+        for (int32_t u = 0; u < kGroup; u++)
         {
+            const int32_t idx = lane + 32 * (g0 + u);
+            const int32_t tr  = idx / (kTileBlocks + 1);
+            const int32_t tb  = idx - tr * (kTileBlocks + 1);
+            const int32_t r   = max(tile_r0 + tr, 0);
             const int32_t b   = band_start(r, gradient, kFastBand, max_column);
             const int32_t blk = (tb == 0) ? 0 : FastMatrix::first_block(j, b) + tb;
-            sts_v4(tile + 16u * idx, __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk));
+            v[u]              = __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk);
         }
+#pragma unroll
+        for (int32_t u = 0; u < kGroup; u++)
+            sts_v4(tile + 16u * (lane + 32 * (g0 + u)), v[u]);
     }
-    for (int32_t tr = lane; tr < kTileRows; tr += 32)
-    {
-        const int32_t r = tile_r0 + tr;
-        if (r >= 1)
-            sts_v2(tile_desc + 8u * tr, make_uint2(rd.d0[r], rd.d1[r]));
-    }
+#pragma unroll
+    for (int32_t u = 0; u < kTileRows / 32; u++)
+        sts_v2(tile_desc + 8u * (lane + 32 * u), dsc[u]);
     __syncwarp();
 }
 
@@ -215,20 +230,46 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     const uint32_t NEG2      = pack2(kNegT, kNegT);
     const uint4 NEG4         = make_uint4(NEG2, NEG2, NEG2, NEG2);
 
-    // pre-pass, one row per lane: row descriptors (independent gather chains in flight)
-#pragma unroll 2
-    for (int32_t r = 1 + lane; r <= node_count; r += 32)
+    // pre-pass: row descriptors.  Each lane takes kPre rows per pass; the three dependent gather levels
+    // (rank -> node -> in-edges -> ranks of the predecessors) are each issued for all of them before the next.
     {
-        const int32_t node = g.sorted[r - 1];
-        const uint32_t pc  = g.in_cnt[node];
-        uint32_t pr[5];
+        constexpr int32_t kPre = 4;
+        for (int32_t rb = 1; rb <= node_count; rb += 32 * kPre)
+        {
+            int32_t node[kPre];
+            uint32_t pc[kPre], word[kPre];
+            int32_t pe[kPre][5];
 #pragma unroll
-        for (int k = 0; k < 5; k++)
-            pr[k] = (static_cast<uint32_t>(k) < pc) ? static_cast<uint32_t>(g.pos[g.in_edge(node, k)] + 1) : 0u;
-        desc.d0[r] = static_cast<uint32_t>(g.nodes[node]) | (pc << 8) | ((g.out_cnt[node] == 0) ? (1u << 14) : 0u) |
-                     (pr[0] << 16);
-        desc.d1[r] = pr[1] | (pr[2] << 16);
-        desc.d2[r] = pr[3] | (pr[4] << 16);
+            for (int u = 0; u < kPre; u++)
+            {
+                const int32_t r = min(rb + lane + 32 * u, node_count);
+                node[u]         = g.sorted[r - 1];
+            }
+#pragma unroll
+            for (int u = 0; u < kPre; u++)
+            {
+                pc[u]   = g.in_cnt[node[u]];
+                word[u] = static_cast<uint32_t>(g.nodes[node[u]]) | ((g.out_cnt[node[u]] == 0) ? (1u << 14) : 0u);
+#pragma unroll
+                for (int k = 0; k < 5; k++)
+                    pe[u][k] = g.in_edge(node[u], k); // slots beyond the in-degree: stale but readable
+            }
+#pragma unroll
+            for (int u = 0; u < kPre; u++)
+            {
+                uint32_t pr[5];
+#pragma unroll
+                for (int k = 0; k < 5; k++)
+                    pr[k] = (static_cast<uint32_t>(k) < pc[u]) ? static_cast<uint32_t>(g.pos[pe[u][k]] + 1) : 0u;
+                const int32_t r = rb + lane + 32 * u;
+                if (r <= node_count)
+                {
+                    desc.d0[r] = word[u] | (pc[u] << 8) | (pr[0] << 16);
+                    desc.d1[r] = pr[1] | (pr[2] << 16);
+                    desc.d2[r] = pr[3] | (pr[4] << 16);
+                }
+            }
+        }
     }
     // Row 0: T == 0 in columns 0 .. band + 3, sentinel beyond (cudapoa_nw_banded.cuh:138-143, :208-212); lead block
     // {band start 0, -, -, left boundary 0}.  Pad blocks exist in the ring only: of row 0 in slot 0 (first pad block
@@ -259,7 +300,6 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     const uint32_t pdx2  = pack2(pd_x, pd_x);
     const uint32_t pdmx2 = pack2(pd_m ^ pd_x, pd_m ^ pd_x);
 
-    int32_t cached_bs = -1;
     uint32_t rb_lo = 0, rb_hi = 0;
     // descriptors of the next chunk of 32 rows, one row per lane, loaded a chunk ahead
     uint32_t n0, n1, n2;
@@ -288,14 +328,12 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
             const int32_t pc    = (meta >> 8) & 0x3f;
             const uint32_t base = meta & 0xff;
 
-            // profile registers Q_i = (pd(cell i), pd(cell i + 4)); the lane's 8 read bases (positions
-            // bs + 8*lane .., zero beyond the read) are re-read only when the band start moves
-            if (bs != cached_bs)
+            // profile registers Q_i = (pd(cell i), pd(cell i + 4)) from the lane's 8 read bases (positions
+            // bs + 8*lane .., zero beyond the read)
             {
                 const uint32_t ra = rd + bs + 8 * lane; // bs is a multiple of 4: 4-byte aligned, not always 8
                 rb_lo             = lds_u32(ra);
                 rb_hi             = lds_u32(ra + 4);
-                cached_bs         = bs;
             }
             uint32_t Q[4];
             {
