@@ -1007,6 +1007,163 @@ __device__ int32_t generate_consensus(const Graph<IdT>& g, int32_t node_count, u
     return kStSuccess;
 }
 
+// The same consensus out of the warp's shared-memory scratch.  All lanes call this.
+//   * forward pass: the warp stages 256 ranks at a time (node, in-degree, first three in-edges and their weights;
+//     two gather levels, eight ranks per lane in flight), lane 0 runs the recurrence with node scores and
+//     predecessors in shared memory (and mirrors them to global memory for branch_completion);
+//   * backtrack: lane 0 follows the predecessor chain in shared memory and records the node ids, then the warp
+//     emits bases and coverages for all of them in parallel.
+// Returns -1 when the graph or the consensus does not fit the scratch (nothing written: use generate_consensus).
+constexpr int32_t kConsStageRanks = 256;
+constexpr int32_t kConsStageBytes = kConsStageRanks * 16;
+
+template <typename IdT>
+__device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus,
+                                           uint16_t* coverage, int32_t max_consensus, uint8_t* smem,
+                                           int32_t smem_bytes, int32_t lane)
+{
+    if (sizeof(IdT) != 2)
+        return -1;
+    const int32_t cap = ((smem_bytes - kConsStageBytes) / 6) & ~7;
+    if (node_count > cap || max_consensus > kConsStageBytes / 2)
+        return -1;
+    const uint32_t stage  = smem_u32(smem);              // uint4[256], later the path as u16[]
+    const uint32_t cscore = stage + kConsStageBytes;     // int32[cap], by node id
+    const uint32_t cpred  = cscore + 4 * cap;            // u16[cap], by node id (0xffff: none)
+
+    int32_t max_id = 0, max_score = -1;
+    for (int32_t c0 = 0; c0 < node_count; c0 += kConsStageRanks)
+    {
+        // stage ranks c0 .. c0 + 255
+        int32_t node[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            node[u] = g.sorted[min(c0 + lane + 32 * u, node_count - 1)];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+        {
+            const uint32_t n  = static_cast<uint32_t>(node[u]);
+            const uint32_t ic = g.in_cnt[n];
+            // slots beyond the in-degree hold stale but readable values
+            const uint32_t e0 = static_cast<uint16_t>(g.in_edge(n, 0)), e1 = static_cast<uint16_t>(g.in_edge(n, 1)),
+                           e2 = static_cast<uint16_t>(g.in_edge(n, 2));
+            const uint32_t w0 = g.weight(n, 0), w1 = g.weight(n, 1), w2 = g.weight(n, 2);
+            sts_v4(stage + 16u * (lane + 32 * u), make_uint4(n | (ic << 16), e0 | (e1 << 16), w0 | (w1 << 16), e2 | (w2 << 16)));
+        }
+        __syncwarp();
+        if (lane == 0)
+        {
+            const int32_t cend = min(kConsStageRanks, node_count - c0);
+            for (int32_t q = 0; q < cend; q++)
+            {
+                const uint4 rec    = lds_v4(stage + 16u * q);
+                const int32_t n    = static_cast<int32_t>(rec.x & 0xffffu);
+                const int32_t ic   = static_cast<int32_t>(rec.x >> 16);
+                int32_t pred       = -1;
+                int32_t score      = -1;
+                int32_t pred_score = 0; // cscore[pred]
+                for (int32_t e = 0; e < ic; e++)
+                {
+                    int32_t begin, w;
+                    if (e == 0)
+                    {
+                        begin = static_cast<int32_t>(rec.y & 0xffffu);
+                        w     = static_cast<int32_t>(rec.z & 0xffffu);
+                    }
+                    else if (e == 1)
+                    {
+                        begin = static_cast<int32_t>(rec.y >> 16);
+                        w     = static_cast<int32_t>(rec.z >> 16);
+                    }
+                    else if (e == 2)
+                    {
+                        begin = static_cast<int32_t>(rec.w & 0xffffu);
+                        w     = static_cast<int32_t>(rec.w >> 16);
+                    }
+                    else
+                    {
+                        begin = static_cast<uint16_t>(g.in_edge(n, e));
+                        w     = g.weight(n, e);
+                    }
+                    const int32_t bsc = static_cast<int32_t>(lds_u32(cscore + 4u * begin));
+                    if (score < w || (score == w && pred_score <= bsc))
+                    {
+                        score      = w;
+                        pred       = begin;
+                        pred_score = bsc;
+                    }
+                }
+                if (pred != -1)
+                    score += pred_score;
+                if (max_score <= score)
+                {
+                    max_id    = n;
+                    max_score = score;
+                }
+                sts_u32(cscore + 4u * n, static_cast<uint32_t>(score));
+                sts_u16(cpred + 2u * n, static_cast<uint32_t>(pred) & 0xffffu);
+                g.cscore[n] = score; // mirrors for branch_completion
+                g.cpred[n]  = static_cast<IdT>(pred);
+            }
+        }
+        __syncwarp();
+    }
+    int32_t loops = 0;
+    if (lane == 0)
+    {
+        while (g.out_cnt[max_id] != 0 && loops < node_count)
+        {
+            max_id = branch_completion<IdT>(g, g.pos[max_id], node_count);
+            loops++;
+        }
+    }
+    loops  = __shfl_sync(kFull, loops, 0);
+    max_id = __shfl_sync(kFull, max_id, 0);
+    if (loops >= node_count)
+        return kStLoopCountExceeded;
+    if (loops > 0) // predecessors changed in global memory: refresh the shared copy
+    {
+        __syncwarp();
+        for (int32_t n = lane; n < node_count; n += 32)
+            sts_u16(cpred + 2u * n, static_cast<uint32_t>(static_cast<int32_t>(g.cpred[n])) & 0xffffu);
+        __syncwarp();
+    }
+    // backtrack: node ids of the path, end -> start
+    const uint32_t path = stage;
+    int32_t count       = 0;
+    if (lane == 0)
+    {
+        uint32_t id = static_cast<uint32_t>(max_id);
+        while (true)
+        {
+            if (count < max_consensus)
+                sts_u16(path + 2u * count, id);
+            const uint32_t pred = lds_u16(cpred + 2u * id);
+            if (pred == 0xffffu)
+                break;
+            id = pred;
+            count++;
+        }
+    }
+    count = __shfl_sync(kFull, count, 0);
+    if (count >= max_consensus - 1)
+        return kStSeqSizeExceeded;
+    __syncwarp();
+    for (int32_t k = lane; k <= count; k += 32)
+    {
+        const int32_t id = static_cast<int32_t>(lds_u16(path + 2u * k));
+        consensus[k]     = g.nodes[id];
+        uint16_t cov     = g.cov[id];
+        const int32_t na = g.aln_cnt[id];
+        for (int32_t a = 0; a < na; a++)
+            cov = static_cast<uint16_t>(cov + g.cov[g.aln(id, a)]);
+        coverage[k] = cov;
+    }
+    if (lane == 0)
+        consensus[count + 1] = 0;
+    return kStSuccess;
+}
+
 // MSA column of every node (cudapoa_generate_msa.cuh:27-46); needs the SPOA-order sort.  Lane 0 only.
 template <typename IdT>
 __device__ int32_t msa_columns(const Graph<IdT>& g, int32_t node_count)

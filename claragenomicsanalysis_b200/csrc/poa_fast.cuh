@@ -131,32 +131,30 @@ struct FastMatrix
         const bool in_tile   = (tr >= 0);
         const uint32_t trow  = tile + static_cast<uint32_t>(tr * (kTileStride * 4));
         const uint32_t* grow = rows + r * kFastRowWords;
-        uint4 lead;
+        uint4 lead; // {band start, first block held by the tile (tile rows only), -, left boundary << 16}
         if (in_tile)
             lead = lds_v4(trow);
         else
             lead = __ldcg(reinterpret_cast<const uint4*>(grow));
-        const int32_t b = static_cast<int32_t>(lead.x);
-        const int32_t c = column - b - 1; // 0-based cell of the band
+        const int32_t c = column - static_cast<int32_t>(lead.x) - 1; // 0-based cell of the band
         int32_t t;
-        if (column == 0 || c == -1)
+        if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && column != 0)
+        {
+            const int32_t tb = (c >> 3) - static_cast<int32_t>(lead.y);
+            uint32_t w;
+            if (in_tile && static_cast<uint32_t>(tb) < static_cast<uint32_t>(kTileBlocks))
+                w = lds_u32(trow + 16u + static_cast<uint32_t>((tb << 4) + ((c & 3) << 2)));
+            else
+                w = __ldcg(grow + 4 + ((c >> 3) << 2) + (c & 3));
+            t = (c & 4) ? hi16(w) : lo16(w);
+        }
+        else if (column == 0 || c == -1)
         {
             t = hi16(lead.w);
         }
-        else if (static_cast<uint32_t>(c) >= static_cast<uint32_t>(kFastBand))
-        {
-            return sentinel;
-        }
         else
         {
-            const int32_t blk = c >> 3;
-            const int32_t tb  = blk - first_block(tile_j, b);
-            uint32_t w;
-            if (in_tile && static_cast<uint32_t>(tb) < static_cast<uint32_t>(kTileBlocks))
-                w = lds_u32(trow + static_cast<uint32_t>((((tb + 1) << 2) + (c & 3)) << 2));
-            else
-                w = __ldcg(grow + ((blk + 1) << 2) + (c & 3));
-            t = (c & 4) ? hi16(w) : lo16(w);
+            return sentinel;
         }
         return (t <= kNegThreshold) ? sentinel : t + gap * column;
     }
@@ -193,6 +191,8 @@ __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& r
             const int32_t b   = band_start(r, gradient, kFastBand, max_column);
             const int32_t blk = (tb == 0) ? 0 : FastMatrix::first_block(j, b) + tb;
             v[u]              = __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk);
+            if (tb == 0)
+                v[u].y = static_cast<uint32_t>(FastMatrix::first_block(j, b)); // free word of the lead block
         }
 #pragma unroll
         for (int32_t u = 0; u < kGroup; u++)
@@ -520,32 +520,51 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                     const uint32_t meta = dd.x;
                     const uint32_t p12  = dd.y;
                     const int32_t pc    = (meta >> 8) & 0x3f;
-                    const uint32_t p34  = (pc > 3) ? desc.d2[i] : 0u;
-                    const int32_t np    = max(pc, 1);
+                    const int32_t p0    = static_cast<int32_t>(meta >> 16);
+                    uint32_t p34        = 0;
                     if (j != 0)
                     {
+                        // diagonal moves, predecessor 0 first: the common step of the walk
                         const int32_t cost = ((meta & 0xff) == lds_u8(rd + j - 1)) ? match : mismatch;
-                        for (int32_t p = 0; p < np && !found; p++)
+                        h                  = M.get(p0, j - 1);
+                        if (sij == h + cost)
                         {
-                            const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
-                            h                = M.get(pi, j - 1);
-                            if (sij == h + cost)
+                            prev_i = p0;
+                            prev_j = j - 1;
+                            found  = true;
+                        }
+                        else if (pc > 1)
+                        {
+                            if (pc > 3)
+                                p34 = desc.d2[i];
+                            for (int32_t p = 1; p < pc && !found; p++)
                             {
-                                prev_i = pi;
-                                prev_j = j - 1;
-                                found  = true;
+                                const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
+                                h                = M.get(pi, j - 1);
+                                if (sij == h + cost)
+                                {
+                                    prev_i = pi;
+                                    prev_j = j - 1;
+                                    found  = true;
+                                }
                             }
                         }
                     }
-                    for (int32_t p = 0; p < np && !found; p++)
+                    if (!found)
                     {
-                        const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
-                        h                = M.get(pi, j);
-                        if (sij == h + gap)
+                        if (pc > 3)
+                            p34 = desc.d2[i];
+                        const int32_t np = max(pc, 1);
+                        for (int32_t p = 0; p < np && !found; p++)
                         {
-                            prev_i = pi;
-                            prev_j = j;
-                            found  = true;
+                            const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
+                            h                = M.get(pi, j);
+                            if (sij == h + gap)
+                            {
+                                prev_i = pi;
+                                prev_j = j;
+                                found  = true;
+                            }
                         }
                     }
                 }

@@ -112,10 +112,17 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
     {
         if (!MSA)
         {
-            if (lane == 0)
-                status = generate_consensus<IdT>(g, node_count, P.consensus + static_cast<int64_t>(w) * P.max_consensus,
-                                                 P.coverage + static_cast<int64_t>(w) * P.max_consensus,
-                                                 P.max_consensus);
+            uint8_t* cons_out  = P.consensus + static_cast<int64_t>(w) * P.max_consensus;
+            uint16_t* cov_out  = P.coverage + static_cast<int64_t>(w) * P.max_consensus;
+            int32_t rc         = generate_consensus_smem<IdT>(g, node_count, cons_out, cov_out, P.max_consensus, smem,
+                                                              P.smem_per_warp, lane);
+            if (rc < 0) // does not fit the scratch: serial version out of global memory
+            {
+                if (lane == 0)
+                    rc = generate_consensus<IdT>(g, node_count, cons_out, cov_out, P.max_consensus);
+                rc = __shfl_sync(kFull, rc, 0);
+            }
+            status = rc;
         }
         else
         {
