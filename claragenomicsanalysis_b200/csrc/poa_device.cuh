@@ -699,10 +699,10 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 // out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
 // node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
 // uses topsort_kahn.  All 32 lanes call this.
-constexpr int32_t kKahnBytesPerNode = 10; // 6 (three out-edges) + 2 (queue) + 1 (out-degree) + 1 (remaining in-degree)
+constexpr int32_t kKahnBytesPerNode = 10; // 8-byte record {edge0, edge1, edge2, out-degree, remaining in-degree} + queue
 
 template <typename IdT>
-__device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* smem, int32_t smem_bytes,
+__device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint32_t smem, int32_t smem_bytes,
                                   int32_t lane)
 {
     if (sizeof(IdT) != 2)
@@ -710,13 +710,10 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
     const int32_t cap = (smem_bytes / kKahnBytesPerNode) & ~7;
     if (node_count > cap)
         return false;
-    const uint32_t edges  = smem_u32(smem);   // u32[cap]: out-edge 0 | out-edge 1 << 16
-    const uint32_t edge2  = edges + 4 * cap;  // u16[cap]: out-edge 2
-    const uint32_t queue  = edges + 6 * cap;  // u16[cap]
-    const uint32_t outdeg = edges + 8 * cap;  // u8[cap]
-    const uint32_t deg    = edges + 9 * cap;  // u8[cap]
-    const unsigned lt     = (1u << lane) - 1u;
-    int32_t tail          = 0;
+    const uint32_t rec   = smem;           // uint2[cap]: x = edge0 | edge1 << 16, y = edge2 | out-degree << 16 | in-degree << 24
+    const uint32_t queue = rec + 8 * cap;  // u16[cap]
+    const unsigned lt    = (1u << lane) - 1u;
+    int32_t tail         = 0;
 #pragma unroll 2
     for (int32_t n0 = 0; n0 < node_count; n0 += 32)
     {
@@ -726,14 +723,11 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
         {
             const uint32_t ic = g.in_cnt[n];
             const uint32_t oc = g.out_cnt[n];
-            // slots beyond the out-degree hold stale but readable values: load unconditionally, mask afterwards
+            // slots beyond the out-degree hold stale but readable values: load unconditionally, never used
             const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0));
             const uint32_t e1 = static_cast<uint16_t>(g.out_edge(n, 1));
             const uint32_t e2 = static_cast<uint16_t>(g.out_edge(n, 2));
-            sts_u32(edges + 4 * n, e0 | (e1 << 16));
-            sts_u16(edge2 + 2 * n, e2);
-            sts_u8(outdeg + n, oc);
-            sts_u8(deg + n, ic);
+            sts_v2(rec + 8 * n, make_uint2(e0 | (e1 << 16), e2 | (oc << 16) | (ic << 24)));
             source = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
@@ -747,59 +741,39 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint8
         uint32_t head_a = queue;            // address of the queue head
         uint32_t tail_a = queue + 2 * tail; // address one past the queue tail
         uint32_t node   = lds_u16(head_a);  // a graph always has a source
+        // visit(child): one in-edge of child is satisfied; queue it when it was the last one
+#define POA_KAHN_VISIT(child_expr)                                  \
+    {                                                               \
+        const uint32_t child_ = (child_expr);                       \
+        const uint32_t da_    = rec + 8 * child_ + 7;               \
+        const uint32_t c_     = lds_u8(da_) - 1;                    \
+        sts_u8(da_, c_);                                            \
+        if (c_ == 0)                                                \
+        {                                                           \
+            sts_u16(tail_a, child_);                                \
+            tail_a += 2;                                            \
+        }                                                           \
+    }
         while (true)
         {
-            const uint32_t v  = lds_u32(edges + 4 * node);
-            const uint32_t oc = lds_u8(outdeg + node);
+            const uint2 v     = lds_v2(rec + 8 * node);
+            const uint32_t oc = (v.y >> 16) & 0xffu;
             if (oc > 0)
-            {
-                const uint32_t child = v & 0xffffu;
-                const uint32_t c     = lds_u8(deg + child) - 1;
-                sts_u8(deg + child, c);
-                if (c == 0)
-                {
-                    sts_u16(tail_a, child);
-                    tail_a += 2;
-                }
-            }
+                POA_KAHN_VISIT(v.x & 0xffffu)
             if (oc > 1)
-            {
-                const uint32_t child = v >> 16;
-                const uint32_t c     = lds_u8(deg + child) - 1;
-                sts_u8(deg + child, c);
-                if (c == 0)
-                {
-                    sts_u16(tail_a, child);
-                    tail_a += 2;
-                }
-            }
+                POA_KAHN_VISIT(v.x >> 16)
             if (oc > 2)
             {
-                const uint32_t child = lds_u16(edge2 + 2 * node);
-                const uint32_t c     = lds_u8(deg + child) - 1;
-                sts_u8(deg + child, c);
-                if (c == 0)
-                {
-                    sts_u16(tail_a, child);
-                    tail_a += 2;
-                }
+                POA_KAHN_VISIT(v.y & 0xffffu)
                 for (uint32_t e = 3; e < oc; e++)
-                {
-                    const uint32_t child2 = static_cast<uint16_t>(g.out_edge(node, e));
-                    const uint32_t c2     = lds_u8(deg + child2) - 1;
-                    sts_u8(deg + child2, c2);
-                    if (c2 == 0)
-                    {
-                        sts_u16(tail_a, child2);
-                        tail_a += 2;
-                    }
-                }
+                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, e)))
             }
             head_a += 2;
             if (head_a >= tail_a)
                 break;
             node = lds_u16(head_a);
         }
+#undef POA_KAHN_VISIT
     }
     __syncwarp();
     for (int32_t i = lane; i < node_count; i += 32)
@@ -1019,7 +993,7 @@ constexpr int32_t kConsStageBytes = kConsStageRanks * 16;
 
 template <typename IdT>
 __device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus,
-                                           uint16_t* coverage, int32_t max_consensus, uint8_t* smem,
+                                           uint16_t* coverage, int32_t max_consensus, uint32_t smem,
                                            int32_t smem_bytes, int32_t lane)
 {
     if (sizeof(IdT) != 2)
@@ -1027,7 +1001,7 @@ __device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_cou
     const int32_t cap = ((smem_bytes - kConsStageBytes) / 6) & ~7;
     if (node_count > cap || max_consensus > kConsStageBytes / 2)
         return -1;
-    const uint32_t stage  = smem_u32(smem);              // uint4[256], later the path as u16[]
+    const uint32_t stage  = smem;                        // uint4[256], later the path as u16[]
     const uint32_t cscore = stage + kConsStageBytes;     // int32[cap], by node id
     const uint32_t cpred  = cscore + 4 * cap;            // u16[cap], by node id (0xffff: none)
 

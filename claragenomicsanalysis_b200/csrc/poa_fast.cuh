@@ -207,7 +207,7 @@ __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& r
 template <typename IdT>
 __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
                                        int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
-                                       int32_t mismatch, int32_t match, uint8_t* smem, int32_t smem_bytes,
+                                       int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
                                        int32_t lane)
 {
     // shared-memory scratch: [ring of recent rows | read, zero padded]
@@ -215,7 +215,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     if (!fast_path_eligible(node_count, read_len, band, gap, mismatch, match) || smem_bytes < kRingBytes + rd_bytes)
         return kFastNotTaken;
     uint32_t* rows      = reinterpret_cast<uint32_t*>(scores);
-    const uint32_t ring = smem_u32(smem);  // shared addresses from here on
+    const uint32_t ring = smem;            // shared addresses from here on
     const uint32_t rd   = ring + kRingBytes;
     for (int32_t k = lane; k < rd_bytes; k += 32)
         sts_u8(rd + k, (k < read_len) ? read[k] : 0u);
@@ -272,21 +272,15 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         }
     }
     // Row 0: T == 0 in columns 0 .. band + 3, sentinel beyond (cudapoa_nw_banded.cuh:138-143, :208-212); lead block
-    // {band start 0, -, -, left boundary 0}.  Pad blocks exist in the ring only: of row 0 in slot 0 (first pad block
-    // (0, sentinel)) and at the sentinel in the other slots; global rows are never read beyond their cell blocks.
+    // {band start 0, -, -, left boundary 0}.  It lives in global memory only: a row whose predecessor is row 0 (a
+    // node without in-edges) takes the far path below, which knows row 0's padding.  Ring slots carry their two pad
+    // blocks at the sentinel once and for all; global rows are never read beyond their cell blocks.
     {
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         __stcg(reinterpret_cast<uint4*>(rows) + lane, z);
-        sts_v4(ring + 16u * lane, z);
         if (lane == 0)
-        {
             __stcg(reinterpret_cast<uint4*>(rows) + 32, z);
-            sts_v4(ring + 16u * 32, z);
-            const uint32_t zn = pack2(0, kNegT);
-            sts_v4(ring + 16u * 33, make_uint4(zn, zn, zn, zn));
-            sts_v4(ring + 16u * 34, NEG4);
-        }
-        else if (lane < kRingRows)
+        if (lane < kRingRows)
         {
             sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 33, NEG4);
             sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 34, NEG4);
@@ -301,32 +295,41 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     const uint32_t pdmx2 = pack2(pd_m ^ pd_x, pd_m ^ pd_x);
 
     uint32_t rb_lo = 0, rb_hi = 0;
-    // descriptors of the next chunk of 32 rows, one row per lane, loaded a chunk ahead
-    uint32_t n0, n1, n2;
+    // Descriptors travel in registers: chunk c* holds rows r0 .. r0 + 31 (one row per lane), chunk n* the next 32
+    // rows, loaded a chunk ahead; band starts likewise.  The row loop receives its descriptor by shuffle, issued one
+    // iteration early.
+    uint32_t c0 = 0, c1 = 0, c2 = 0, n0, n1, n2;
+    int32_t cbs = 0, nbs;
     {
         const int32_t rr = min(1 + lane, node_count);
-        n0 = desc.d0[rr];
-        n1 = desc.d1[rr];
-        n2 = desc.d2[rr];
+        n0  = desc.d0[rr];
+        n1  = desc.d1[rr];
+        n2  = desc.d2[rr];
+        nbs = band_start(rr, gradient, kFastBand, max_column);
     }
-    for (int32_t r0 = 1; r0 <= node_count; r0 += 32)
+    uint32_t meta_next = __shfl_sync(kFull, n0, 0);
+    int32_t bs_next    = __shfl_sync(kFull, nbs, 0);
     {
-        const uint32_t c0 = n0, c1 = n1, c2 = n2;
-        const int32_t cbs = band_start(min(r0 + lane, node_count), gradient, kFastBand, max_column);
+        for (int32_t r = 1; r <= node_count; r++)
         {
-            const int32_t rr = min(r0 + 32 + lane, node_count);
-            n0 = desc.d0[rr];
-            n1 = desc.d1[rr];
-            n2 = desc.d2[rr];
-        }
-        const int32_t kmax = min(32, node_count - r0 + 1);
-        for (int32_t k = 0; k < kmax; k++)
-        {
-            const int32_t r     = r0 + k;
-            const uint32_t meta = __shfl_sync(kFull, c0, k);
-            const int32_t bs    = __shfl_sync(kFull, cbs, k);
-            const int32_t pc    = (meta >> 8) & 0x3f;
-            const uint32_t base = meta & 0xff;
+            const int32_t k = (r - 1) & 31;
+            if (k == 0) // next chunk becomes current, fetch the one after
+            {
+                c0  = n0;
+                c1  = n1;
+                c2  = n2;
+                cbs = nbs;
+                const int32_t rr = min(r + 32 + lane, node_count);
+                n0  = desc.d0[rr];
+                n1  = desc.d1[rr];
+                n2  = desc.d2[rr];
+                nbs = band_start(rr, gradient, kFastBand, max_column);
+            }
+            const uint32_t meta   = meta_next;
+            const int32_t bs      = bs_next;
+            const int32_t pc      = (meta >> 8) & 0x3f;
+            const uint32_t base   = meta & 0xff;
+            const int32_t ring_lo = max(r - (kRingRows - 1), 1); // oldest row the ring still holds (never row 0)
 
             // profile registers Q_i = (pd(cell i), pd(cell i + 4)) from the lane's 8 read bases (positions
             // bs + 8*lane .., zero beyond the read)
@@ -356,7 +359,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 uint4 lead, a, b;
                 uint32_t wv;
                 int32_t d;
-                if (r - prow < kRingRows) // shared-memory ring
+                if (prow >= ring_lo) // shared-memory ring
                 {
                     const uint32_t pa = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
                     lead              = lds_v4(pa);
@@ -412,6 +415,12 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 S[3] = __viaddmax_s16x2(V2, Q[3], __viaddmax_s16x2(V3, gapv, S[3]));
             };
             step(static_cast<int32_t>(meta >> 16)); // predecessor 0 (row 0 for a node without in-edges)
+            {
+                // descriptor of the next row, needed first thing next iteration
+                const int32_t kn = r & 31;
+                meta_next        = __shfl_sync(kFull, kn ? c0 : n0, kn);
+                bs_next          = __shfl_sync(kFull, kn ? cbs : nbs, kn);
+            }
             if (pc > 1)
             {
                 const uint32_t p12 = __shfl_sync(kFull, c1, k);
@@ -455,8 +464,6 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, static_cast<uint32_t>(left_t) << 16);
                 __stcg(this_row, lead);
                 sts_v4(rrow, lead);
-                if (r == kRingRows) // row 0 leaves ring slot 0: its special pad block goes with it
-                    sts_v4(rrow + 16u * 33, NEG4);
             }
             __syncwarp();
         }

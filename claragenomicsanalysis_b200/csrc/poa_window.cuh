@@ -17,11 +17,15 @@ template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
-    const int32_t lane = threadIdx.x & 31;
-    const int32_t w    = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    int32_t lane    = threadIdx.x & 31;
+    const int32_t w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     if (w >= P.n_windows)
         return;
-    uint8_t* smem = smem_block + static_cast<size_t>(threadIdx.x >> 5) * P.smem_per_warp; // this warp's scratch
+    // this warp's scratch as a 32-bit shared address; both values are made opaque so that they live in registers
+    // instead of being recomputed from the special registers all over the kernel
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
 
     const WindowDesc wd = P.windows[w];
     const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
