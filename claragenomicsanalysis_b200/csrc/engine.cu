@@ -201,6 +201,8 @@ private:
     uint32_t* stat_rows_d_ = nullptr;
     uint32_t* stat_exact_d_ = nullptr;
     unsigned long long* stat_cells_d_ = nullptr;
+    int32_t* next_window_d_           = nullptr; // windows are handed to warps through this counter
+    int32_t sm_count_                 = 0;
     uint8_t* consensus_d_  = nullptr;
     uint16_t* coverage_d_  = nullptr;
     uint8_t* msa_d_        = nullptr;
@@ -257,7 +259,7 @@ void B200Batch::allocate(size_t max_mem)
         a(n * 4);                     // node_count
         a(n * 4);                     // stat_rows
         a(n * 4);                     // stat_exact
-        a(n * 8);                     // stat_cells
+        a((n + 1) * 8);               // stat_cells + the launch's window counter
         a(msa_ ? 0 : n * C);          // consensus
         a(msa_ ? 0 : n * C * 2);      // coverage
         a(msa_ ? n * S * C : 0);      // msa
@@ -278,7 +280,9 @@ void B200Batch::allocate(size_t max_mem)
     node_count_d_   = carve<int32_t>(cur, n);
     stat_rows_d_    = carve<uint32_t>(cur, n);
     stat_exact_d_   = carve<uint32_t>(cur, n);
-    stat_cells_d_   = carve<unsigned long long>(cur, n);
+    GW_CU_CHECK_ERR(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_id_));
+    stat_cells_d_   = carve<unsigned long long>(cur, n + 1);
+    next_window_d_  = reinterpret_cast<int32_t*>(stat_cells_d_ + n);
     consensus_d_    = carve<uint8_t>(cur, msa_ ? 0 : n * C);
     coverage_d_     = carve<uint16_t>(cur, msa_ ? 0 : n * C);
     msa_d_          = carve<uint8_t>(cur, msa_ ? n * S * C : 0);
@@ -410,33 +414,37 @@ StatusType B200Batch::add_poa_group(std::vector<StatusType>& per_seq_status, con
 }
 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
-static void launch_one(const KernelParams& P, cudaStream_t stream)
+static void launch_one(const KernelParams& P, int32_t sm_count, cudaStream_t stream)
 {
     const dim3 block(kWarpsPerBlock * 32);
-    const dim3 grid((P.n_windows + kWarpsPerBlock - 1) / kWarpsPerBlock);
     const size_t smem = static_cast<size_t>(kWarpsPerBlock) * static_cast<size_t>(P.smem_per_warp);
     auto kernel       = poa_window_kernel<ScoreT, IdT, BANDED, MSA>;
     // per device and cheap; batches on several devices share this code
     GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    // persistent warps: at most one resident wave of CTAs, windows are pulled from P.next_window
+    const int32_t needed = (P.n_windows + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    int per_sm           = 1;
+    GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
+    const dim3 grid(std::max(1, std::min(needed, sm_count * std::max(per_sm, 1))));
     kernel<<<grid, block, smem, stream>>>(P);
 }
 
 template <typename ScoreT, typename IdT>
-static void launch_typed(const KernelParams& P, bool banded, bool msa, cudaStream_t stream)
+static void launch_typed(const KernelParams& P, bool banded, bool msa, int32_t sm_count, cudaStream_t stream)
 {
     if (banded)
     {
         if (msa)
-            launch_one<ScoreT, IdT, true, true>(P, stream);
+            launch_one<ScoreT, IdT, true, true>(P, sm_count, stream);
         else
-            launch_one<ScoreT, IdT, true, false>(P, stream);
+            launch_one<ScoreT, IdT, true, false>(P, sm_count, stream);
     }
     else
     {
         if (msa)
-            launch_one<ScoreT, IdT, false, true>(P, stream);
+            launch_one<ScoreT, IdT, false, true>(P, sm_count, stream);
         else
-            launch_one<ScoreT, IdT, false, false>(P, stream);
+            launch_one<ScoreT, IdT, false, false>(P, sm_count, stream);
     }
 }
 
@@ -460,6 +468,7 @@ void B200Batch::launch()
     P.stat_rows           = stat_rows_d_;
     P.stat_exact          = stat_exact_d_;
     P.stat_cells          = stat_cells_d_;
+    P.next_window         = next_window_d_;
     P.max_nodes           = plan_.M;
     P.max_consensus       = batch_size_.max_consensus_size;
     P.max_reads           = std::max(max_sequences_per_poa_, 1);
@@ -474,12 +483,13 @@ void B200Batch::launch()
     const char* env = std::getenv("CUDAPOA_B200_SPOA_ACCURATE");
     P.spoa_accurate = (env != nullptr && env[0] == '1') ? 1 : 0;
 #endif
+    GW_CU_CHECK_ERR(cudaMemsetAsync(next_window_d_, 0, sizeof(int32_t), stream_));
     if (!plan_.score32)
-        launch_typed<int16_t, int16_t>(P, banded_, msa_, stream_);
+        launch_typed<int16_t, int16_t>(P, banded_, msa_, sm_count_, stream_);
     else if (!plan_.size32)
-        launch_typed<int32_t, int16_t>(P, banded_, msa_, stream_);
+        launch_typed<int32_t, int16_t>(P, banded_, msa_, sm_count_, stream_);
     else
-        launch_typed<int32_t, int32_t>(P, banded_, msa_, stream_);
+        launch_typed<int32_t, int32_t>(P, banded_, msa_, sm_count_, stream_);
     GW_CU_CHECK_ERR(cudaPeekAtLastError());
 }
 

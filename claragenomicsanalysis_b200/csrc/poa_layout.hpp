@@ -80,6 +80,7 @@ struct KernelParams
     int32_t band;
     int32_t gap, mismatch, match;
     int32_t spoa_accurate;
+    int32_t* next_window; // zeroed before the launch; warps take window ids from it
     int32_t smem_per_warp; // bytes of shared-memory scratch each warp (= window) owns
 };
 

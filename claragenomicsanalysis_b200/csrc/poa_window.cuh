@@ -17,15 +17,22 @@ template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
-    int32_t lane    = threadIdx.x & 31;
-    const int32_t w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    if (w >= P.n_windows)
-        return;
+    int32_t lane = threadIdx.x & 31;
     // this warp's scratch as a 32-bit shared address; both values are made opaque so that they live in registers
     // instead of being recomputed from the special registers all over the kernel
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
     asm volatile("" : "+r"(smem));
+
+    // persistent warp: windows differ in length and depth, so they are handed out one at a time
+    for (;;)
+    {
+    int32_t w = 0;
+    if (lane == 0)
+        w = atomicAdd(P.next_window, 1);
+    w = __shfl_sync(kFull, w, 0);
+    if (w >= P.n_windows)
+        break;
 
     const WindowDesc wd = P.windows[w];
     const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
@@ -159,6 +166,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
         P.stat_rows[w]  = rows;
         P.stat_exact[w] = exact;
         P.stat_cells[w] = cells;
+    }
+    __syncwarp(); // the scratch is reused by the next window
     }
 }
 
