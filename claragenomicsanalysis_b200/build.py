@@ -15,7 +15,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-DCUDAPOA_B200_NATIVE", "-Xptxas", "-v",
     "-I" + os.path.join(ROOT, "include"), "-I" + CSRC,
-]
+] + os.environ.get("CUDAPOA_B200_DEFS", "").split()  # development only: -D switches for A/B kernels
 
 
 def _inputs():

@@ -67,6 +67,23 @@ __device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v)
 {
     asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v));
 }
+__device__ __forceinline__ int32_t lds_s16(uint32_t a)
+{
+    int32_t v;
+    asm volatile("{\n\t.reg .s16 t;\n\tld.shared.s16 t, [%1];\n\tcvt.s32.s16 %0, t;\n\t}" : "=r"(v) : "r"(a));
+    return v;
+}
+// predicated stores: straight-line code where a branch would cost more than the store
+__device__ __forceinline__ void sts_u16_if(uint32_t a, uint32_t v, bool on)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u16 [%0], %1;\n\t}" ::"r"(a),
+                 "h"(static_cast<uint16_t>(v)), "r"(static_cast<uint32_t>(on)));
+}
+__device__ __forceinline__ void sts_u8_if(uint32_t a, uint32_t v, bool on)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u8 [%0], %1;\n\t}" ::"r"(a), "r"(v),
+                 "r"(static_cast<uint32_t>(on)));
+}
 __device__ __forceinline__ void sts_v2(uint32_t a, uint2 v)
 {
     asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y));
@@ -699,6 +716,9 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 // out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
 // node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
 // uses topsort_kahn.  All 32 lanes call this.
+#ifndef POA_AB
+#define POA_AB 0
+#endif
 constexpr int32_t kKahnBytesPerNode = 10; // 8-byte record {edge0, edge1, edge2, out-degree, remaining in-degree} + queue
 
 template <typename IdT>

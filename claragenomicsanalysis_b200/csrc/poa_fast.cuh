@@ -46,11 +46,12 @@ constexpr int32_t kNegT         = -30000; // tilted-domain stand-in for the refe
 constexpr int32_t kNegThreshold = -25000; // anything at or below is sentinel class
 constexpr int32_t kRingRows     = 16;     // power of two
 constexpr int32_t kRingBytes    = kRingRows * kFastRowWords * 4;
-constexpr int32_t kTileRows     = 64;     // traceback tile: rows x (lead block + kTileBlocks cell blocks)
-constexpr int32_t kTileBlocks   = 6;
-constexpr int32_t kTileStride   = (kTileBlocks + 1) * 4; // words per tile row
+constexpr int32_t kTileRows     = 64; // traceback tile: rows x columns of plain int16 tilted scores
+constexpr int32_t kTileCols     = 48; // columns the walk may use; a tile row also has 8 cells of slack on either side
+constexpr int32_t kTileRowBytes = (kTileCols + 16) * 2;
+constexpr int32_t kTileItems    = kTileCols / 8 + 1; // 16-byte blocks of a score row that can overlap the columns
 static_assert(kRowBlocks == 35, "row layout");
-static_assert(kTileRows * kTileStride * 4 + kTileRows * 8 <= kRingBytes, "the tile reuses the ring's memory");
+static_assert(kTileRows * kTileRowBytes + kTileRows * 8 <= kRingBytes, "the tile reuses the ring's memory");
 
 __device__ __forceinline__ uint32_t pack2(int32_t lo, int32_t hi)
 {
@@ -107,100 +108,91 @@ __device__ __forceinline__ int32_t pred_row(const Graph<IdT>& g, uint32_t d0, ui
     return g.pos[g.in_edge(g.sorted[row - 1], p)] + 1;
 }
 
-// Reads of the tilted score matrix with the reference's get_score semantics (cudapoa_nw_banded.cuh:106-120),
-// returning un-tilted H values; sentinel-class cells come back as the reference's sentinel.  Rows of the current
-// tile are served from shared memory, anything else from the global score matrix.  A tile row holds the row's
-// lead block and the kTileBlocks cell blocks that end with the block of column tile_j.
-struct FastMatrix
+// Reads of the tilted score matrix from global memory with the reference's get_score semantics
+// (cudapoa_nw_banded.cuh:106-120), in the tilted domain: out-of-band cells come back as kNegT, which stands for the
+// reference's sentinel.  Real values are above kNegThreshold by construction, so a comparison "score == neighbour +
+// cost" between a real score and a sentinel-class neighbour is false here exactly as it is in the reference.
+__device__ __forceinline__ int32_t tilted_score_global(const uint32_t* rows, int32_t r, int32_t column)
 {
-    const uint32_t* rows; // row r at rows + r * kFastRowWords
-    uint32_t tile;        // shared address of [kTileRows][kTileStride] words
-    int32_t tile_r0;      // first row of the tile
-    int32_t tile_j;
-    int32_t gap;
-    int32_t sentinel;
-
-    static __device__ __forceinline__ int32_t first_block(int32_t tile_j, int32_t b)
+    const uint32_t* grow = rows + r * kFastRowWords;
+    const uint4 lead     = __ldcg(reinterpret_cast<const uint4*>(grow)); // {band start, -, -, left boundary << 16}
+    const int32_t c      = column - static_cast<int32_t>(lead.x) - 1;    // 0-based cell of the band
+    int32_t t            = kNegT;
+    if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && column != 0)
     {
-        const int32_t hi = min(max((tile_j - b - 1) >> 3, 0), 31); // block of column tile_j, clamped to the row
-        return max(hi - (kTileBlocks - 1), 0);
+        const uint32_t w = __ldcg(grow + 4 + ((c >> 3) << 2) + (c & 3));
+        t                = (c & 4) ? hi16(w) : lo16(w);
     }
-    __device__ __forceinline__ int32_t get(int32_t r, int32_t column) const
+    else if (column == 0 || c == -1)
     {
-        const int32_t tr     = r - tile_r0;
-        const bool in_tile   = (tr >= 0);
-        const uint32_t trow  = tile + static_cast<uint32_t>(tr * (kTileStride * 4));
-        const uint32_t* grow = rows + r * kFastRowWords;
-        uint4 lead; // {band start, first block held by the tile (tile rows only), -, left boundary << 16}
-        if (in_tile)
-            lead = lds_v4(trow);
-        else
-            lead = __ldcg(reinterpret_cast<const uint4*>(grow));
-        const int32_t c = column - static_cast<int32_t>(lead.x) - 1; // 0-based cell of the band
-        int32_t t;
-        if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && column != 0)
-        {
-            const int32_t tb = (c >> 3) - static_cast<int32_t>(lead.y);
-            uint32_t w;
-            if (in_tile && static_cast<uint32_t>(tb) < static_cast<uint32_t>(kTileBlocks))
-                w = lds_u32(trow + 16u + static_cast<uint32_t>((tb << 4) + ((c & 3) << 2)));
-            else
-                w = __ldcg(grow + 4 + ((c >> 3) << 2) + (c & 3));
-            t = (c & 4) ? hi16(w) : lo16(w);
-        }
-        else if (column == 0 || c == -1)
-        {
-            t = hi16(lead.w);
-        }
-        else
-        {
-            return sentinel;
-        }
-        return (t <= kNegThreshold) ? sentinel : t + gap * column;
+        t = hi16(lead.w);
     }
-};
+    return (t <= kNegThreshold) ? kNegT : t;
+}
 
-// Load the tile that ends at (row tile_r0 + kTileRows - 1, column j): score blocks and descriptors.  All lanes.
-// Loads are issued in groups of seven per lane before any of them is consumed, so a tile costs two or three
-// round trips to L2/HBM instead of one per block.
+// Load the traceback tile: rows tile_r0 .. tile_r0 + kTileRows - 1, absolute columns tile_c0 .. tile_c0 + kTileCols - 1
+// (tile_c0 = 1 mod 4), as plain int16 tilted scores indexed by absolute column: cell (row, column) lives at
+//   tile + (row - tile_r0) * kTileRowBytes + 2 * (column - tile_c0 + 8).
+// The row-register order of the score matrix is undone here, once per tile, so that the walk reads a cell with one
+// address computation and one load.  Cells outside a row's band are written as kNegT, the left-boundary value goes
+// to column == band start, which reproduces get_score for every column of the tile.  Row descriptors (d0, d1) go to
+// tile_desc.  All lanes; loads are issued in groups of seven per lane before any of them is consumed.
 __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& rd, uint32_t tile, uint32_t tile_desc,
-                                          int32_t tile_r0, int32_t j, float gradient, int32_t max_column,
+                                          int32_t tile_r0, int32_t tile_c0, float gradient, int32_t max_column,
                                           int32_t lane)
 {
-    constexpr int32_t kPerLane = kTileRows * (kTileBlocks + 1) / 32; // 14
+    constexpr int32_t kPerLane = kTileRows * kTileItems / 32; // 14
     constexpr int32_t kGroup   = 7;
     static_assert(kPerLane % kGroup == 0 && kTileRows % 32 == 0, "tile shape");
+    const uint32_t NEG2 = pack2(kNegT, kNegT);
     uint2 dsc[kTileRows / 32];
+    uint4 lead[kTileRows / 32];
 #pragma unroll
     for (int32_t u = 0; u < kTileRows / 32; u++)
     {
         const int32_t r = tile_r0 + lane + 32 * u;
         dsc[u]          = (r >= 1) ? make_uint2(rd.d0[r], rd.d1[r]) : make_uint2(0u, 0u);
+        lead[u]         = __ldcg(reinterpret_cast<const uint4*>(rows + max(r, 0) * kFastRowWords));
     }
 #pragma unroll
     for (int32_t g0 = 0; g0 < kPerLane; g0 += kGroup)
     {
         uint4 v[kGroup];
+        uint32_t at[kGroup];
 #pragma unroll
         for (int32_t u = 0; u < kGroup; u++)
         {
             const int32_t idx = lane + 32 * (g0 + u);
-            const int32_t tr  = idx / (kTileBlocks + 1);
-            const int32_t tb  = idx - tr * (kTileBlocks + 1);
+            const int32_t tr  = idx / kTileItems;
+            const int32_t kb  = idx - tr * kTileItems;
             const int32_t r   = max(tile_r0 + tr, 0);
             const int32_t b   = band_start(r, gradient, kFastBand, max_column);
-            const int32_t blk = (tb == 0) ? 0 : FastMatrix::first_block(j, b) + tb;
-            v[u]              = __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + blk);
-            if (tb == 0)
-                v[u].y = static_cast<uint32_t>(FastMatrix::first_block(j, b)); // free word of the lead block
+            const int32_t c0  = tile_c0 - b - 1;  // band cell under the tile's first column, a multiple of 4
+            const int32_t blk = (c0 >> 3) + kb;   // block of the row this item moves (floor division)
+            const int32_t x   = 8 * blk - c0 + 8; // its first cell in the tile row: 4 .. 56
+            at[u]             = tile + static_cast<uint32_t>(tr * kTileRowBytes + 2 * x);
+            v[u]              = make_uint4(NEG2, NEG2, NEG2, NEG2);
+            if (static_cast<uint32_t>(blk) < 32u)
+                v[u] = __ldcg(reinterpret_cast<const uint4*>(rows + r * kFastRowWords) + 1 + blk);
         }
 #pragma unroll
         for (int32_t u = 0; u < kGroup; u++)
-            sts_v4(tile + 16u * (lane + 32 * (g0 + u)), v[u]);
+        {
+            // words (c0,c4) (c1,c5) (c2,c6) (c3,c7) -> cells in column order
+            sts_v2(at[u], make_uint2(__byte_perm(v[u].x, v[u].y, 0x5410), __byte_perm(v[u].z, v[u].w, 0x5410)));
+            sts_v2(at[u] + 8u, make_uint2(__byte_perm(v[u].x, v[u].y, 0x7632), __byte_perm(v[u].z, v[u].w, 0x7632)));
+        }
     }
+    __syncwarp();
 #pragma unroll
     for (int32_t u = 0; u < kTileRows / 32; u++)
+    {
         sts_v2(tile_desc + 8u * (lane + 32 * u), dsc[u]);
+        // left boundary: the cell at column == band start
+        const int32_t x = static_cast<int32_t>(lead[u].x) - tile_c0;
+        if (static_cast<uint32_t>(x) < static_cast<uint32_t>(kTileCols))
+            sts_u16(tile + static_cast<uint32_t>((lane + 32 * u) * kTileRowBytes + 2 * (x + 8)), lead[u].w >> 16);
+    }
     __syncwarp();
 }
 
@@ -226,7 +218,6 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
 
     const int32_t max_column = read_len + 1;
     const float gradient     = band_gradient(read_len, node_count);
-    const int32_t sentinel   = band_sentinel<int16_t>(gap, mismatch, match);
     const uint32_t NEG2      = pack2(kNegT, kNegT);
     const uint4 NEG4         = make_uint4(NEG2, NEG2, NEG2, NEG2);
 
@@ -443,9 +434,19 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
             S[3] = __vmaxs2(S[3], S[2]);
             const uint32_t tl = __byte_perm(S[3], NEG2, 0x1054); // (NEG, S3.lo): cells 0..3 feed cells 4..7
             uint32_t tot      = __vmaxs2(S[3], tl);         // hi half = maximum over this lane's 8 cells
-#pragma unroll
-            for (int32_t s = 1; s < 32; s <<= 1)
-                tot = __vmaxs2(tot, __shfl_up_sync(kFull, tot, s)); // lanes < s receive their own value back
+            // prefix maximum over the lanes in three rounds (radix 4, 4, 2): the shuffles of a round are independent,
+            // so the chain is three shuffle latencies instead of five.  Lanes below the shift receive their own value.
+            {
+                const uint32_t u1 = __shfl_up_sync(kFull, tot, 1);
+                const uint32_t u2 = __shfl_up_sync(kFull, tot, 2);
+                const uint32_t u3 = __shfl_up_sync(kFull, tot, 3);
+                tot               = __vmaxs2(__vimax3_s16x2(tot, u1, u2), u3);
+                const uint32_t v1 = __shfl_up_sync(kFull, tot, 4);
+                const uint32_t v2 = __shfl_up_sync(kFull, tot, 8);
+                const uint32_t v3 = __shfl_up_sync(kFull, tot, 12);
+                tot               = __vmaxs2(__vimax3_s16x2(tot, v1, v2), v3);
+                tot               = __vmaxs2(tot, __shfl_up_sync(kFull, tot, 16));
+            }
             uint32_t excl = __shfl_up_sync(kFull, tot, 1);
             if (lane == 0)
                 excl = static_cast<uint32_t>(left_t) << 16;
@@ -469,16 +470,16 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         }
     }
 
-    // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len
+    // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len.
+    // All candidates share the column, so tilted scores compare like the scores themselves.
     const uint32_t tile      = ring;
-    const uint32_t tile_desc = ring + kTileRows * kTileStride * 4;
-    FastMatrix M{rows, tile, 1 << 30, 0, gap, sentinel}; // no tile yet: every cell comes from global memory
+    const uint32_t tile_desc = ring + kTileRows * kTileRowBytes;
     int32_t best = INT16_MIN, best_row = 0;
     for (int32_t r = 1 + lane; r <= node_count; r += 32)
     {
         if (desc.d0[r] & (1u << 14))
         {
-            const int32_t s = M.get(r, read_len);
+            const int32_t s = tilted_score_global(rows, r, read_len);
             if (s > best)
             {
                 best     = s;
@@ -500,23 +501,34 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     }
 
     // traceback (cudapoa_nw_banded.cuh:386-480): lane 0 walks, the warp reloads the tile when the walk leaves it.
+    // The walk compares tilted scores: with T = H - gap * j, "H[i][j] == H[p][j-1] + cost" reads
+    // "T[i][j] == T[p][j-1] + cost - gap", the vertical move "T[i][j] == T[p][j] + gap", the horizontal move
+    // "T[i][j] == T[i][j-1]".  This is the reference's decision as long as the cell the walk stands on is a real
+    // score (see tilted_score_global); it is from the first cell on, or the exact path takes over.
     // g.aln_node[] first receives ROW indices (0: inserted base); they become node ids in a parallel pass below.
     int32_t i = (best > INT16_MIN) ? best_row : 0, j = read_len;
+    if (tilted_score_global(rows, i, j) <= kNegThreshold)
+        return kFastNotTaken;
     int32_t aligned = 0, loops = 0;
     int32_t prev_i = 0, prev_j = 0; // lane 0's copies carry over between tiles, as in the reference's single loop
     const int32_t limit = read_len + node_count + 2;
     while (!(i == 0 && j == 0) && loops < limit) // uniform: i, j, loops are broadcast at the end of every round
     {
         const int32_t tile_r0 = i - (kTileRows - 1);
-        load_tile(rows, desc, tile, tile_desc, tile_r0, j, gradient, max_column, lane);
-        M.tile_r0 = tile_r0;
-        M.tile_j  = j;
+        const int32_t tile_c0 = ((j + 3) & ~3) + 1 - kTileCols; // columns tile_c0 .. tile_c0 + 47 include j
+        load_tile(rows, desc, tile, tile_desc, tile_r0, tile_c0, gradient, max_column, lane);
         if (lane == 0)
         {
             const int32_t row_floor = (tile_r0 <= 0) ? 0 : tile_r0 + 12; // leave before predecessors fall out
-            const int32_t col_floor = j - 8 * (kTileBlocks - 2);         // ... or column j - 1 does
-            int32_t sij             = M.get(i, j);
-            while (!(i == 0 && j == 0) && loops < limit && i >= row_floor && j > col_floor)
+            // tilted score of (row, column), column within the tile's columns
+            auto cell = [&](int32_t row, int32_t column) -> int32_t {
+                const int32_t tr = row - tile_r0;
+                if (tr >= 0)
+                    return lds_s16(tile + static_cast<uint32_t>(tr * kTileRowBytes + 2 * (column - tile_c0 + 8)));
+                return tilted_score_global(rows, row, column);
+            };
+            int32_t sij = cell(i, j);
+            while (!(i == 0 && j == 0) && loops < limit && i >= row_floor && j > tile_c0)
             {
                 loops++;
                 bool found = false;
@@ -532,8 +544,8 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                     if (j != 0)
                     {
                         // diagonal moves, predecessor 0 first: the common step of the walk
-                        const int32_t cost = ((meta & 0xff) == lds_u8(rd + j - 1)) ? match : mismatch;
-                        h                  = M.get(p0, j - 1);
+                        const int32_t cost = ((meta & 0xff) == lds_u8(rd + j - 1)) ? pd_m : pd_x;
+                        h                  = cell(p0, j - 1);
                         if (sij == h + cost)
                         {
                             prev_i = p0;
@@ -547,7 +559,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                             for (int32_t p = 1; p < pc && !found; p++)
                             {
                                 const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
-                                h                = M.get(pi, j - 1);
+                                h                = cell(pi, j - 1);
                                 if (sij == h + cost)
                                 {
                                     prev_i = pi;
@@ -565,7 +577,7 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                         for (int32_t p = 0; p < np && !found; p++)
                         {
                             const int32_t pi = pred_row<IdT>(g, meta, p12, p34, i, p);
-                            h                = M.get(pi, j);
+                            h                = cell(pi, j);
                             if (sij == h + gap)
                             {
                                 prev_i = pi;
@@ -577,8 +589,8 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                 }
                 if (!found && j > 0)
                 {
-                    h = M.get(i, j - 1);
-                    if (sij == h + gap)
+                    h = cell(i, j - 1);
+                    if (sij == h)
                     {
                         prev_i = i;
                         prev_j = j - 1;
