@@ -75,7 +75,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
                 break;
             }
             int32_t aln_len = kFastNotTaken;
-            if (BANDED && sizeof(ScoreT) == 2)
+            // The packed path computes exact integer scores whenever it accepts a window, so it also serves batches
+            // whose score type is int32 because of their largest window; it only borrows the window's score area.
+            if (BANDED)
                 aln_len = align_fast_banded16<IdT>(g, node_count, seq, len, reinterpret_cast<int16_t*>(scores),
                                                    P.band, P.gap, P.mismatch, P.match, smem, P.smem_per_warp, lane);
             if (aln_len == kFastNotTaken)
