@@ -173,6 +173,17 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def ncu_traffic(n_windows):
+    """DRAM bytes one launch of n_windows moves, from the committed ncu capture (bytes per window x windows)."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            t = json.load(f)
+        return float(t["dram_bytes_per_window"]) * n_windows
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def run_native(args, rank, world, local_rank):
     import torch  # device sync + torch.distributed plumbing only
 
@@ -307,7 +318,9 @@ def run_native(args, rank, world, local_rank):
                         "get_consensus), chunks of %d windows" % (args.workers, chunk)},
         "gpu_launches": args.steps + e2e_launches,
         "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                     "frac": achieved_gbs / hbm_peak, "traffic": ncu_traffic(n_win), "peak_source": hbm_src,
+                     "traffic_source": "profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of "
+                                       "one ncu --set full capture of this kernel, scaled to this launch's windows",
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "note": "integer DP: the binding roofline is the DPX issue rate, see roofline_dpx"},
         "roofline_dpx": {"bound": "dpx-int16", "achieved": per_gpu_gcups, "peak": dpx_peak_gcups, "unit": "GCUPS",
@@ -319,7 +332,8 @@ def run_native(args, rank, world, local_rank):
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args, base, batch, lib)
-        ref_gpu = reference_cudapoa(args, base)
+        with _StdoutToStderr():
+            ref_gpu = reference_cudapoa(args, base)
         if ref_gpu is not None:
             line["reference_cudapoa_gpu"] = ref_gpu
     batch.close()
@@ -351,6 +365,22 @@ def cpu_baseline(args, base, batch, lib):
             "gcups": r.cells / r.seconds / 1e9,
             "sample": "%d cfg2 windows, SPOA v3.0.0 (AVX2, full alignment) on %d threads, %.1f s" % (n, cores, r.seconds),
             "consensus_agreement_with_engine": agree / n}
+
+
+class _StdoutToStderr:
+    """fd-level redirect: native code that logs on stdout must not break the one-JSON-line contract."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self._saved, 1)
+        os.close(self._saved)
+        return False
 
 
 def reference_cudapoa(args, base):

@@ -24,6 +24,7 @@ CASES = {
     "cfg4_msa": ("cfg4", 32, 6400, 100, "msa", True, 32 << 30, 8),
     "cfg5b": ("cfg5b", 1024, 2560, 60, "consensus", True, 32 << 30, 256),
     "cfg5b_big": ("cfg5b", 4096, 2560, 60, "consensus", True, 100 << 30, 2048),
+    "cfg5b_huge": ("cfg5b", 8192, 2560, 60, "consensus", True, 130 << 30, 8192),
 }
 
 
