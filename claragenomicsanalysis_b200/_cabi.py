@@ -59,6 +59,7 @@ class StatsC(ctypes.Structure):
         ("d2h_bytes", ctypes.c_int64),
         ("kernel_ms", ctypes.c_double),
         ("graph_kernel_ms", ctypes.c_double),
+        ("widened", ctypes.c_int64),
     ]
 
 

@@ -180,9 +180,19 @@ cudapoa_b200_batch* CUDAPOA_CABI(create_batch)(int32_t device_id, void* stream, 
     cudapoa_b200_batch* handle = nullptr;
     int32_t rc                 = guarded([&]() {
         std::unique_ptr<cudapoa_b200_batch> h(new cudapoa_b200_batch());
-        h->impl = poa::create_batch(device_id, static_cast<cudaStream_t>(stream), max_mem, output_mask,
-                                    from_c(*batch_size), gap_score, mismatch_score, match_score,
-                                    cuda_banded_alignment != 0);
+#ifdef CUDAPOA_B200_NATIVE
+        if (cuda_banded_alignment == 2) // extension: BandMode::adaptive_band
+            h->impl = poa::create_batch(device_id, static_cast<cudaStream_t>(stream), max_mem, output_mask,
+                                        from_c(*batch_size), gap_score, mismatch_score, match_score,
+                                        poa::BandMode::adaptive_band);
+        else
+#else
+        if (cuda_banded_alignment == 2)
+            throw std::invalid_argument("adaptive banding is not part of this cudapoa build");
+#endif
+            h->impl = poa::create_batch(device_id, static_cast<cudaStream_t>(stream), max_mem, output_mask,
+                                        from_c(*batch_size), gap_score, mismatch_score, match_score,
+                                        cuda_banded_alignment != 0);
         handle  = h.release();
         return 0;
     });

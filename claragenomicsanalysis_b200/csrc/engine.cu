@@ -54,6 +54,7 @@ struct MemoryPlan
     bool size32  = false;
     int32_t M    = 0; // node capacity
     int32_t G    = 0; // score matrix rows
+    int32_t band_cells = 0; // widest band a score row must hold (adaptive mode: kAdaptiveBandFactor x the band)
     ArenaLayout layout{};
     int64_t input_per_poa  = 0;
     int64_t output_per_poa = 0;
@@ -61,9 +62,11 @@ struct MemoryPlan
     int64_t score_per_poa  = 0; // banded: exact; full: for the widest allowed read
 };
 
-MemoryPlan make_plan(const BatchSize& b, bool banded, bool msa, int32_t gap, int32_t mismatch, int32_t match)
+MemoryPlan make_plan(const BatchSize& b, bool banded, bool msa, int32_t gap, int32_t mismatch, int32_t match,
+                     bool adaptive = false)
 {
     MemoryPlan p;
+    p.band_cells = b.alignment_band_width * ((banded && adaptive) ? kAdaptiveBandFactor : 1);
     p.score32 = use_32bit_score(b, gap, mismatch, match);
     p.size32  = p.score32 && use_32bit_size(b, banded);
     p.M       = banded ? b.max_nodes_per_window_banded : b.max_nodes_per_window;
@@ -77,7 +80,7 @@ MemoryPlan make_plan(const BatchSize& b, bool banded, bool msa, int32_t gap, int
                        (msa ? static_cast<int64_t>(S) * b.max_consensus_size
                             : static_cast<int64_t>(b.max_consensus_size) * 3);
     p.fixed_per_poa = p.layout.stride + align_up64(p.input_per_poa, 16) + align_up64(p.output_per_poa, 16) + 64;
-    const int64_t width = banded ? b.alignment_band_width + kBandRowPad : b.max_matrix_sequence_dimension + 8;
+    const int64_t width = banded ? p.band_cells + kBandRowPad : b.max_matrix_sequence_dimension + 8;
     p.score_per_poa     = width * static_cast<int64_t>(p.G) * (p.score32 ? 4 : 2);
     return p;
 }
@@ -98,7 +101,7 @@ class B200Batch : public Batch, public EngineStatsSource
 {
 public:
     B200Batch(int32_t device_id, cudaStream_t stream, size_t max_mem, int8_t output_mask, const BatchSize& batch_size,
-              int32_t gap, int32_t mismatch, int32_t match, bool banded)
+              int32_t gap, int32_t mismatch, int32_t match, bool banded, bool adaptive = false)
         : max_sequences_per_poa_(throw_on_negative(batch_size.max_sequences_per_poa,
                                                    "Maximum sequences per POA has to be non-negative"))
         , device_id_(throw_on_negative(device_id, "Device ID has to be non-negative"))
@@ -109,9 +112,10 @@ public:
         , mismatch_(mismatch)
         , match_(match)
         , banded_(banded)
+        , adaptive_(banded && adaptive)
         , msa_((output_mask & OutputType::msa) != 0)
     {
-        plan_ = make_plan(batch_size_, banded_, msa_, gap_, mismatch_, match_);
+        plan_ = make_plan(batch_size_, banded_, msa_, gap_, mismatch_, match_, adaptive_);
         // allocate_block.hpp:66-76: refuse budgets that cannot hold a single POA
         const size_t minimum = static_cast<size_t>(plan_.fixed_per_poa);
         if (max_mem < minimum + static_cast<size_t>(plan_.score_per_poa))
@@ -185,6 +189,7 @@ private:
     BatchSize batch_size_;
     int32_t gap_, mismatch_, match_;
     bool banded_;
+    bool adaptive_; // static band first, widened on demand (BandMode::adaptive_band)
     bool msa_;
     MemoryPlan plan_;
     int32_t max_poas_ = 0;
@@ -318,7 +323,7 @@ void B200Batch::allocate(size_t max_mem)
 // reserve_buf, cudapoa_batch.cuh:542-564
 bool B200Batch::reserve_scores(int32_t max_seq_length)
 {
-    const int64_t width = banded_ ? batch_size_.alignment_band_width + kBandRowPad
+    const int64_t width = banded_ ? plan_.band_cells + kBandRowPad
                                   : cudautils::align<int32_t, 4>(max_seq_length + 1 + 4);
     const size_t bytes  = static_cast<size_t>(width) * static_cast<size_t>(plan_.G) * (plan_.score32 ? 4 : 2);
     if (bytes > avail_score_mem_)
@@ -459,7 +464,8 @@ void B200Batch::launch()
     P.arena               = arena_d_;
     P.layout              = plan_.layout;
     P.scores              = scores_d_;
-    P.banded_score_stride = static_cast<int64_t>(batch_size_.alignment_band_width + kBandRowPad) * plan_.G;
+    P.banded_score_stride = static_cast<int64_t>(plan_.band_cells + kBandRowPad) * plan_.G;
+    P.adaptive_max_band   = adaptive_ ? plan_.band_cells : 0;
     P.status              = status_d_;
     P.node_count          = node_count_d_;
     P.consensus           = consensus_d_;
@@ -536,15 +542,17 @@ void B200Batch::sync_and_collect()
         GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, ev_start_, ev_stop_));
         stats_.kernel_ms       = ms / static_cast<float>(timed_iters_);
         stats_.graph_kernel_ms = stats_.kernel_ms;
-        int64_t rows = 0, exact = 0, cells = 0;
+        int64_t rows = 0, exact = 0, cells = 0, widened = 0;
         for (size_t i = 0; i < n; i++)
         {
             rows += stat_rows_h_[i];
-            exact += stat_exact_h_[i];
+            exact += stat_exact_h_[i] & 0xffffu;
+            widened += stat_exact_h_[i] >> 16;
             cells += static_cast<int64_t>(stat_cells_h_[i]);
         }
         stats_.graph_rows = rows;
         stats_.exact_path = exact;
+        stats_.widened    = widened;
         stats_.dp_cells   = cells; // sum of N_s * Wc
         timed_          = true;
     }
@@ -703,6 +711,17 @@ std::unique_ptr<Batch> create_batch(int32_t device_id, cudaStream_t stream, size
 {
     return std::unique_ptr<Batch>(new B200Batch(device_id, stream, max_mem, output_mask, batch_size, gap_score,
                                                 mismatch_score, match_score, cuda_banded_alignment));
+}
+
+// Extension (BandMode as in later GenomeWorks releases): adaptive_band aligns with the static band first and repeats
+// the alignment with a doubled band while the path found runs along a band edge (poa_window.cuh).
+std::unique_ptr<Batch> create_batch(int32_t device_id, cudaStream_t stream, size_t max_mem, int8_t output_mask,
+                                    const BatchSize& batch_size, int16_t gap_score, int16_t mismatch_score,
+                                    int16_t match_score, BandMode band_mode)
+{
+    return std::unique_ptr<Batch>(new B200Batch(device_id, stream, max_mem, output_mask, batch_size, gap_score,
+                                                mismatch_score, match_score, band_mode != BandMode::full_band,
+                                                band_mode == BandMode::adaptive_band));
 }
 
 // cudapoa.cpp:23-29.  The engine has no logger to start; the call stays for source compatibility.

@@ -104,7 +104,8 @@ cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int3
                     cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess)
                     throw std::runtime_error("pipeline: cannot create a stream on device " + std::to_string(w.device));
                 w.batch = poa::create_batch(w.device, w.stream, mem_per_worker, output_mask, size, gap_score,
-                                            mismatch_score, match_score, cuda_banded_alignment != 0);
+                                            mismatch_score, match_score,
+                                            static_cast<poa::BandMode>(std::min(std::max(cuda_banded_alignment, 0), 2)));
                 auto* src  = dynamic_cast<poa::EngineStatsSource*>(w.batch.get());
                 w.capacity = src != nullptr ? src->max_poas() : 0;
                 p->workers.push_back(std::move(w));
@@ -252,6 +253,7 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
                                 local.dp_cells += s.dp_cells;
                                 local.graph_rows += s.graph_rows;
                                 local.exact_path += s.exact_path;
+                                local.widened += s.widened;
                                 local.h2d_bytes += s.h2d_bytes;
                                 local.d2h_bytes += s.d2h_bytes;
                                 local.kernel_ms += s.kernel_ms;
@@ -274,6 +276,7 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
                 p->stats.dp_cells += local.dp_cells;
                 p->stats.graph_rows += local.graph_rows;
                 p->stats.exact_path += local.exact_path;
+                p->stats.widened += local.widened;
                 p->stats.h2d_bytes += local.h2d_bytes;
                 p->stats.d2h_bytes += local.d2h_bytes;
                 p->stats.kernel_ms += local.kernel_ms;

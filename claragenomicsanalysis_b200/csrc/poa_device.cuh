@@ -298,7 +298,7 @@ struct ScoreMatrix
 template <typename ScoreT, typename IdT, bool BANDED>
 __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                                ScoreT* scores, int32_t width, int32_t band, int32_t gap, int32_t mismatch,
-                               int32_t match, int32_t lane)
+                               int32_t match, int32_t lane, int32_t* score_out = nullptr)
 {
     using O = ScoreOps<ScoreT>;
     ScoreMatrix<ScoreT, BANDED> M;
@@ -424,6 +424,7 @@ __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const ui
 
     // sink selection + traceback on lane 0 (cudapoa_nw_banded.cuh:369-480 / cudapoa_nw.cuh:328-459)
     int32_t aligned = 0;
+    int32_t start_score = 0; // score of the cell the traceback starts from
     if (lane == 0)
     {
         int32_t i = 0, j = read_len;
@@ -442,6 +443,7 @@ __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const ui
         }
         int32_t prev_i = 0, prev_j = 0, loops = 0;
         const int32_t limit = read_len + node_count + 2;
+        start_score         = static_cast<int32_t>(M.get(i, j));
         while (!(i == 0 && j == 0) && loops < limit)
         {
             loops++;
@@ -491,6 +493,8 @@ __device__ int32_t align_exact(const Graph<IdT>& g, int32_t node_count, const ui
         if (loops >= limit)
             aligned = -1;
     }
+    if (score_out != nullptr)
+        *score_out = __shfl_sync(kFull, start_score, 0);
     return __shfl_sync(kFull, aligned, 0);
 }
 
@@ -677,6 +681,30 @@ __device__ int32_t add_alignment(const Graph<IdT>& g, int32_t& node_count, const
     }
     node_count = n;
     return kStSuccess;
+}
+
+// Adaptive banding: does the alignment just found (g.aln_node[k] = node paired with read position k, or < 0) come
+// within kAdaptiveBandMargin cells of an edge of the band of width `band` that is not an edge of the matrix?
+// Band placement as in the alignment itself (band_gradient / band_start).  All lanes; uniform result.
+template <typename IdT>
+__device__ bool alignment_touches_band(const Graph<IdT>& g, int32_t node_count, int32_t read_len, int32_t band,
+                                       int32_t lane)
+{
+    const int32_t max_column = read_len + 1;
+    const float gradient     = band_gradient(read_len, node_count);
+    bool touch               = false;
+    for (int32_t k = lane; k < read_len; k += 32)
+    {
+        const int32_t node = g.aln_node[k];
+        if (node < 0)
+            continue;
+        const int32_t row = static_cast<int32_t>(g.pos[node]) + 1;
+        const int32_t bs  = band_start(row, gradient, band, max_column);
+        const int32_t c   = k - bs; // 0-based cell of column k + 1 inside the band
+        if ((bs > 0 && c < kAdaptiveBandMargin) || (bs + band < max_column && c >= band - kAdaptiveBandMargin))
+            touch = true;
+    }
+    return __any_sync(kFull, touch);
 }
 
 // Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88).  Lane 0 only, global memory.

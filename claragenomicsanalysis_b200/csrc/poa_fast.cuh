@@ -200,7 +200,7 @@ template <typename IdT>
 __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
                                        int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
                                        int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
-                                       int32_t lane)
+                                       int32_t lane, int32_t* score_out = nullptr)
 {
     // shared-memory scratch: [ring of recent rows | read, zero padded]
     const int32_t rd_bytes = (read_len + kFastBand + 8 + 15) & ~15;
@@ -509,6 +509,8 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     int32_t i = (best > INT16_MIN) ? best_row : 0, j = read_len;
     if (tilted_score_global(rows, i, j) <= kNegThreshold)
         return kFastNotTaken;
+    if (score_out != nullptr) // alignment score, un-tilted (the start cell is a real score here)
+        *score_out = tilted_score_global(rows, i, j) + gap * read_len;
     int32_t aligned = 0, loops = 0;
     int32_t prev_i = 0, prev_j = 0; // lane 0's copies carry over between tiles, as in the reference's single loop
     const int32_t limit = read_len + node_count + 2;

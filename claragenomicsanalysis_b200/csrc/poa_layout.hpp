@@ -17,6 +17,8 @@ constexpr int32_t kMaxNodeAlignments = 50; // edge_count_exceeded_maximum_graph_
 constexpr int32_t kBandPad           = 8;  // cells right of the band kept at the sentinel (reference layout)
 constexpr int32_t kBandRowPad        = 24; // cells of padding in this engine's banded row stride (three 16-byte blocks)
 constexpr int32_t kWarp              = 32;
+constexpr int32_t kAdaptiveBandFactor = 4; // adaptive banding: the band may double up to this multiple
+constexpr int32_t kAdaptiveBandMargin = 4; // ... while an aligned pair lies within this many cells of a band edge
 
 struct WindowDesc
 {
@@ -81,6 +83,7 @@ struct KernelParams
     int32_t gap, mismatch, match;
     int32_t spoa_accurate;
     int32_t* next_window; // zeroed before the launch; warps take window ids from it
+    int32_t adaptive_max_band; // 0: static band; else the widest band the score rows can hold
     int32_t smem_per_warp; // bytes of shared-memory scratch each warp (= window) owns
 };
 

@@ -74,20 +74,46 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
                 status = kStNodeCountExceeded;
                 break;
             }
-            int32_t aln_len = kFastNotTaken;
+            int32_t aln_len   = kFastNotTaken;
+            int32_t aln_score = 0;
             // The packed path computes exact integer scores whenever it accepts a window, so it also serves batches
             // whose score type is int32 because of their largest window; it only borrows the window's score area.
             if (BANDED)
                 aln_len = align_fast_banded16<IdT>(g, node_count, seq, len, reinterpret_cast<int16_t*>(scores),
-                                                   P.band, P.gap, P.mismatch, P.match, smem, P.smem_per_warp, lane);
+                                                   P.band, P.gap, P.mismatch, P.match, smem, P.smem_per_warp, lane,
+                                                   &aln_score);
             if (aln_len == kFastNotTaken)
             {
                 aln_len = align_exact<ScoreT, IdT, BANDED>(g, node_count, seq, len, scores, width, P.band, P.gap,
-                                                           P.mismatch, P.match, lane);
+                                                           P.mismatch, P.match, lane, &aln_score);
                 exact++;
             }
             rows += static_cast<uint32_t>(node_count);
             cells += static_cast<unsigned long long>(node_count) * static_cast<unsigned long long>(BANDED ? P.band : len);
+            if (BANDED && P.adaptive_max_band > 0)
+            {
+                // Adaptive banding (extension, no counterpart in the reference).  A static band can miss the optimum
+                // in two ways: the path found runs along a band edge, or it stays on the diagonal as a run of
+                // mismatches because the true path left the band.  So the alignment is repeated with the band
+                // doubled when an aligned pair lies within kAdaptiveBandMargin cells of a band edge that is not a
+                // matrix edge, or when the score is below 3/4 of a perfect match; doubling goes on while it raises
+                // the score or the path still hugs an edge.  Repeats use the exact path (its band is a parameter).
+                int32_t band_now = P.band;
+                bool again       = aln_len >= 0 && (4 * aln_score < 3 * P.match * len ||
+                                              alignment_touches_band<IdT>(g, node_count, len, band_now, lane));
+                while (again && band_now < P.adaptive_max_band)
+                {
+                    band_now *= 2;
+                    const int32_t before = aln_score;
+                    __syncwarp();
+                    aln_len = align_exact<ScoreT, IdT, true>(g, node_count, seq, len, scores, band_now + kBandRowPad,
+                                                             band_now, P.gap, P.mismatch, P.match, lane, &aln_score);
+                    exact += 0x10000u; // high half: widened alignments
+                    cells += static_cast<unsigned long long>(node_count) * static_cast<unsigned long long>(band_now);
+                    again = aln_len >= 0 &&
+                            (aln_score > before || alignment_touches_band<IdT>(g, node_count, len, band_now, lane));
+                }
+            }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {
                 status = kStLoopCountExceeded;

@@ -39,6 +39,13 @@ def batch_size(max_sequence_size=1024, max_sequences_per_poa=100, alignment_band
     return out
 
 
+def band_mode_value(cuda_banded_alignment):
+    """False/True as in the reference binding; "adaptive" (or 2) selects this engine's adaptive banding."""
+    if cuda_banded_alignment == "adaptive" or cuda_banded_alignment == 2:
+        return 2
+    return 1 if cuda_banded_alignment else 0
+
+
 class CudaPoaBatch:
     """Python API for CUDA-accelerated partial order alignment (mirror of pygenomeworks' CudaPoaBatch)."""
 
@@ -91,7 +98,7 @@ class CudaPoaBatch:
                 alignment_band_width, max_sequences_per_poa), "BatchSize")
         self.batch_size = bs
         handle = self._lib.create_batch(device_id, stream_ptr, int(max_gpu_mem), self._mask, ctypes.byref(bs),
-                                        gap_score, mismatch_score, match_score, 1 if cuda_banded_alignment else 0)
+                                        gap_score, mismatch_score, match_score, band_mode_value(cuda_banded_alignment))
         if not handle:
             msg = self._lib.error()
             if "negative" in msg or "should" in msg:

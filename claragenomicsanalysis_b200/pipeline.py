@@ -8,6 +8,7 @@ import numpy as np
 
 from . import _cabi
 from ._cabi import OUTPUT_CONSENSUS, OUTPUT_MSA, BatchSizeC, StatsC
+from .cudapoa import band_mode_value
 
 _configured = False
 
@@ -66,7 +67,7 @@ class WindowPipeline:
         devs = np.ascontiguousarray(list(devices), dtype=np.int32)
         h = self._dll.cudapoa_b200_pipeline_create(devs.ctypes.data, int(devs.shape[0]), workers_per_device,
                                                    int(mem_per_worker), self._mask, ctypes.byref(bs), gap_score,
-                                                   mismatch_score, match_score, 1 if cuda_banded_alignment else 0)
+                                                   mismatch_score, match_score, band_mode_value(cuda_banded_alignment))
         if not h:
             raise RuntimeError(self._dll.cudapoa_b200_pipeline_last_error().decode("utf-8", "replace"))
         self._h = ctypes.c_void_p(h)

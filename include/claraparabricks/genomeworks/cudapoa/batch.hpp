@@ -151,6 +151,19 @@ std::unique_ptr<Batch> create_batch(int32_t device_id, cudaStream_t stream, size
                                     const BatchSize& batch_size, int16_t gap_score, int16_t mismatch_score,
                                     int16_t match_score, bool cuda_banded_alignment);
 
+/// Extension of this engine (names follow later GenomeWorks releases): how the score matrix is banded.
+enum class BandMode : int8_t
+{
+    full_band     = 0, ///< cuda_banded_alignment == false
+    static_band   = 1, ///< cuda_banded_alignment == true
+    adaptive_band = 2  ///< static band first; the band doubles (up to 4x) while the alignment runs along a band edge
+};
+
+/// Same as create_batch above with the band mode spelled out; adaptive_band has no counterpart in the reference.
+std::unique_ptr<Batch> create_batch(int32_t device_id, cudaStream_t stream, size_t max_mem, int8_t output_mask,
+                                    const BatchSize& batch_size, int16_t gap_score, int16_t mismatch_score,
+                                    int16_t match_score, BandMode band_mode);
+
 } // namespace cudapoa
 } // namespace genomeworks
 } // namespace claraparabricks

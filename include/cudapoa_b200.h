@@ -101,6 +101,7 @@ typedef struct cudapoa_b200_stats
     int64_t d2h_bytes;      /* bytes copied device->host by the last get_*                   */
     double kernel_ms;       /* CUDA-event time of the device work of generate_poa            */
     double graph_kernel_ms; /* the POA graph-build kernel alone                              */
+    int64_t widened;        /* adaptive banding: alignments repeated with a wider band       */
 } cudapoa_b200_stats;
 
 const char* CUDAPOA_CABI(last_error)(void);
@@ -114,7 +115,9 @@ int32_t CUDAPOA_CABI(batch_size_explicit)(cudapoa_b200_batch_size* out, int32_t 
                                           int32_t max_nodes_per_w, int32_t max_nodes_per_w_banded, int32_t band_width,
                                           int32_t max_seq_per_poa);
 
-/* stream is a cudaStream_t passed as void* (NULL = default stream); the caller keeps ownership. */
+/* stream is a cudaStream_t passed as void* (NULL = default stream); the caller keeps ownership.
+ * cuda_banded_alignment: 0 / 1 as the reference's bool; 2 (native engine only, an extension) = adaptive banding:
+ * static band first, repeated with the band doubled (up to 4x) while the alignment runs along a band edge. */
 cudapoa_b200_batch* CUDAPOA_CABI(create_batch)(int32_t device_id, void* stream, size_t max_mem, int8_t output_mask,
                                                const cudapoa_b200_batch_size* batch_size, int16_t gap_score,
                                                int16_t mismatch_score, int16_t match_score,

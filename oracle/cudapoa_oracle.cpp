@@ -25,6 +25,8 @@ namespace
 constexpr int32_t kMaxEdges      = 50; // CUDAPOA_MAX_NODE_EDGES, cudapoa_structs.cuh:18
 constexpr int32_t kMaxAlignments = 50; // CUDAPOA_MAX_NODE_ALIGNMENTS, cudapoa_structs.cuh:21
 constexpr int32_t kCellsPerLane  = 4;  // CELLS_PER_THREAD, cudapoa_structs.cuh:25
+constexpr int32_t kAdaptiveBandFactor = 4; // adaptive banding (engine extension): the band doubles up to 4x ...
+constexpr int32_t kAdaptiveBandMargin = 4; // ... while an aligned pair is this close to a band edge
 constexpr int32_t kRightPad      = 8;  // CUDAPOA_BANDED_MATRIX_RIGHT_PADDING, cudapoa_structs.cuh:27
 
 // cudapoa::StatusType values (cudapoa.hpp:26-38)
@@ -159,7 +161,7 @@ template <typename ScoreT, typename IdT>
 int32_t nw_banded(const uint8_t* nodes, const IdT* graph, const IdT* node_id_to_pos, int32_t graph_count,
                   const uint16_t* in_cnt, const IdT* in_edges, const uint16_t* out_cnt, const uint8_t* read,
                   int32_t read_length, ScoreT* scores, IdT* aln_graph, IdT* aln_read, int32_t band_width,
-                  int32_t gap, int32_t mismatch, int32_t match, float gradient)
+                  int32_t gap, int32_t mismatch, int32_t match, float gradient, int32_t* score_out = nullptr)
 {
     const ScoreT type_min  = std::numeric_limits<ScoreT>::min();
     const ScoreT min_score = banded_min_score<ScoreT>(gap, mismatch, match);
@@ -275,6 +277,9 @@ int32_t nw_banded(const uint8_t* nodes, const IdT* graph, const IdT* node_id_to_
             }
         }
     }
+
+    if (score_out != nullptr) // score of the cell the traceback starts from (adaptive banding, engine extension)
+        *score_out = static_cast<int32_t>(M.get(i, j, min_score));
 
     // traceback, :386-480
     int32_t aligned = 0;
@@ -907,6 +912,7 @@ struct RunResult
     int64_t dp_cells    = 0;
     int64_t graph_rows  = 0;
     int64_t rcp_misses  = 0;
+    int64_t widened     = 0; // adaptive banding: alignments repeated with a wider band
 };
 
 // cudapoa_limits.hpp:28-53
@@ -960,7 +966,8 @@ void run_window(const oracle_params& P, const std::vector<const uint8_t*>& reads
     int32_t full_width = 0;
     for (int32_t l : lens)
         full_width = std::max(full_width, align_up(l + 1 + kCellsPerLane, 4)); // cudapoa_batch.cuh:498-503
-    const int32_t width = P.banded ? P.alignment_band_width + kRightPad : full_width;
+    const int32_t band_cap = P.alignment_band_width * ((P.banded && P.adaptive_band) ? kAdaptiveBandFactor : 1);
+    const int32_t width    = P.banded ? band_cap + kRightPad : full_width;
     // a few hundred spare rows: the reference's column-0 quirk writes at row*W + band_start(row)
     std::vector<ScoreT> scores((static_cast<size_t>(max_g) + 64) * static_cast<size_t>(std::max(width, 1)) +
                                static_cast<size_t>(P.max_sequence_size) + 4096);
@@ -1012,14 +1019,52 @@ void run_window(const oracle_params& P, const std::vector<const uint8_t*>& reads
             break;
         }
         int32_t aln_len;
+        int32_t aln_score = 0;
         if (P.banded)
         {
             float gradient = banded_gradient(lens[s], node_count, rcp, &totals.rcp_misses);
             aln_len = nw_banded<ScoreT, IdT>(nodes.data(), sorted.data(), pos.data(), node_count, in_cnt.data(),
                                              in_edges.data(), out_cnt.data(), reads[s], lens[s], scores.data(),
                                              aln_graph.data(), aln_read.data(), P.alignment_band_width, P.gap_score,
-                                             P.mismatch_score, P.match_score, gradient);
+                                             P.mismatch_score, P.match_score, gradient, &aln_score);
             totals.dp_cells += static_cast<int64_t>(node_count) * P.alignment_band_width;
+            if (P.adaptive_band)
+            {
+                // engine extension (poa_window.cuh): repeat with the band doubled when the path hugs a band edge or
+                // the score is below 3/4 of a perfect match, and go on while that raises the score or the path still
+                // hugs an edge
+                int32_t band_now = P.alignment_band_width;
+                auto touches     = [&]() {
+                    const int32_t max_column = lens[s] + 1;
+                    for (int32_t a = 0; a < aln_len; a++)
+                    {
+                        const int32_t node = aln_graph[static_cast<size_t>(a)], k = aln_read[static_cast<size_t>(a)];
+                        if (node < 0 || k < 0)
+                            continue;
+                        const int32_t row = pos[static_cast<size_t>(node)] + 1;
+                        const int32_t bs  = band_start_for_row(row, gradient, band_now, max_column);
+                        const int32_t c   = k - bs;
+                        if ((bs > 0 && c < kAdaptiveBandMargin) ||
+                            (bs + band_now < max_column && c >= band_now - kAdaptiveBandMargin))
+                            return true;
+                    }
+                    return false;
+                };
+                bool again = aln_len >= 0 && (4 * aln_score < 3 * P.match_score * lens[s] || touches());
+                while (again && band_now < band_cap)
+                {
+                    band_now *= 2;
+                    const int32_t before = aln_score;
+                    aln_len = nw_banded<ScoreT, IdT>(nodes.data(), sorted.data(), pos.data(), node_count,
+                                                     in_cnt.data(), in_edges.data(), out_cnt.data(), reads[s], lens[s],
+                                                     scores.data(), aln_graph.data(), aln_read.data(), band_now,
+                                                     P.gap_score, P.mismatch_score, P.match_score, gradient,
+                                                     &aln_score);
+                    totals.dp_cells += static_cast<int64_t>(node_count) * band_now;
+                    totals.widened++;
+                    again = aln_len >= 0 && (aln_score > before || touches());
+                }
+            }
         }
         else
         {
@@ -1248,6 +1293,11 @@ int64_t oracle_graph_rows(void* h)
 {
     return static_cast<RunResult*>(h)->graph_rows;
 }
+int64_t oracle_widened(void* h)
+{
+    return static_cast<RunResult*>(h)->widened;
+}
+
 int64_t oracle_rcp_misses(void* h)
 {
     return static_cast<RunResult*>(h)->rcp_misses;

@@ -61,3 +61,30 @@ def case_windows(name):
             wins.append(reads)
         ws = WindowSet.from_lists(wins)
     return ws
+
+
+def structural_windows(n, start=11000, template_length=800, n_reads=12, block=(80, 140), every=3):
+    """Windows in which every `every`-th read lost a block of `block` bases a fifth of the way in and gained a random
+    block of the same size a fifth before its end: between the two the alignment runs `block` cells off the diagonal,
+    more than a 128-wide static band follows.  Used by the adaptive-banding tests (no reference counterpart; the
+    yardstick is the full alignment)."""
+    import numpy as np
+
+    from claragenomicsanalysis_b200.windows import WindowSet
+
+    base = generate_windows(n, start_index=start, template_length=template_length, n_reads=n_reads)
+    rng = np.random.default_rng(start)
+    acgt = "ACGT"
+    wins = []
+    for i in range(len(base)):
+        reads = base.window(i)
+        for r in range(1, len(reads)):
+            if r % every == 0:
+                rd = reads[r]
+                d = int(rng.integers(block[0], block[1] + 1))
+                a = len(rd) // 5
+                b = max(a + d + 1, 4 * len(rd) // 5)
+                ins = "".join(acgt[int(x)] for x in rng.integers(0, 4, d))
+                reads[r] = rd[:a] + rd[a + d:b] + ins + rd[b:]
+        wins.append(reads)
+    return WindowSet.from_lists(wins)

@@ -20,7 +20,8 @@ class OracleParams(ctypes.Structure):
         "max_matrix_graph_dimension", "max_matrix_graph_dimension_banded", "max_matrix_sequence_dimension",
         "alignment_band_width", "max_sequences_per_poa", "gap_score", "mismatch_score", "match_score", "banded",
         "output_mask", "spoa_accurate", "stale_fill")] + [("rcp_table", ctypes.c_void_p),
-                                                           ("rcp_table_len", ctypes.c_int32)]
+                                                           ("rcp_table_len", ctypes.c_int32),
+                                                           ("adaptive_band", ctypes.c_int32)]
 
 
 def build_oracle():
@@ -68,7 +69,7 @@ def oracle():
 
 
 def make_params(max_seq=1024, max_reads=100, band=256, banded=True, output="consensus", gap=-8, mismatch=-6,
-                match=8, spoa_accurate=False, stale_fill=0, use_rcp=True, batch_size=None):
+                match=8, spoa_accurate=False, stale_fill=0, use_rcp=True, batch_size=None, adaptive=False):
     p = OracleParams()
     oracle().oracle_default_params(ctypes.byref(p), max_seq, max_reads, band)
     if batch_size is not None:  # a BatchSizeC or dict with the nine BatchSize fields
@@ -80,6 +81,7 @@ def make_params(max_seq=1024, max_reads=100, band=256, banded=True, output="cons
     p.output_mask = {"consensus": 1, "msa": 2, "both": 3}[output]
     p.spoa_accurate = 1 if spoa_accurate else 0
     p.stale_fill = stale_fill
+    p.adaptive_band = 1 if adaptive else 0
     t = rcp_table() if use_rcp else None
     if t is not None:
         p.rcp_table = t.ctypes.data
@@ -122,6 +124,10 @@ class OracleRun:
     @property
     def rcp_misses(self):
         return self._lib.oracle_rcp_misses(self._h)
+
+    @property
+    def widened(self):
+        return self._lib.oracle_widened(self._h)
 
     def status(self, w):
         return self._lib.oracle_status(self._h, w)
