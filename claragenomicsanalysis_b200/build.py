@@ -8,6 +8,8 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libcudapoa_b200.so")
+BIN_DIR = os.path.join(HERE, "bin")
+CLI = os.path.join(BIN_DIR, "cudapoa")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 SOURCES = ["engine.cu", "c_api.cpp", "pipeline.cpp"]
@@ -27,7 +29,7 @@ def _inputs():
 
 
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(CLI):
         return True
     t = os.path.getmtime(LIB)
     return any(os.path.getmtime(f) > t for f in _inputs())
@@ -54,6 +56,15 @@ def build(force=False, verbose=False):
     if res.returncode != 0:
         sys.stderr.write(res.stdout)
         raise RuntimeError("link failed")
+    # the command line tool (cudapoa/src/main.cpp of the reference), linked against the library next to it
+    os.makedirs(BIN_DIR, exist_ok=True)
+    cmd = [NVCC, "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), os.path.join(CSRC, "cli_main.cpp"),
+           "-o", CLI, "-L" + LIB_DIR, "-lcudapoa_b200", "-Xlinker", "-rpath=$ORIGIN/../lib"]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    log.append(res.stdout)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError("building the cudapoa command line tool failed")
     with open(os.path.join(LIB_DIR, "build.log"), "w") as f:
         f.write("\n".join(log))
     if verbose:
