@@ -133,3 +133,24 @@ class WindowPipeline:
 
     def digest(self, first=0, count=None):
         return int(self._dll.cudapoa_b200_pipeline_digest(self._h, first, self.n_windows if count is None else count))
+
+
+def assembly(consensus, coverage):
+    """Concatenate window consensuses into one sequence, trimming each window at both ends while the per-base
+    coverage is below the window's average coverage -- the reference's end-to-end check
+    (cudapoa/benchmarks/multi_batch.hpp:176-207; integer average, a window whose trimmed range is empty or a single
+    base contributes nothing, exactly as there)."""
+    genome = []
+    for cons, cov in zip(consensus, coverage):
+        n = len(cov)
+        if n == 0:
+            continue
+        average = int(sum(int(c) for c in cov)) // n
+        begin, end = 0, len(cons) - 1
+        while begin < n and cov[begin] < average:
+            begin += 1
+        while end >= 0 and cov[end] < average:
+            end -= 1
+        if begin < end:
+            genome.append(cons[begin:end + 1])
+    return "".join(genome)
