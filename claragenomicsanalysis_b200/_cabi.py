@@ -60,6 +60,7 @@ class StatsC(ctypes.Structure):
         ("kernel_ms", ctypes.c_double),
         ("graph_kernel_ms", ctypes.c_double),
         ("widened", ctypes.c_int64),
+        ("kernel_launches", ctypes.c_int64),
     ]
 
 

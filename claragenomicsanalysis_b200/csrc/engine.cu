@@ -5,6 +5,7 @@
 #include "engine_stats.hpp"
 #include "poa_layout.hpp"
 #include "poa_window.cuh"
+#include "poa_phases.cuh"
 
 #include <claraparabricks/genomeworks/cudapoa/batch.hpp>
 #include <claraparabricks/genomeworks/cudapoa/cudapoa.hpp>
@@ -176,6 +177,7 @@ private:
     StatusType add_sequence(const Entry& e);
     void ensure_weights();
     void launch();
+    bool launch_split(KernelParams& P);
     void sync_and_collect();
     void push_status(std::vector<StatusType>& out, int32_t poa) const
     {
@@ -207,6 +209,8 @@ private:
     uint32_t* stat_exact_d_ = nullptr;
     unsigned long long* stat_cells_d_ = nullptr;
     int32_t* next_window_d_           = nullptr; // windows are handed to warps through this counter
+    int32_t* phase_counters_d_        = nullptr; // phase-split schedule: one such counter per launch
+    PhaseState* phase_d_              = nullptr; // phase-split schedule: per-window state between launches
     int32_t sm_count_                 = 0;
     uint8_t* consensus_d_  = nullptr;
     uint16_t* coverage_d_  = nullptr;
@@ -238,6 +242,7 @@ private:
     size_t avail_score_mem_ = 0;
     bool has_weights_       = false;
     bool launched_          = false;
+    int64_t kernel_launches_ = 0; // kernels enqueued by the last generate_poa / relaunch
     bool timed_             = false;
     int32_t timed_iters_    = 1;
 
@@ -265,6 +270,7 @@ void B200Batch::allocate(size_t max_mem)
         a(n * 4);                     // stat_rows
         a(n * 4);                     // stat_exact
         a((n + 1) * 8);               // stat_cells + the launch's window counter
+        a(n * static_cast<int64_t>(sizeof(PhaseState)) + kPhaseCounters * 4); // phase-split schedule
         a(msa_ ? 0 : n * C);          // consensus
         a(msa_ ? 0 : n * C * 2);      // coverage
         a(msa_ ? n * S * C : 0);      // msa
@@ -288,6 +294,8 @@ void B200Batch::allocate(size_t max_mem)
     GW_CU_CHECK_ERR(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_id_));
     stat_cells_d_   = carve<unsigned long long>(cur, n + 1);
     next_window_d_  = reinterpret_cast<int32_t*>(stat_cells_d_ + n);
+    phase_counters_d_ = carve<int32_t>(cur, kPhaseCounters);
+    phase_d_          = reinterpret_cast<PhaseState*>(carve<uint8_t>(cur, n * static_cast<int64_t>(sizeof(PhaseState))));
     consensus_d_    = carve<uint8_t>(cur, msa_ ? 0 : n * C);
     coverage_d_     = carve<uint16_t>(cur, msa_ ? 0 : n * C);
     msa_d_          = carve<uint8_t>(cur, msa_ ? n * S * C : 0);
@@ -453,6 +461,104 @@ static void launch_typed(const KernelParams& P, bool banded, bool msa, int32_t s
     }
 }
 
+// One launch of a phase kernel: persistent warps, at most one resident wave of CTAs.
+template <typename Kernel>
+static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per_block, int32_t sm_count,
+                         cudaStream_t stream)
+{
+    const dim3 block(warps_per_block * 32);
+    const size_t smem = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
+    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
+    int per_sm           = 1;
+    GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
+    const dim3 grid(std::max(1, std::min(needed, sm_count * std::max(per_sm, 1))));
+    kernel<<<grid, block, smem, stream>>>(P);
+}
+
+// Nodes a graph may have for the sort (10 bytes per node) and the consensus (staging area + 6 bytes per node) to run
+// out of `smem` bytes of scratch.
+static int32_t graph_scratch_nodes(int32_t smem)
+{
+    return std::min((smem / kKahnBytesPerNode) & ~7, ((smem - kConsStageBytes) / 6) & ~7);
+}
+
+template <typename ScoreT, typename IdT, bool MSA>
+static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_smem, int32_t graph_smem,
+                                  int32_t graph_smem_large, int32_t* counters, int32_t sm_count, cudaStream_t stream)
+{
+    int32_t launches = 0;
+    const bool two   = graph_smem_large > graph_smem;
+    P.class_cap      = two ? graph_scratch_nodes(graph_smem) : INT32_MAX - kClassMargin;
+    for (int32_t s = 1; s <= steps; s++)
+    {
+        P.step          = s;
+        P.next_window   = counters + 3 * (s - 1);
+        P.smem_per_warp = fill_smem;
+        launch_phase(poa_fill_kernel<ScoreT, IdT, MSA>, P, kFillWarpsPerBlock, sm_count, stream);
+        P.next_window   = counters + 3 * (s - 1) + 1;
+        P.smem_per_warp = graph_smem;
+        P.phase_class   = 0;
+        launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+        launches += 2;
+        if (two)
+        {
+            P.next_window   = counters + 3 * (s - 1) + 2;
+            P.smem_per_warp = graph_smem_large;
+            P.phase_class   = 1;
+            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+            launches++;
+        }
+    }
+    return launches;
+}
+
+// Phase-split schedule (poa_phases.cuh) for banded batches: two launches per read instead of one launch per batch.
+// Returns false when the batch has to take the single launch (full alignment, adaptive banding, very deep windows,
+// or CUDAPOA_B200_SCHEDULE=fused).
+bool B200Batch::launch_split(KernelParams& P)
+{
+    static const bool fused_by_env = [] {
+        const char* env = std::getenv("CUDAPOA_B200_SCHEDULE");
+        return env != nullptr && std::strcmp(env, "fused") == 0;
+    }();
+    if (!banded_ || adaptive_ || fused_by_env || plan_.size32)
+        return false;
+    int32_t max_reads = 1;
+    for (int32_t i = 0; i < poa_count_; i++)
+        max_reads = std::max(max_reads, windows_h_[i].n_reads);
+    const int32_t steps = std::max(max_reads - 1, 1);
+    if (3 * steps > kPhaseCounters)
+        return false;
+    // shared memory per window: the fill needs the row ring and the padded read, the graph phases the traceback
+    // tile and the read (the topological sort and the consensus reuse that scratch)
+    const int32_t L          = std::max(batch_size_.max_sequence_size, 1);
+    const int32_t fill_smem  = (kRingBytes + ((L + kFastBand + 8 + 15) & ~15) + 255) & ~255;
+    const int32_t graph_smem = (kTileBytes + ((L + 15) & ~15) + 255) & ~255;
+    const int32_t graph_smem_large = std::max(graph_smem, kSmemPerWarp);
+    if (4 * std::max(fill_smem, graph_smem_large) > 200 * 1024)
+        return false;
+    P.phase = phase_d_;
+    int32_t launches = 0;
+    GW_CU_CHECK_ERR(cudaMemsetAsync(phase_counters_d_, 0, sizeof(int32_t) * kPhaseCounters, stream_));
+    if (!plan_.score32)
+    {
+        if (msa_)
+            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+        else
+            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+    }
+    else
+    {
+        if (msa_)
+            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+        else
+            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+    }
+    kernel_launches_ += launches;
+    return true;
+}
+
 void B200Batch::launch()
 {
     KernelParams P{};
@@ -489,7 +595,13 @@ void B200Batch::launch()
     const char* env = std::getenv("CUDAPOA_B200_SPOA_ACCURATE");
     P.spoa_accurate = (env != nullptr && env[0] == '1') ? 1 : 0;
 #endif
+    if (launch_split(P))
+    {
+        GW_CU_CHECK_ERR(cudaPeekAtLastError());
+        return;
+    }
     GW_CU_CHECK_ERR(cudaMemsetAsync(next_window_d_, 0, sizeof(int32_t), stream_));
+    kernel_launches_ += 1;
     if (!plan_.score32)
         launch_typed<int16_t, int16_t>(P, banded_, msa_, sm_count_, stream_);
     else if (!plan_.size32)
@@ -519,6 +631,7 @@ void B200Batch::generate_poa()
     GW_CU_CHECK_ERR(cudaMemcpyAsync(windows_d_, windows_h_, sizeof(WindowDesc) * poa_count_, cudaMemcpyHostToDevice, stream_));
     stats_.h2d_bytes += static_cast<int64_t>(sizeof(int32_t)) * num_reads_ + static_cast<int64_t>(sizeof(WindowDesc)) * poa_count_;
     GW_CU_CHECK_ERR(cudaEventRecord(ev_start_, stream_));
+    kernel_launches_ = 0;
     launch();
     GW_CU_CHECK_ERR(cudaEventRecord(ev_stop_, stream_));
     launched_    = true;
@@ -553,6 +666,7 @@ void B200Batch::sync_and_collect()
         stats_.graph_rows = rows;
         stats_.exact_path = exact;
         stats_.widened    = widened;
+        stats_.kernel_launches = kernel_launches_;
         stats_.dp_cells   = cells; // sum of N_s * Wc
         timed_          = true;
     }
@@ -564,6 +678,7 @@ double B200Batch::relaunch(int32_t iterations)
     if (!launched_ || poa_count_ == 0 || iterations <= 0)
         return -1.0;
     GW_CU_CHECK_ERR(cudaEventRecord(ev_start_, stream_));
+    kernel_launches_ = 0;
     for (int32_t i = 0; i < iterations; i++)
         launch();
     GW_CU_CHECK_ERR(cudaEventRecord(ev_stop_, stream_));

@@ -254,6 +254,7 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
                                 local.graph_rows += s.graph_rows;
                                 local.exact_path += s.exact_path;
                                 local.widened += s.widened;
+                                local.kernel_launches += s.kernel_launches;
                                 local.h2d_bytes += s.h2d_bytes;
                                 local.d2h_bytes += s.d2h_bytes;
                                 local.kernel_ms += s.kernel_ms;
@@ -277,6 +278,7 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
                 p->stats.graph_rows += local.graph_rows;
                 p->stats.exact_path += local.exact_path;
                 p->stats.widened += local.widened;
+                p->stats.kernel_launches += local.kernel_launches;
                 p->stats.h2d_bytes += local.h2d_bytes;
                 p->stats.d2h_bytes += local.d2h_bytes;
                 p->stats.kernel_ms += local.kernel_ms;

@@ -196,11 +196,20 @@ __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& r
     __syncwarp();
 }
 
+// Shared memory the packed fill needs for a read of this length: the ring plus the zero-padded read.
+__device__ __forceinline__ int32_t fast_fill_smem_bytes(int32_t read_len)
+{
+    return kRingBytes + ((read_len + kFastBand + 8 + 15) & ~15);
+}
+
+// First half of the packed alignment: row descriptors, the fill (every row streamed to the score matrix) and the
+// sink selection.  Returns kFastNotTaken, or 0 with the row the traceback starts from in start_row (uniform over
+// the warp).  The read stays staged at smem + kRingBytes.
 template <typename IdT>
-__device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
-                                       int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
-                                       int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
-                                       int32_t lane, int32_t* score_out = nullptr)
+__device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                             int16_t* scores, int32_t band, int32_t gap, int32_t mismatch, int32_t match,
+                             uint32_t smem, int32_t smem_bytes, int32_t lane, int32_t& start_row,
+                             int32_t* score_out = nullptr)
 {
     // shared-memory scratch: [ring of recent rows | read, zero padded]
     const int32_t rd_bytes = (read_len + kFastBand + 8 + 15) & ~15;
@@ -472,8 +481,6 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
 
     // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len.
     // All candidates share the column, so tilted scores compare like the scores themselves.
-    const uint32_t tile      = ring;
-    const uint32_t tile_desc = ring + kTileRows * kTileRowBytes;
     int32_t best = INT16_MIN, best_row = 0;
     for (int32_t r = 1 + lane; r <= node_count; r += 32)
     {
@@ -500,17 +507,46 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
         }
     }
 
-    // traceback (cudapoa_nw_banded.cuh:386-480): lane 0 walks, the warp reloads the tile when the walk leaves it.
-    // The walk compares tilted scores: with T = H - gap * j, "H[i][j] == H[p][j-1] + cost" reads
-    // "T[i][j] == T[p][j-1] + cost - gap", the vertical move "T[i][j] == T[p][j] + gap", the horizontal move
-    // "T[i][j] == T[i][j-1]".  This is the reference's decision as long as the cell the walk stands on is a real
-    // score (see tilted_score_global); it is from the first cell on, or the exact path takes over.
-    // g.aln_node[] first receives ROW indices (0: inserted base); they become node ids in a parallel pass below.
-    int32_t i = (best > INT16_MIN) ? best_row : 0, j = read_len;
-    if (tilted_score_global(rows, i, j) <= kNegThreshold)
+    const int32_t i0 = (best > INT16_MIN) ? best_row : 0;
+    if (tilted_score_global(rows, i0, read_len) <= kNegThreshold)
         return kFastNotTaken;
     if (score_out != nullptr) // alignment score, un-tilted (the start cell is a real score here)
-        *score_out = tilted_score_global(rows, i, j) + gap * read_len;
+        *score_out = tilted_score_global(rows, i0, read_len) + gap * read_len;
+    start_row = i0;
+    return 0;
+}
+
+// Second half: traceback (cudapoa_nw_banded.cuh:386-480) from (start_row, read_len): lane 0 walks, the warp reloads
+// the tile when the walk leaves it.  `tile` is kTileRows * (kTileRowBytes + 8) bytes of shared memory, `rd` the read
+// in shared memory (staged here from `read` unless the caller's fill left it there: read == nullptr).
+// The walk compares tilted scores: with T = H - gap * j, "H[i][j] == H[p][j-1] + cost" reads
+// "T[i][j] == T[p][j-1] + cost - gap", the vertical move "T[i][j] == T[p][j] + gap", the horizontal move
+// "T[i][j] == T[i][j-1]".  This is the reference's decision as long as the cell the walk stands on is a real
+// score (see tilted_score_global); it is from the first cell on, or the exact path took over.
+// g.aln_node[] first receives ROW indices (0: inserted base); they become node ids in a parallel pass below.
+// Returns the alignment length, or -1 when the walk exceeds the reference's step limit.
+template <typename IdT>
+__device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                                  int16_t* scores, int32_t gap, int32_t mismatch, int32_t match, uint32_t tile,
+                                  uint32_t rd, int32_t start_row, int32_t lane)
+{
+    uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
+    RowDesc desc;
+    desc.d0 = g.rowinfo;
+    desc.d1 = desc.d0 + (g.M + 40);
+    desc.d2 = desc.d1 + (g.M + 40);
+    const int32_t max_column = read_len + 1;
+    const float gradient     = band_gradient(read_len, node_count);
+    const int32_t pd_m       = match - gap;
+    const int32_t pd_x       = mismatch - gap;
+    const uint32_t tile_desc = tile + kTileRows * kTileRowBytes;
+    if (read != nullptr)
+    {
+        for (int32_t k = lane; k < read_len; k += 32)
+            sts_u8(rd + k, read[k]);
+        __syncwarp();
+    }
+    int32_t i = start_row, j = read_len;
     int32_t aligned = 0, loops = 0;
     int32_t prev_i = 0, prev_j = 0; // lane 0's copies carry over between tiles, as in the reference's single loop
     const int32_t limit = read_len + node_count + 2;
@@ -622,6 +658,21 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     if (loops >= limit)
         aligned = -1;
     return aligned;
+}
+
+// Both halves back to back (the single-launch kernel): the tile reuses the ring's memory.
+template <typename IdT>
+__device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
+                                       int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
+                                       int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
+                                       int32_t lane, int32_t* score_out = nullptr)
+{
+    int32_t start_row = 0;
+    if (fast_fill<IdT>(g, node_count, read, read_len, scores, band, gap, mismatch, match, smem, smem_bytes, lane,
+                       start_row, score_out) == kFastNotTaken)
+        return kFastNotTaken;
+    return fast_traceback<IdT>(g, node_count, nullptr, read_len, scores, gap, mismatch, match, smem,
+                               smem + kRingBytes, start_row, lane);
 }
 
 } // namespace poa_b200

@@ -54,6 +54,23 @@ struct ArenaLayout
     int32_t max_seq;
 };
 
+// Per-window state carried between the launches of the phase-split schedule (poa_phases.cuh).
+struct PhaseState
+{
+    int32_t status;     // kSt* value; anything but success stops the window
+    int32_t node_count;
+    int32_t finalized;  // outputs written
+    int32_t aln_len;    // kAlnPendingTraceback, or the result of the exact path
+    int32_t start_row;  // row the packed traceback starts from
+    int32_t graph_step; // last step whose graph phase ran (a step has two graph launches, a window takes one)
+    uint32_t rows, exact;
+    unsigned long long cells;
+    int64_t seq_off;    // offset of the current read's first base from the window's first base
+};
+constexpr int32_t kAlnPendingTraceback = -3;
+constexpr int32_t kClassMargin         = 64;  // nodes one fusion is allowed to add before the scratch is outgrown
+constexpr int32_t kPhaseCounters       = 512; // one window counter per launch of a batch
+
 struct KernelParams
 {
     const uint8_t* bases;
@@ -85,6 +102,10 @@ struct KernelParams
     int32_t* next_window; // zeroed before the launch; warps take window ids from it
     int32_t adaptive_max_band; // 0: static band; else the widest band the score rows can hold
     int32_t smem_per_warp; // bytes of shared-memory scratch each warp (= window) owns
+    PhaseState* phase;     // phase-split schedule: per-window state, else nullptr
+    int32_t step;          // phase-split schedule: the read (1 .. n_reads - 1) this launch works on
+    int32_t phase_class;   // graph launches come in two shared-memory sizes: 0 takes the windows whose graph fits
+    int32_t class_cap;     // ... the smaller scratch (node_count + kClassMargin <= class_cap), 1 the others
 };
 
 inline int64_t align_up64(int64_t v, int64_t a)

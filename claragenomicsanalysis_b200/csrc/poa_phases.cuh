@@ -1,0 +1,244 @@
+// Phase-split schedule of the banded POA build: the per-read loop of poa_window_kernel (poa_window.cuh) cut at the
+// boundary between the score fill and the graph work, one launch per phase and read:
+//
+//   for s = 1 .. max reads - 1:   poa_fill_kernel(s)    descriptors, fill, sink selection          (all lanes busy)
+//                                 poa_graph_kernel(s)   traceback, fusion, topological sort, and -- for windows whose
+//                                                       last read this is -- consensus / MSA       (mostly one lane)
+//
+// Same device functions, same order per window, hence the same results as the single launch; what changes is what
+// shares an SM.  The fill is a chain of packed integer instructions that needs 128 registers and the row ring; the
+// graph phases are latency-bound walks that need few registers and the traceback tile.  In one kernel every warp holds
+// the larger of the two footprints all the time (16 windows per SM); apart, the graph launches keep 24 windows per SM
+// in flight and the fill launches run with every resident warp in the fill.  Windows carry their state between
+// launches in PhaseState; the graph, the score rows and the row descriptors already live in global memory.
+// Follows generatePOAKernel's control flow and error protocol (cudapoa_kernels.cuh:171-359) like poa_window.cuh.
+#pragma once
+
+#include "poa_device.cuh"
+#include "poa_fast.cuh"
+
+namespace poa_b200
+{
+
+constexpr int32_t kFillWarpsPerBlock  = 4;
+constexpr int32_t kGraphWarpsPerBlock = 4;
+constexpr int32_t kTileBytes          = kTileRows * (kTileRowBytes + 8); // traceback tile + its row descriptors
+
+template <typename ScoreT, typename IdT, bool MSA>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 5) poa_fill_kernel(const KernelParams P)
+{
+    extern __shared__ __align__(16) uint8_t smem_block[];
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+
+        const WindowDesc wd = P.windows[w];
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t* rlen = P.read_len + wd.read_off;
+        PhaseState* ps      = P.phase + w;
+        PhaseState st;
+        if (s == 1) // first launch of the batch: backbone from read 0 (cudapoa_kernels.cuh:171-209)
+        {
+            st            = PhaseState{};
+            st.status     = kStSuccess;
+            if (wd.n_reads <= 0 || rlen[0] <= 0)
+                st.status = kStGenericError; // the reference has no defined behaviour for an empty backbone
+            else if (rlen[0] > P.layout.M)
+                st.status = kStNodeCountExceeded;
+            else
+            {
+                st.node_count = rlen[0];
+                init_backbone<IdT, MSA>(g, P.bases + wd.base_off, P.weights ? P.weights + wd.base_off : nullptr,
+                                        st.node_count, lane);
+            }
+            __syncwarp();
+        }
+        else
+        {
+            st = *ps;
+        }
+        if (st.status == kStSuccess && s < wd.n_reads)
+        {
+            st.seq_off += rlen[s - 1];
+            const uint8_t* seq = P.bases + wd.base_off + st.seq_off;
+            const int32_t len  = rlen[s];
+            if (st.node_count >= P.max_nodes) // cudapoa_kernels.cuh:220-226
+            {
+                st.status = kStNodeCountExceeded;
+            }
+            else
+            {
+                ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
+                int32_t aln_len     = kFastNotTaken;
+                int32_t aln_score   = 0;
+                int32_t start_row   = 0;
+                if (fast_fill<IdT>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.band, P.gap,
+                                   P.mismatch, P.match, smem, P.smem_per_warp, lane, start_row, &aln_score) == 0)
+                {
+                    aln_len = kAlnPendingTraceback;
+                }
+                else
+                {
+                    aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, len, scores, P.band + kBandRowPad,
+                                                             P.band, P.gap, P.mismatch, P.match, lane, &aln_score);
+                    st.exact++;
+                }
+                st.aln_len   = aln_len;
+                st.start_row = start_row;
+                st.rows += static_cast<uint32_t>(st.node_count);
+                st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(P.band);
+            }
+        }
+        if (lane == 0)
+            *ps = st;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+template <typename ScoreT, typename IdT, bool MSA>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(const KernelParams P)
+{
+    extern __shared__ __align__(16) uint8_t smem_block[];
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+
+        PhaseState* ps = P.phase + w;
+        PhaseState st  = *ps;
+        if (st.finalized || st.graph_step == s)
+            continue;
+        // two launches per step, differing in scratch size: each window goes to the one its graph fits (outgrowing
+        // the scratch is legal, the sort and the consensus then run out of global memory)
+        if ((st.node_count + kClassMargin > P.class_cap) != (P.phase_class == 1))
+            continue;
+        const WindowDesc wd = P.windows[w];
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t* rlen = P.read_len + wd.read_off;
+
+        if (st.status == kStSuccess && s < wd.n_reads)
+        {
+            const uint8_t* seq = P.bases + wd.base_off + st.seq_off;
+            const int8_t* wts  = P.weights ? P.weights + wd.base_off + st.seq_off : nullptr;
+            const int32_t len  = rlen[s];
+            int32_t aln_len    = st.aln_len;
+            if (aln_len == kAlnPendingTraceback)
+            {
+                int16_t* scores = reinterpret_cast<int16_t*>(static_cast<ScoreT*>(P.scores) +
+                                                             static_cast<int64_t>(w) * P.banded_score_stride);
+                aln_len = fast_traceback<IdT>(g, st.node_count, seq, len, scores, P.gap, P.mismatch, P.match, smem,
+                                              smem + kTileBytes, st.start_row, lane);
+            }
+            if (aln_len == -1) // cudapoa_kernels.cuh:281-289
+            {
+                st.status = kStLoopCountExceeded;
+            }
+            else
+            {
+                __syncwarp(); // lane 0's traceback output becomes visible to the warp
+                int32_t rc = add_alignment<IdT, MSA>(g, st.node_count, seq, len, wts,
+                                                     MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
+                                                     P.max_nodes, lane);
+                __syncwarp();
+                if (rc == kStSuccess)
+                {
+                    if (P.spoa_accurate)
+                    {
+                        if (lane == 0 && !topsort_spoa_order<IdT>(g, st.node_count))
+                            rc = kStGenericError;
+                        rc = __shfl_sync(kFull, rc, 0);
+                    }
+                    else if (!topsort_kahn_smem<IdT>(g, st.node_count, smem, P.smem_per_warp, lane))
+                    {
+                        if (lane == 0)
+                            topsort_kahn<IdT>(g, st.node_count);
+                    }
+                }
+                __syncwarp();
+                if (rc != kStSuccess) // cudapoa_kernels.cuh:314-319
+                    st.status = rc;
+            }
+        }
+
+        if (st.status != kStSuccess || s >= wd.n_reads - 1) // the window is complete: outputs
+        {
+            int32_t status = st.status;
+            if (status == kStSuccess)
+            {
+                if (!MSA)
+                {
+                    uint8_t* cons_out = P.consensus + static_cast<int64_t>(w) * P.max_consensus;
+                    uint16_t* cov_out = P.coverage + static_cast<int64_t>(w) * P.max_consensus;
+                    int32_t rc = generate_consensus_smem<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus, smem,
+                                                              P.smem_per_warp, lane);
+                    if (rc < 0) // does not fit the scratch: serial version out of global memory
+                    {
+                        if (lane == 0)
+                            rc = generate_consensus<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus);
+                        rc = __shfl_sync(kFull, rc, 0);
+                    }
+                    status = rc;
+                }
+                else
+                {
+                    int32_t msa_len = 0;
+                    if (lane == 0)
+                    {
+                        if (!topsort_spoa_order<IdT>(g, st.node_count))
+                            status = kStGenericError;
+                        else
+                        {
+                            msa_len = msa_columns<IdT>(g, st.node_count);
+                            if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
+                                status = kStSeqSizeExceeded;
+                        }
+                    }
+                    status  = __shfl_sync(kFull, status, 0);
+                    msa_len = __shfl_sync(kFull, msa_len, 0);
+                    __syncwarp();
+                    if (status == kStSuccess)
+                        msa_rows<IdT>(g, P.bases + wd.base_off, rlen, wd.n_reads,
+                                      P.msa + static_cast<int64_t>(w) * P.max_reads * P.max_consensus, msa_len,
+                                      P.max_consensus, P.layout.max_seq, lane);
+                }
+            }
+            if (lane == 0)
+            {
+                P.status[w]     = static_cast<uint8_t>(status);
+                P.node_count[w] = st.node_count;
+                P.stat_rows[w]  = st.rows;
+                P.stat_exact[w] = st.exact;
+                P.stat_cells[w] = st.cells;
+            }
+            st.status    = status;
+            st.finalized = 1;
+        }
+        st.graph_step = s;
+        if (lane == 0)
+            *ps = st;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+} // namespace poa_b200

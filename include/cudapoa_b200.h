@@ -102,6 +102,7 @@ typedef struct cudapoa_b200_stats
     double kernel_ms;       /* CUDA-event time of the device work of generate_poa            */
     double graph_kernel_ms; /* the POA graph-build kernel alone                              */
     int64_t widened;        /* adaptive banding: alignments repeated with a wider band       */
+    int64_t kernel_launches; /* kernels enqueued by generate_poa (and by bench_relaunch since)   */
 } cudapoa_b200_stats;
 
 const char* CUDAPOA_CABI(last_error)(void);
