@@ -270,7 +270,8 @@ void B200Batch::allocate(size_t max_mem)
         a(n * 4);                     // stat_rows
         a(n * 4);                     // stat_exact
         a((n + 1) * 8);               // stat_cells + the launch's window counter
-        a(n * static_cast<int64_t>(sizeof(PhaseState)) + kPhaseCounters * 4); // phase-split schedule
+        a(kPhaseCounters * 4);                              // phase-split schedule: window counters
+        a(n * static_cast<int64_t>(sizeof(PhaseState)));    // ... and per-window state
         a(msa_ ? 0 : n * C);          // consensus
         a(msa_ ? 0 : n * C * 2);      // coverage
         a(msa_ ? n * S * C : 0);      // msa
@@ -462,13 +463,17 @@ static void launch_typed(const KernelParams& P, bool banded, bool msa, int32_t s
 }
 
 // One launch of a phase kernel: persistent warps, at most one resident wave of CTAs.
+// The dynamic shared-memory limit is an attribute of the function, shared by every batch and host thread of the
+// process: it is only ever set to one value, the most any launch uses.
+constexpr int kPhaseSmemLimit = 200 * 1024;
+
 template <typename Kernel>
 static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per_block, int32_t sm_count,
                          cudaStream_t stream)
 {
     const dim3 block(warps_per_block * 32);
     const size_t smem = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
-    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPhaseSmemLimit));
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
     int per_sm           = 1;
     GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
@@ -536,7 +541,7 @@ bool B200Batch::launch_split(KernelParams& P)
     const int32_t fill_smem  = (kRingBytes + ((L + kFastBand + 8 + 15) & ~15) + 255) & ~255;
     const int32_t graph_smem = (kTileBytes + ((L + 15) & ~15) + 255) & ~255;
     const int32_t graph_smem_large = std::max(graph_smem, kSmemPerWarp);
-    if (4 * std::max(fill_smem, graph_smem_large) > 200 * 1024)
+    if (4 * std::max(fill_smem, graph_smem_large) > kPhaseSmemLimit)
         return false;
     P.phase = phase_d_;
     int32_t launches = 0;

@@ -531,6 +531,7 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
                                   uint32_t rd, int32_t start_row, int32_t lane)
 {
     uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
+    asm volatile("" : "+l"(rows)); // keep the pointer in registers: recomputing it inside the walk costs more
     RowDesc desc;
     desc.d0 = g.rowinfo;
     desc.d1 = desc.d0 + (g.M + 40);
@@ -566,8 +567,48 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
                 return tilted_score_global(rows, row, column);
             };
             int32_t sij = cell(i, j);
+            // addresses of descriptor(row) and cell(row, column) as base + 8 * row and base + kTileRowBytes * row +
+            // 2 * column (32-bit shared addresses: the arithmetic may wrap)
+            const uint32_t desc_base = tile_desc - 8u * static_cast<uint32_t>(tile_r0);
+            const uint32_t cell_base = tile + 2u * static_cast<uint32_t>(8 - tile_c0) -
+                                       static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(tile_r0);
+            const int32_t fast_row_floor = max(row_floor, 1);
+            const int32_t fast_col_floor = max(tile_c0, 0);
             while (!(i == 0 && j == 0) && loops < limit && i >= row_floor && j > tile_c0)
             {
+                // Runs of diagonal moves through predecessor 0 -- most of the walk -- in a loop of their own: the
+                // first test of the general step below, with nothing else around it.  Overshooting `limit` is
+                // harmless: the result is -1 as soon as loops reaches it.
+                {
+                    int32_t fi = i, fj = j, fs = sij;
+                    IdT* out = g.aln_node + (fj - 1);
+                    while (fi >= fast_row_floor && fj > fast_col_floor)
+                    {
+                        const uint32_t meta = lds_u32(desc_base + 8u * static_cast<uint32_t>(fi));
+                        const int32_t p0    = static_cast<int32_t>(meta >> 16);
+                        if (p0 < tile_r0)
+                            break;
+                        const int32_t cost = ((meta & 0xff) == lds_u8(rd + fj - 1)) ? pd_m : pd_x;
+                        const int32_t h    = lds_s16(cell_base + static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(p0) +
+                                                  2u * static_cast<uint32_t>(fj - 1));
+                        if (fs != h + cost)
+                            break;
+                        *out-- = static_cast<IdT>(fi);
+                        fi     = p0;
+                        fj--;
+                        fs = h;
+                    }
+                    const int32_t n = j - fj;
+                    if (n > 0)
+                    {
+                        loops += n;
+                        aligned += n;
+                        prev_i = i = fi;
+                        prev_j = j = fj;
+                        sij    = fs;
+                        continue;
+                    }
+                }
                 loops++;
                 bool found = false;
                 int32_t h  = 0;
