@@ -173,15 +173,15 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
-def ncu_traffic(n_windows):
-    """DRAM bytes one launch of n_windows moves, from the committed ncu capture (bytes per window x windows)."""
+def ncu_traffic():
+    """DRAM bytes per window and step of each kernel, from the committed ncu launch list (profiles/ncu_traffic.json:
+    dram__bytes_read.sum + dram__bytes_write.sum summed over the launches of one step, divided by its windows)."""
     path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     try:
         with open(path) as f:
-            t = json.load(f)
-        return float(t["dram_bytes_per_window"]) * n_windows
-    except (OSError, KeyError, ValueError):
-        return None
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
 
 
 def run_native(args, rank, world, local_rank):
@@ -199,6 +199,9 @@ def run_native(args, rank, world, local_rank):
     dll.cudapoa_b200_bench_relaunch.argtypes = [ctypes.c_void_p, ctypes.c_int32]
     dll.cudapoa_b200_debug_dpx_peak.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_double),
                                                 ctypes.POINTER(ctypes.c_double)]
+    dll.cudapoa_b200_bench_relaunch_phases.restype = ctypes.c_int32
+    dll.cudapoa_b200_bench_relaunch_phases.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
+                                                       ctypes.POINTER(ctypes.c_double)]
 
     device = local_rank
     torch.cuda.set_device(device)
@@ -252,6 +255,12 @@ def run_native(args, rank, world, local_rank):
     if ms_total <= 0:
         raise RuntimeError("relaunch failed: " + lib.error())
     ms_step = max_over_ranks(ms_total / args.steps)
+    # the same step once more with a CUDA event between its launches: time per kernel (outside the timed region)
+    fill_ms = ctypes.c_double(0)
+    graph_ms = ctypes.c_double(0)
+    launches_per_step = dll.cudapoa_b200_bench_relaunch_phases(batch._handle, ctypes.byref(fill_ms), ctypes.byref(graph_ms))
+    if launches_per_step <= 0:
+        raise RuntimeError("relaunch_phases failed: " + lib.error())
     batch.fetch("consensus")
     if batch.result_digest() != digest0:
         raise RuntimeError("results changed between launches")
@@ -277,11 +286,13 @@ def run_native(args, rank, world, local_rank):
     barrier()
     t0 = time.perf_counter()
     h2d = d2h = 0
+    e2e_launches = 0
     for _ in range(args.steps):
         pipe.run(ws, chunk)
         st2 = pipe.stats()
         h2d += st2["h2d_bytes"]
         d2h += st2["d2h_bytes"]
+        e2e_launches += st2["kernel_launches"]
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     e2e_s = max_over_ranks((t1 - t0) / args.steps)
@@ -289,13 +300,26 @@ def run_native(args, rank, world, local_rank):
     e2e_value = total_windows / e2e_s
     if pipe.digest() != digest0:
         raise RuntimeError("end-to-end results differ from the first pass")
-    e2e_launches = args.steps * ((n_win + chunk - 1) // chunk)
     pipe.close()
 
     # ---- rooflines ----
+    # The dominant kernel is poa_fill_kernel (one launch per read; share of the step measured above).  HBM view:
+    # algorithmic bytes of a fill launch = the bases of the reads it aligns + their 4-byte lengths (SURVEY.md 8(d)'s
+    # per-window figure restricted to what this kernel consumes; everything else it touches -- graph, descriptors,
+    # score rows -- is intermediate state), against the launch durations measured with CUDA events.  `traffic` is what
+    # ncu measured for the same launches: the streamed score rows.
     hbm_peak, hbm_src = measured_peaks()
     alg_bytes = algorithmic_bytes(ws, cons_chars)
-    achieved_gbs = alg_bytes / (ms_step * 1e-3) / 1e9 if world == 1 else sum_over_ranks(float(alg_bytes)) / (ms_step * 1e-3) / 1e9 / world
+    n_fill = max(1, int(ws.window_n_reads.max()) - 1)
+    first_reads = np.concatenate(([0], np.cumsum(ws.window_n_reads, dtype=np.int64)[:-1]))
+    backbone_bytes = int(ws.read_lengths[first_reads].sum())
+    fill_alg_bytes = (int(ws.n_bases) - backbone_bytes + 4 * (int(ws.n_reads) - n_win)) / n_fill  # per launch
+    fill_launch_ms = fill_ms.value / n_fill
+    achieved_gbs = fill_alg_bytes / (fill_launch_ms * 1e-3) / 1e9
+    traffic = ncu_traffic()
+    fill_traffic = traffic.get("poa_fill_kernel", {}).get("dram_bytes_per_window_step")
+    graph_traffic = traffic.get("poa_graph_kernel", {}).get("dram_bytes_per_window_step")
+    phase_ms = fill_ms.value + graph_ms.value
     r16 = ctypes.c_double(0)
     r16ms = ctypes.c_double(0)
     dll.cudapoa_b200_debug_dpx_peak(device, 0, ctypes.byref(r16), ctypes.byref(r16ms))
@@ -316,15 +340,34 @@ def run_native(args, rank, world, local_rank):
                 "d2h_bytes_per_step": int(d2h // args.steps), "ms_per_step": e2e_s * 1e3,
                 "path": "cudapoa_b200_pipeline_run(host buffers): %d workers x (add_poa_group -> generate_poa -> "
                         "get_consensus), chunks of %d windows" % (args.workers, chunk)},
-        "gpu_launches": args.steps + e2e_launches,
-        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved_gbs / hbm_peak, "traffic": ncu_traffic(n_win), "peak_source": hbm_src,
-                     "traffic_source": "profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of "
-                                       "one ncu --set full capture of this kernel, scaled to this launch's windows",
-                     "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "integer DP: the binding roofline is the DPX issue rate, see roofline_dpx"},
-        "roofline_dpx": {"bound": "dpx-int16", "achieved": per_gpu_gcups, "peak": dpx_peak_gcups, "unit": "GCUPS",
-                         "frac": per_gpu_gcups / dpx_peak_gcups if dpx_peak_gcups > 0 else None,
+        "gpu_launches": int(args.steps * launches_per_step + e2e_launches),
+        "kernels": {
+            "launches_per_step": int(launches_per_step),
+            "poa_fill_kernel": {"launches": n_fill, "ms_per_step": fill_ms.value,
+                                "share_of_step": fill_ms.value / phase_ms if phase_ms > 0 else None,
+                                "gcups": stats["dp_cells"] / (fill_ms.value * 1e-3) / 1e9,
+                                "dram_gb_per_s": (fill_traffic * n_win / (fill_ms.value * 1e-3) / 1e9) if fill_traffic else None},
+            "poa_graph_kernel": {"launches": int(launches_per_step) - n_fill, "ms_per_step": graph_ms.value,
+                                 "share_of_step": graph_ms.value / phase_ms if phase_ms > 0 else None,
+                                 "dram_gb_per_s": (graph_traffic * n_win / (graph_ms.value * 1e-3) / 1e9) if graph_traffic else None},
+            "note": "one extra pass of the step with a CUDA event between launches, rank 0's GPU",
+        },
+        "roofline": {"bound": "hbm", "kernel": "poa_fill_kernel", "achieved": achieved_gbs, "peak": hbm_peak,
+                     "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                     "traffic": (fill_traffic * n_win / n_fill) if fill_traffic else None, "peak_source": hbm_src,
+                     "traffic_source": "profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of this "
+                                       "kernel's launches in the committed ncu capture, per launch, scaled to this "
+                                       "step's windows",
+                     "algorithmic_bytes_per_launch": fill_alg_bytes, "launch_ms": fill_launch_ms,
+                     "algorithmic_bytes_per_step_all_kernels": alg_bytes,
+                     "note": "integer DP: the binding roofline is the DPX issue rate, see roofline_dpx; the DRAM "
+                             "traffic is the score matrix streamed for the traceback, not input"},
+        "roofline_dpx": {"bound": "dpx-int16", "kernel": "poa_fill_kernel",
+                         "achieved": stats["dp_cells"] / (fill_ms.value * 1e-3) / 1e9, "peak": dpx_peak_gcups,
+                         "unit": "GCUPS",
+                         "frac": stats["dp_cells"] / (fill_ms.value * 1e-3) / 1e9 / dpx_peak_gcups if dpx_peak_gcups > 0 else None,
+                         "whole_step_gcups": per_gpu_gcups,
+                         "whole_step_frac": per_gpu_gcups / dpx_peak_gcups if dpx_peak_gcups > 0 else None,
                          "peak_source": "VIADDMNMX.S16x2 thread-instructions/s measured in this run "
                                         "(cudapoa_b200_debug_dpx_peak, %.2f ms)" % r16ms.value},
         "clocks": clocks,
@@ -423,7 +466,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--windows", type=int, default=18944, help="windows per step per GPU (8 waves of 148 x 16)")
     ap.add_argument("--chunk", type=int, default=2368, help="end-to-end leg: windows per batch round")
-    ap.add_argument("--workers", type=int, default=3, help="end-to-end leg: host threads / streams / batches")
+    ap.add_argument("--workers", type=int, default=6, help="end-to-end leg: host threads / streams / batches")
     ap.add_argument("--worker-mem-gb", type=float, default=8.0)
     ap.add_argument("--distinct", type=int, default=1024, help="distinct generated windows (tiled to --windows)")
     ap.add_argument("--max-mem-gb", type=float, default=64.0)

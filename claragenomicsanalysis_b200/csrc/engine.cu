@@ -98,6 +98,8 @@ T* carve(uint8_t*& cursor, int64_t count)
 
 } // namespace
 
+struct PhaseTimeline;
+
 class B200Batch : public Batch, public EngineStatsSource
 {
 public:
@@ -170,6 +172,7 @@ public:
     void fill_stats(cudapoa_b200_stats* out) const override;
     int32_t max_poas() const override { return max_poas_; }
     double relaunch(int32_t iterations) override;
+    int32_t relaunch_phases(double* fill_ms, double* graph_ms) override;
 
 private:
     void allocate(size_t max_mem);
@@ -243,6 +246,7 @@ private:
     bool has_weights_       = false;
     bool launched_          = false;
     int64_t kernel_launches_ = 0; // kernels enqueued by the last generate_poa / relaunch
+    PhaseTimeline* timeline_ = nullptr; // set while relaunch_phases() is timing the launches
     bool timed_             = false;
     int32_t timed_iters_    = 1;
 
@@ -488,11 +492,39 @@ static int32_t graph_scratch_nodes(int32_t smem)
     return std::min((smem / kKahnBytesPerNode) & ~7, ((smem - kConsStageBytes) / 6) & ~7);
 }
 
+// Optional CUDA events between the launches of one batch (relaunch_phases): kinds[i] tells what ran before events[i + 1].
+struct PhaseTimeline
+{
+    std::vector<cudaEvent_t> events;
+    std::vector<int8_t> kinds; // 0 fill, 1 graph
+    size_t used = 0;
+    void mark(cudaStream_t stream, int kind)
+    {
+        if (used == events.size())
+        {
+            cudaEvent_t e;
+            GW_CU_CHECK_ERR(cudaEventCreate(&e));
+            events.push_back(e);
+        }
+        GW_CU_CHECK_ERR(cudaEventRecord(events[used++], stream));
+        if (kind >= 0)
+            kinds.push_back(static_cast<int8_t>(kind));
+    }
+    ~PhaseTimeline()
+    {
+        for (cudaEvent_t e : events)
+            cudaEventDestroy(e);
+    }
+};
+
 template <typename ScoreT, typename IdT, bool MSA>
 static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_smem, int32_t graph_smem,
-                                  int32_t graph_smem_large, int32_t* counters, int32_t sm_count, cudaStream_t stream)
+                                  int32_t graph_smem_large, int32_t* counters, int32_t sm_count, cudaStream_t stream,
+                                  PhaseTimeline* timeline)
 {
     int32_t launches = 0;
+    if (timeline)
+        timeline->mark(stream, -1);
     const bool two   = graph_smem_large > graph_smem;
     P.class_cap      = two ? graph_scratch_nodes(graph_smem) : INT32_MAX - kClassMargin;
     for (int32_t s = 1; s <= steps; s++)
@@ -501,10 +533,14 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
         P.next_window   = counters + 3 * (s - 1);
         P.smem_per_warp = fill_smem;
         launch_phase(poa_fill_kernel<ScoreT, IdT, MSA>, P, kFillWarpsPerBlock, sm_count, stream);
+        if (timeline)
+            timeline->mark(stream, 0);
         P.next_window   = counters + 3 * (s - 1) + 1;
         P.smem_per_warp = graph_smem;
         P.phase_class   = 0;
         launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+        if (timeline)
+            timeline->mark(stream, 1);
         launches += 2;
         if (two)
         {
@@ -512,6 +548,8 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
             P.smem_per_warp = graph_smem_large;
             P.phase_class   = 1;
             launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+            if (timeline)
+                timeline->mark(stream, 1);
             launches++;
         }
     }
@@ -549,16 +587,16 @@ bool B200Batch::launch_split(KernelParams& P)
     if (!plan_.score32)
     {
         if (msa_)
-            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     else
     {
         if (msa_)
-            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_);
+            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     kernel_launches_ += launches;
     return true;
@@ -693,6 +731,41 @@ double B200Batch::relaunch(int32_t iterations)
     timed_       = false; // the next get_* refreshes kernel_ms from these events
     timed_iters_ = iterations;
     return static_cast<double>(ms);
+}
+
+int32_t B200Batch::relaunch_phases(double* fill_ms, double* graph_ms)
+{
+    scoped_device_switch dev(device_id_);
+    if (!launched_ || poa_count_ == 0)
+        return -1;
+    PhaseTimeline timeline;
+    timeline_        = &timeline;
+    kernel_launches_ = 0;
+    GW_CU_CHECK_ERR(cudaEventRecord(ev_start_, stream_));
+    launch();
+    GW_CU_CHECK_ERR(cudaEventRecord(ev_stop_, stream_));
+    timeline_ = nullptr;
+    GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
+    double fill = 0.0, graph = 0.0;
+    if (timeline.used < 2) // single launch: everything is one kernel
+    {
+        float ms = 0.f;
+        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, ev_start_, ev_stop_));
+        fill = ms;
+    }
+    for (size_t i = 0; i + 1 < timeline.used; i++)
+    {
+        float ms = 0.f;
+        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, timeline.events[i], timeline.events[i + 1]));
+        (timeline.kinds[i] == 0 ? fill : graph) += ms;
+    }
+    if (fill_ms)
+        *fill_ms = fill;
+    if (graph_ms)
+        *graph_ms = graph;
+    timed_       = false;
+    timed_iters_ = 1;
+    return static_cast<int32_t>(kernel_launches_);
 }
 
 void B200Batch::fill_stats(cudapoa_b200_stats* out) const

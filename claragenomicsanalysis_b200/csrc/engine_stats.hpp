@@ -21,6 +21,10 @@ public:
     // Benchmark hook: re-run the device work of the last generate_poa() `iterations` times on inputs that are
     // already resident in device memory; returns the CUDA-event time of all iterations in ms (< 0: nothing staged).
     virtual double relaunch(int32_t iterations) = 0;
+    // Same device work once more, with a CUDA event between the launches: milliseconds spent in the fill launches and
+    // in the graph launches of the phase-split schedule (a batch on the single launch reports everything as fill_ms).
+    // Returns the number of launches timed, < 0 if nothing has been staged.
+    virtual int32_t relaunch_phases(double* fill_ms, double* graph_ms) = 0;
 };
 
 } // namespace cudapoa

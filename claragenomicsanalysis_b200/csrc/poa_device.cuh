@@ -789,9 +789,7 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         uint32_t head_a = queue;            // address of the queue head
         uint32_t tail_a = queue + 2 * tail; // address one past the queue tail
         uint32_t node   = lds_u16(head_a);  // a graph always has a source
-        uint2 v         = lds_v2(rec + 8 * node);
-        uint32_t last   = 0xffffffffu;      // node most recently queued by this loop (the element before tail_a)
-        const uint32_t last_rec = static_cast<uint32_t>(cap - 1);
+
         // visit(child): one in-edge of child is satisfied; queue it when it was the last one
 #define POA_KAHN_VISIT(child_expr)                                  \
     {                                                               \
@@ -803,17 +801,12 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         {                                                           \
             sts_u16(tail_a, child_);                                \
             tail_a += 2;                                            \
-            last = child_;                                          \
         }                                                           \
     }
-        // In a chain the next node to leave the queue is the first child of this one, queued a moment ago: its record
-        // is fetched ahead of the bookkeeping (only edges and out-degree are used from it, which that does not
-        // touch) and the queue read is skipped, which halves the chain of dependent shared-memory accesses per node.
         while (true)
         {
-            const uint32_t oc    = (v.y >> 16) & 0xffu;
-            const uint32_t first = v.x & 0xffffu;
-            const uint2 ahead    = lds_v2(rec + 8 * min(first, last_rec)); // stale ids beyond the out-degree: clamped
+            const uint2 v     = lds_v2(rec + 8 * node);
+            const uint32_t oc = (v.y >> 16) & 0xffu;
             if (oc > 0)
                 POA_KAHN_VISIT(v.x & 0xffffu)
             if (oc > 1)
@@ -827,16 +820,7 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
             head_a += 2;
             if (head_a >= tail_a)
                 break;
-            if (head_a + 2 == tail_a && last == first && oc > 0)
-            {
-                node = first;
-                v    = ahead;
-            }
-            else
-            {
-                node = lds_u16(head_a);
-                v    = lds_v2(rec + 8 * node);
-            }
+            node = lds_u16(head_a);
         }
 #undef POA_KAHN_VISIT
     }

@@ -295,6 +295,9 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
     const uint32_t pdmx2 = pack2(pd_m ^ pd_x, pd_m ^ pd_x);
 
     uint32_t rb_lo = 0, rb_hi = 0;
+    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last, its band start and left boundary
+    int32_t prev_bs     = -1;
+    int32_t prev_left_t = 0;
     // Descriptors travel in registers: chunk c* holds rows r0 .. r0 + 31 (one row per lane), chunk n* the next 32
     // rows, loaded a chunk ahead; band starts likewise.  The row loop receives its descriptor by shuffle, issued one
     // iteration early.
@@ -353,34 +356,68 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
             int32_t min_d     = 1 << 20;   // smallest band shift over the predecessors
             int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
 
-            // one predecessor row: S = max(S, diagonal and vertical candidates)
+            // one predecessor row: S = max(S, diagonal and vertical candidates).  The vertical operands V_i are the
+            // predecessor's cells under this lane's cells, the diagonal operands D_i = V_{i-1}, D_0 = (corner, V_3.lo).
+            // All branches below are warp-uniform (band shifts and row numbers are).
             auto step = [&](int32_t prow) {
-                const int32_t sl0 = lane + 1;     // block of this lane's cells
-                uint4 lead, a, b;
-                uint32_t wv;
+                uint32_t V0, V1, V2, V3, D0;
                 int32_t d;
-                if (prow >= ring_lo) // shared-memory ring
+                if (prow == r - 1 && bs == prev_bs && r > 1)
+                {
+                    // the row just written, same band start: its cells are still in this lane's registers; the
+                    // corner is the last cell of the lane to the left (lane 0: that row's left boundary)
+                    d  = 0;
+                    V0 = prev_out.x;
+                    V1 = prev_out.y;
+                    V2 = prev_out.z;
+                    V3 = prev_out.w;
+                    uint32_t X = __shfl_up_sync(kFull, prev_out.w, 1);
+                    if (lane == 0)
+                        X = static_cast<uint32_t>(prev_left_t) << 16;
+                    D0        = __byte_perm(X, V3, 0x5432);
+                    left_best = max(left_best, prev_left_t);
+                }
+                else if (prow >= ring_lo) // shared-memory ring
                 {
                     const uint32_t pa = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
-                    lead              = lds_v4(pa);
+                    const uint4 lead  = lds_v4(pa);
                     d                 = bs - static_cast<int32_t>(lead.x); // >= 0, multiple of 4
-                    const int32_t sl  = min(sl0 + (d >> 3), kPadBlock);    // block of the first vertical operand
-                    const int32_t sn  = min(sl + 1, kPadBlock);
-                    const int32_t sc  = min((8 * lane + d + 7) >> 3, kPadBlock); // block of the cell before it
-                    a                 = lds_v4(pa + 16u * sl);
-                    b                 = lds_v4(pa + 16u * sn);
-                    wv                = lds_u32(pa + 16u * sc + 12u);
+                    const int32_t su  = lane + 1 + (d >> 3);               // block of the first vertical operand
+                    const uint4 a     = lds_v4(pa + 16u * min(su, kPadBlock));
+                    if (d & 4)
+                    {
+                        // shift by an odd multiple of 4: operands straddle two blocks -> (hi of this block, lo of the
+                        // next); the corner is the low half of this block's last word
+                        const uint4 b = lds_v4(pa + 16u * min(su + 1, kPadBlock));
+                        V0            = __byte_perm(a.x, b.x, 0x5432);
+                        V1            = __byte_perm(a.y, b.y, 0x5432);
+                        V2            = __byte_perm(a.z, b.z, 0x5432);
+                        V3            = __byte_perm(a.w, b.w, 0x5432);
+                        D0            = __byte_perm(a.w, V3, 0x5410);
+                    }
+                    else
+                    {
+                        // whole blocks: the corner is the high half of the previous block's last word (the lead
+                        // block for lane 0: the predecessor's left boundary)
+                        const uint32_t wv = lds_u32(pa + 16u * min(su - 1, kPadBlock) + 12u);
+                        V0                = a.x;
+                        V1                = a.y;
+                        V2                = a.z;
+                        V3                = a.w;
+                        D0                = __byte_perm(wv, V3, 0x5432);
+                    }
+                    left_best = max(left_best, hi16(lead.w));
                 }
                 else // far predecessor: the global score matrix (through L2); pad blocks are implied
                 {
                     const uint4* prow4 = reinterpret_cast<const uint4*>(rows + prow * kFastRowWords);
-                    lead               = __ldcg(prow4);
+                    const uint4 lead   = __ldcg(prow4);
                     d                  = bs - static_cast<int32_t>(lead.x);
-                    const int32_t sl   = sl0 + (d >> 3);
+                    const int32_t sl   = lane + 1 + (d >> 3);
                     const int32_t sc   = (8 * lane + d + 7) >> 3;
                     const uint32_t p33 = (prow == 0) ? pack2(0, kNegT) : NEG2; // row 0's first pad block
-                    a = b    = NEG4;
-                    wv       = NEG2;
+                    uint4 a = NEG4, b = NEG4;
+                    uint32_t wv = NEG2;
                     if (sl <= 32)
                         a = __ldcg(prow4 + sl);
                     else if (sl == 33)
@@ -393,26 +430,20 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
                         wv = __ldcg(reinterpret_cast<const uint32_t*>(prow4 + sc) + 3);
                     else if (sc == 33)
                         wv = p33;
+                    const bool odd      = (d & 4) != 0;
+                    const uint32_t selV = odd ? 0x5432u : 0x3210u;
+                    V0                  = __byte_perm(a.x, b.x, selV);
+                    V1                  = __byte_perm(a.y, b.y, selV);
+                    V2                  = __byte_perm(a.z, b.z, selV);
+                    V3                  = __byte_perm(a.w, b.w, selV);
+                    D0                  = __byte_perm(odd ? a.w : wv, V3, odd ? 0x5410u : 0x5432u);
+                    left_best           = max(left_best, hi16(lead.w));
                 }
-                left_best = max(left_best, hi16(lead.w));
-                min_d     = min(min_d, d);
-                // shift by an odd multiple of 4: operands straddle two blocks -> (hi of this block, lo of the
-                // next); the corner is then the low half of this block's last word, else the high half of the
-                // previous block's (the lead block for lane 0: the predecessor's left boundary)
-                const bool odd      = (d & 4) != 0;
-                const uint32_t selV = odd ? 0x5432u : 0x3210u;
-                const uint32_t selD = odd ? 0x5410u : 0x5432u;
-                const uint32_t X    = odd ? a.w : wv;
-                const uint32_t V0   = __byte_perm(a.x, b.x, selV);
-                const uint32_t V1   = __byte_perm(a.y, b.y, selV);
-                const uint32_t V2   = __byte_perm(a.z, b.z, selV);
-                const uint32_t V3   = __byte_perm(a.w, b.w, selV);
-                // diagonal operands: D_i = V_{i-1}; D_0 = (corner, V_3.lo)
-                const uint32_t D0 = __byte_perm(X, V3, selD);
-                S[0] = __viaddmax_s16x2(D0, Q[0], __viaddmax_s16x2(V0, gapv, S[0]));
-                S[1] = __viaddmax_s16x2(V0, Q[1], __viaddmax_s16x2(V1, gapv, S[1]));
-                S[2] = __viaddmax_s16x2(V1, Q[2], __viaddmax_s16x2(V2, gapv, S[2]));
-                S[3] = __viaddmax_s16x2(V2, Q[3], __viaddmax_s16x2(V3, gapv, S[3]));
+                min_d = min(min_d, d);
+                S[0]  = __viaddmax_s16x2(D0, Q[0], __viaddmax_s16x2(V0, gapv, S[0]));
+                S[1]  = __viaddmax_s16x2(V0, Q[1], __viaddmax_s16x2(V1, gapv, S[1]));
+                S[2]  = __viaddmax_s16x2(V1, Q[2], __viaddmax_s16x2(V2, gapv, S[2]));
+                S[3]  = __viaddmax_s16x2(V2, Q[3], __viaddmax_s16x2(V3, gapv, S[3]));
             };
             step(static_cast<int32_t>(meta >> 16)); // predecessor 0 (row 0 for a node without in-edges)
             {
@@ -475,6 +506,9 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
                 __stcg(this_row, lead);
                 sts_v4(rrow, lead);
             }
+            prev_out    = out;
+            prev_bs     = bs;
+            prev_left_t = static_cast<int16_t>(left_t);
             __syncwarp();
         }
     }

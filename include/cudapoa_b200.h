@@ -199,6 +199,11 @@ int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* ins
  * iterations in milliseconds, measured on the batch's own stream; negative if nothing has been staged. */
 double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations);
 
+/* Native library only: the same device work once more with a CUDA event between the kernel launches.  *fill_ms and
+ * *graph_ms receive the time spent in the score-fill launches and in the graph launches (traceback, fusion,
+ * topological sort, consensus) of the phase-split schedule; returns the number of launches, negative on error. */
+int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fill_ms, double* graph_ms);
+
 /* ---- Window pipeline (native library only; no reference counterpart) ------------------------------------------
  * The stream scheduler / sharding layer above the Batch interface (the reference drives several Batch objects from
  * std::async tasks in cudapoa/benchmarks/multi_batch.hpp:157-170; it has no multi-GPU code).  Each worker thread owns
