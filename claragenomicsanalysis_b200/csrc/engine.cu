@@ -485,11 +485,10 @@ static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per
     kernel<<<grid, block, smem, stream>>>(P);
 }
 
-// Nodes a graph may have for the sort (10 bytes per node) and the consensus (staging area + 6 bytes per node) to run
-// out of `smem` bytes of scratch.
-static int32_t graph_scratch_nodes(int32_t smem)
+// Nodes a graph may have for the consensus (staging area + 6 bytes per node) to run out of `smem` bytes of scratch.
+static int32_t consensus_scratch_nodes(int32_t smem)
 {
-    return std::min((smem / kKahnBytesPerNode) & ~7, ((smem - kConsStageBytes) / 6) & ~7);
+    return ((smem - kConsStageBytes) / 6) & ~7;
 }
 
 // Optional CUDA events between the launches of one batch (relaunch_phases): kinds[i] tells what ran before events[i + 1].
@@ -526,7 +525,8 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
     if (timeline)
         timeline->mark(stream, -1);
     const bool two   = graph_smem_large > graph_smem;
-    P.class_cap      = two ? graph_scratch_nodes(graph_smem) : INT32_MAX - kClassMargin;
+    P.class_cap       = two ? kahn_smem_nodes(graph_smem) : INT32_MAX - kClassMargin;
+    P.class_cap_final = two ? std::min(kahn_smem_nodes(graph_smem), consensus_scratch_nodes(graph_smem)) : P.class_cap;
     for (int32_t s = 1; s <= steps; s++)
     {
         P.step          = s;

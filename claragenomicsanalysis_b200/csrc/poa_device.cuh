@@ -747,7 +747,14 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 #ifndef POA_AB
 #define POA_AB 0
 #endif
-constexpr int32_t kKahnBytesPerNode = 10; // 8-byte record {edge0, edge1, edge2, out-degree, remaining in-degree} + queue
+constexpr int32_t kKahnBytesPerNode = 8;   // record {edge0, edge1, edge2, out-degree, remaining in-degree}
+constexpr int32_t kKahnQueueEntries = 128; // the FIFO is a ring: a POA graph's frontier is a handful of nodes
+
+// Nodes a graph may have for the sort to run out of `smem_bytes` of scratch.
+__host__ __device__ inline int32_t kahn_smem_nodes(int32_t smem_bytes)
+{
+    return ((smem_bytes - 2 * kKahnQueueEntries) / kKahnBytesPerNode) & ~7;
+}
 
 template <typename IdT>
 __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint32_t smem, int32_t smem_bytes,
@@ -755,11 +762,12 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
 {
     if (sizeof(IdT) != 2)
         return false;
-    const int32_t cap = (smem_bytes / kKahnBytesPerNode) & ~7;
+    const int32_t cap = kahn_smem_nodes(smem_bytes);
     if (node_count > cap)
         return false;
     const uint32_t rec   = smem;           // uint2[cap]: x = edge0 | edge1 << 16, y = edge2 | out-degree << 16 | in-degree << 24
-    const uint32_t queue = rec + 8 * cap;  // u16[cap]
+    const uint32_t queue = rec + 8 * cap;  // u16[kKahnQueueEntries], a ring indexed by pop / push counts
+    constexpr uint32_t kQMask = kKahnQueueEntries - 1;
     const unsigned lt    = (1u << lane) - 1u;
     int32_t tail         = 0;
 #pragma unroll 2
@@ -779,17 +787,20 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
             source = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
+        if (tail + __popc(mask) > kKahnQueueEntries) // more sources than the ring holds (uniform; nothing written yet)
+            return false;
         if (source)
             sts_u16(queue + 2 * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
         tail += __popc(mask);
     }
     __syncwarp();
+    int32_t ok = 1;
     if (lane == 0)
     {
-        uint32_t head_a = queue;            // address of the queue head
-        uint32_t tail_a = queue + 2 * tail; // address one past the queue tail
-        uint32_t node   = lds_u16(head_a);  // a graph always has a source
-
+        // sorted[] and node_id_to_pos[] are written as nodes leave the queue (nothing waits for these stores)
+        uint32_t head   = 0;                                   // nodes popped so far == rank of the next node
+        uint32_t pushed = static_cast<uint32_t>(tail);         // nodes queued so far
+        IdT* sorted_out = g.sorted;
         // visit(child): one in-edge of child is satisfied; queue it when it was the last one
 #define POA_KAHN_VISIT(child_expr)                                  \
     {                                                               \
@@ -799,14 +810,17 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         sts_u8(da_, c_);                                            \
         if (c_ == 0)                                                \
         {                                                           \
-            sts_u16(tail_a, child_);                                \
-            tail_a += 2;                                            \
+            sts_u16(queue + 2 * (pushed & kQMask), child_);         \
+            pushed++;                                               \
         }                                                           \
     }
         while (true)
         {
-            const uint2 v     = lds_v2(rec + 8 * node);
-            const uint32_t oc = (v.y >> 16) & 0xffu;
+            const uint32_t node = lds_u16(queue + 2 * (head & kQMask)); // a graph always has a source
+            const uint2 v       = lds_v2(rec + 8 * node);
+            *sorted_out++       = static_cast<IdT>(node);
+            g.pos[node]         = static_cast<IdT>(head);
+            const uint32_t oc   = (v.y >> 16) & 0xffu;
             if (oc > 0)
                 POA_KAHN_VISIT(v.x & 0xffffu)
             if (oc > 1)
@@ -817,22 +831,20 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
                 for (uint32_t e = 3; e < oc; e++)
                     POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, e)))
             }
-            head_a += 2;
-            if (head_a >= tail_a)
+            head++;
+            if (head == pushed)
                 break;
-            node = lds_u16(head_a);
+            if (pushed - head > kKahnQueueEntries) // the ring was overrun: give up, the caller sorts again
+            {
+                ok = 0;
+                break;
+            }
         }
 #undef POA_KAHN_VISIT
     }
+    ok = __shfl_sync(kFull, ok, 0);
     __syncwarp();
-    for (int32_t i = lane; i < node_count; i += 32)
-    {
-        const int32_t n = static_cast<int32_t>(lds_u16(queue + 2 * i));
-        g.sorted[i]     = static_cast<IdT>(n);
-        g.pos[n]        = static_cast<IdT>(i);
-    }
-    __syncwarp();
-    return true;
+    return ok != 0;
 }
 
 // SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.

@@ -44,14 +44,18 @@ constexpr int32_t kRowBlocks    = kFastRowWords / 4;             // 35
 constexpr int32_t kPadBlock     = kRowBlocks - 1;                // last block of a row, always at the sentinel
 constexpr int32_t kNegT         = -30000; // tilted-domain stand-in for the reference's sentinel class
 constexpr int32_t kNegThreshold = -25000; // anything at or below is sentinel class
-constexpr int32_t kRingRows     = 16;     // power of two
+#ifndef POA_RING_ROWS
+#define POA_RING_ROWS 8
+#endif
+constexpr int32_t kRingRows     = POA_RING_ROWS; // power of two; predecessors further back are read through L2
 constexpr int32_t kRingBytes    = kRingRows * kFastRowWords * 4;
 constexpr int32_t kTileRows     = 64; // traceback tile: rows x columns of plain int16 tilted scores
 constexpr int32_t kTileCols     = 48; // columns the walk may use; a tile row also has 8 cells of slack on either side
 constexpr int32_t kTileRowBytes = (kTileCols + 16) * 2;
 constexpr int32_t kTileItems    = kTileCols / 8 + 1; // 16-byte blocks of a score row that can overlap the columns
 static_assert(kRowBlocks == 35, "row layout");
-static_assert(kTileRows * kTileRowBytes + kTileRows * 8 <= kRingBytes, "the tile reuses the ring's memory");
+constexpr int32_t kTileAndDescBytes = kTileRows * kTileRowBytes + kTileRows * 8;
+static_assert((kRingRows & (kRingRows - 1)) == 0 && kRingRows >= 4, "ring rows are addressed with a mask");
 
 __device__ __forceinline__ uint32_t pack2(int32_t lo, int32_t hi)
 {
@@ -746,8 +750,15 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
     if (fast_fill<IdT>(g, node_count, read, read_len, scores, band, gap, mismatch, match, smem, smem_bytes, lane,
                        start_row, score_out) == kFastNotTaken)
         return kFastNotTaken;
-    return fast_traceback<IdT>(g, node_count, nullptr, read_len, scores, gap, mismatch, match, smem,
-                               smem + kRingBytes, start_row, lane);
+    // the tile reuses the ring's memory; the read stays where the fill staged it unless the tile would cover it
+    if (kTileAndDescBytes <= kRingBytes)
+        return fast_traceback<IdT>(g, node_count, nullptr, read_len, scores, gap, mismatch, match, smem,
+                                   smem + kRingBytes, start_row, lane);
+    if (smem_bytes < kTileAndDescBytes + read_len)
+        return kFastNotTaken;
+    __syncwarp();
+    return fast_traceback<IdT>(g, node_count, read, read_len, scores, gap, mismatch, match, smem,
+                               smem + kTileAndDescBytes, start_row, lane);
 }
 
 } // namespace poa_b200

@@ -22,10 +22,13 @@ namespace poa_b200
 
 constexpr int32_t kFillWarpsPerBlock  = 4;
 constexpr int32_t kGraphWarpsPerBlock = 4;
-constexpr int32_t kTileBytes          = kTileRows * (kTileRowBytes + 8); // traceback tile + its row descriptors
+constexpr int32_t kTileBytes          = kTileAndDescBytes; // traceback tile + its row descriptors
+#ifndef POA_FILL_MIN_BLOCKS
+#define POA_FILL_MIN_BLOCKS 6
+#endif
 
 template <typename ScoreT, typename IdT, bool MSA>
-__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 5) poa_fill_kernel(const KernelParams P)
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
     int32_t lane  = threadIdx.x & 31;
@@ -131,9 +134,10 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
             continue;
         // two launches per step, differing in scratch size: each window goes to the one its graph fits (outgrowing
         // the scratch is legal, the sort and the consensus then run out of global memory)
-        if ((st.node_count + kClassMargin > P.class_cap) != (P.phase_class == 1))
-            continue;
         const WindowDesc wd = P.windows[w];
+        const int32_t fits  = (s >= wd.n_reads - 1) ? P.class_cap_final : P.class_cap; // last read: consensus too
+        if ((st.node_count + kClassMargin > fits) != (P.phase_class == 1))
+            continue;
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         const int32_t* rlen = P.read_len + wd.read_off;
 
