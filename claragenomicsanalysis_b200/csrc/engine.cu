@@ -100,6 +100,10 @@ T* carve(uint8_t*& cursor, int64_t count)
 
 struct PhaseTimeline;
 
+// 0: phase-split schedule wherever it applies (unless CUDAPOA_B200_SCHEDULE=fused), 1: always the single launch,
+// 2: phase-split regardless of the environment.  Process-wide; set through cudapoa_b200_debug_set_schedule.
+static std::atomic<int32_t> g_schedule_override{0};
+
 class B200Batch : public Batch, public EngineStatsSource
 {
 public:
@@ -565,7 +569,8 @@ bool B200Batch::launch_split(KernelParams& P)
         const char* env = std::getenv("CUDAPOA_B200_SCHEDULE");
         return env != nullptr && std::strcmp(env, "fused") == 0;
     }();
-    if (!banded_ || adaptive_ || fused_by_env || plan_.size32)
+    const int32_t mode = g_schedule_override.load();
+    if (!banded_ || adaptive_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
         return false;
     int32_t max_reads = 1;
     for (int32_t i = 0; i < poa_count_; i++)
@@ -1105,4 +1110,9 @@ extern "C" int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, 
     if (ms_out != nullptr)
         *ms_out = best;
     return static_cast<int32_t>(e);
+}
+
+extern "C" void cudapoa_b200_debug_set_schedule(int32_t mode)
+{
+    claraparabricks::genomeworks::cudapoa::g_schedule_override.store(mode);
 }

@@ -199,6 +199,12 @@ int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* ins
  * iterations in milliseconds, measured on the batch's own stream; negative if nothing has been staged. */
 double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations);
 
+/* Native library only (tests, A/B measurements): how banded batches are scheduled on the device from now on, process
+ * wide.  0 = default (one launch per phase and read -- poa_fill_kernel / poa_graph_kernel -- unless the environment
+ * says CUDAPOA_B200_SCHEDULE=fused), 1 = always the single launch (poa_window_kernel), 2 = always phase-split.
+ * Results are identical either way. */
+void cudapoa_b200_debug_set_schedule(int32_t mode);
+
 /* Native library only: the same device work once more with a CUDA event between the kernel launches.  *fill_ms and
  * *graph_ms receive the time spent in the score-fill launches and in the graph launches (traceback, fusion,
  * topological sort, consensus) of the phase-split schedule; returns the number of launches, negative on error. */

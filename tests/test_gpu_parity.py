@@ -57,6 +57,61 @@ def test_native_matches_live_reference(lib, name):
     assert parity.compare(n, r, case["engine"]["output"]) == []
 
 
+# ---- the two device schedules of a banded batch: one launch per window set, or one launch per phase and read ----------
+BANDED_CASES = sorted(n for n in CASES if CASES[n]["engine"].get("banded", True))
+
+
+@pytest.fixture
+def schedule(lib):
+    """Sets the process-wide schedule override for one test and restores the default afterwards."""
+    def set_mode(mode):
+        lib._dll.cudapoa_b200_debug_set_schedule(int(mode))
+    yield set_mode
+    set_mode(0)
+
+
+@pytest.mark.parametrize("name", BANDED_CASES)
+def test_single_launch_and_phase_split_agree(lib, schedule, name):
+    """poa_window_kernel (mode 1) and poa_fill_kernel + poa_graph_kernel (mode 2) run the same device functions in the
+    same order per window: statuses, outputs, graphs, per-sequence statuses and work counters must be identical, and
+    both must equal the oracle.  The default mode is covered by every other test of this file."""
+    case = CASES[name]
+    eng = case["engine"]
+    ws = case_windows(name)
+    o = parity.run_oracle(ws, want_graphs=True, **eng)
+    got = {}
+    for mode in (1, 2):
+        schedule(mode)
+        got[mode] = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+        assert parity.compare(got[mode], o, eng["output"]) == []
+        launches = sum(s["kernel_launches"] for s in got[mode]["stats"])
+        assert (launches == len(got[mode]["stats"])) == (mode == 1)
+    assert got[1]["status"] == got[2]["status"]
+    assert got[1]["graphs"] == got[2]["graphs"]
+    assert got[1]["seq_status"] == got[2]["seq_status"]
+    for key in ("dp_cells", "graph_rows", "exact_path", "reads_aligned"):
+        assert [s[key] for s in got[1]["stats"]] == [s[key] for s in got[2]["stats"]]
+
+
+def test_phase_split_many_windows_property(lib, schedule):
+    """Size-independent property at a size the oracle does not reach: 4096 windows, every 512th input repeated, give
+    identical outputs for identical inputs whatever warp, launch class or schedule handled them."""
+    base = generate_windows(512, start_index=7000, template_length=400, n_reads=24)
+    ws = base.tile(4096)
+    eng = dict(max_seq=512, max_reads=24, band=256, banded=True, output="consensus")
+    res = {}
+    for mode in (1, 2):
+        schedule(mode)
+        res[mode] = parity.run_abi(lib, ws, max_mem=16 << 30, **eng)
+        r = res[mode]
+        assert r["status"] == [0] * 4096
+        for w in range(512, 4096):
+            assert r["consensus"][w] == r["consensus"][w % 512]
+            assert list(r["coverage"][w]) == list(r["coverage"][w % 512])
+    assert res[1]["consensus"] == res[2]["consensus"]
+    assert [list(c) for c in res[1]["coverage"]] == [list(c) for c in res[2]["coverage"]]
+
+
 # ---- Batch API behaviour, after cudapoa/tests/Test_CudapoaBatch.cu:66-199 -----------------------------------------
 def test_initialize_and_zero_memory(lib):
     b = CudaPoaBatch(5, 1024, MEM, lib=lib)
