@@ -70,22 +70,32 @@ __device__ __forceinline__ int32_t hi16(uint32_t v)
     return static_cast<int16_t>(v >> 16);
 }
 
-// Real tilted scores stay inside [-20000, 30000] for this alignment; sentinel-class values stay below -25000.
-__device__ __forceinline__ bool fast_path_eligible(int32_t node_count, int32_t read_len, int32_t band, int32_t gap,
-                                                   int32_t mismatch, int32_t match)
+// Which packed formulation serves this alignment.
+//   0    real tilted scores provably stay inside [-20000, 30000]; sentinel-class values stay below -25000.
+//   > 0  longer windows: scores of row r are stored relative to beta * band_start(r) ("rebased"), which follows the
+//        score's growth along the band; the range [kRealLo, kRealHi] is then checked row by row during the fill and
+//        the exact path takes over when a row leaves it.  beta is a slope between the tilted score's extremes
+//        (-gap per column for a run of poor matches, match - gap for perfect ones).
+//   < 0  not eligible.
+constexpr int32_t kRealLo = -16000;
+constexpr int32_t kRealHi = 28000;
+constexpr int32_t kNegAbs = -(1 << 30); // sentinel class once the row offset has been added back (rebased rows)
+
+__device__ __forceinline__ int32_t fast_path_beta(int32_t node_count, int32_t read_len, int32_t band, int32_t gap,
+                                                  int32_t mismatch, int32_t match)
 {
     if (band != kFastBand || gap >= 0 || match <= 0)
-        return false;
+        return -1;
     const int32_t a = max(max(-gap, abs(mismatch)), match);
-    if (a > 127)
-        return false;
-    if (a * (node_count + read_len + 2) > 20000)
-        return false;
-    if ((match - gap) * (read_len + 2) > 30000)
-        return false;
-    if (node_count + 1 >= 32768)
-        return false;
-    return true;
+    if (a > 127 || node_count + 1 >= 32768)
+        return -1;
+    if (a * (node_count + read_len + 2) <= 20000 && (match - gap) * (read_len + 2) <= 30000)
+        return 0;
+    const int32_t beta = -gap + (5 * match) / 8;
+    // the offset between two rows whose bands overlap must leave real scores real, and a row's own spread must fit
+    if (beta > 30 || (match - gap) * (kFastBand + 16) > 12000)
+        return -1;
+    return beta;
 }
 
 // Per-row descriptors, three 32-bit words in three global arrays of stride g.M + 40:
@@ -134,6 +144,18 @@ __device__ __forceinline__ int32_t tilted_score_global(const uint32_t* rows, int
     return (t <= kNegThreshold) ? kNegT : t;
 }
 
+// The same cell with the row's offset added back (rebased rows, beta > 0): an int32 that compares across rows; the
+// sentinel class becomes kNegAbs.  beta == 0: tilted_score_global.
+__device__ __forceinline__ int32_t tilted_score_abs(const uint32_t* rows, int32_t r, int32_t column, int32_t beta)
+{
+    const int32_t t = tilted_score_global(rows, r, column);
+    if (beta == 0)
+        return t;
+    if (t == kNegT)
+        return kNegAbs;
+    return t + beta * static_cast<int32_t>(__ldcg(rows + r * kFastRowWords));
+}
+
 // Load the traceback tile: rows tile_r0 .. tile_r0 + kTileRows - 1, absolute columns tile_c0 .. tile_c0 + kTileCols - 1
 // (tile_c0 = 1 mod 4), as plain int16 tilted scores indexed by absolute column: cell (row, column) lives at
 //   tile + (row - tile_r0) * kTileRowBytes + 2 * (column - tile_c0 + 8).
@@ -143,7 +165,7 @@ __device__ __forceinline__ int32_t tilted_score_global(const uint32_t* rows, int
 // tile_desc.  All lanes; loads are issued in groups of seven per lane before any of them is consumed.
 __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& rd, uint32_t tile, uint32_t tile_desc,
                                           int32_t tile_r0, int32_t tile_c0, float gradient, int32_t max_column,
-                                          int32_t lane)
+                                          int32_t lane, int32_t beta)
 {
     constexpr int32_t kPerLane = kTileRows * kTileItems / 32; // 14
     constexpr int32_t kGroup   = 7;
@@ -192,6 +214,8 @@ __device__ __forceinline__ void load_tile(const uint32_t* rows, const RowDesc& r
     for (int32_t u = 0; u < kTileRows / 32; u++)
     {
         sts_v2(tile_desc + 8u * (lane + 32 * u), dsc[u]);
+        // the row's score offset (rebased rows) in the first, otherwise unused, bytes of the tile row
+        sts_u32(tile + static_cast<uint32_t>((lane + 32 * u) * kTileRowBytes), static_cast<uint32_t>(beta) * lead[u].x);
         // left boundary: the cell at column == band start
         const int32_t x = static_cast<int32_t>(lead[u].x) - tile_c0;
         if (static_cast<uint32_t>(x) < static_cast<uint32_t>(kTileCols))
@@ -212,13 +236,15 @@ __device__ __forceinline__ int32_t fast_fill_smem_bytes(int32_t read_len)
 template <typename IdT>
 __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                              int16_t* scores, int32_t band, int32_t gap, int32_t mismatch, int32_t match,
-                             uint32_t smem, int32_t smem_bytes, int32_t lane, int32_t& start_row,
+                             uint32_t smem, int32_t smem_bytes, int32_t lane, int32_t& start_row, int32_t& beta_out,
                              int32_t* score_out = nullptr)
 {
     // shared-memory scratch: [ring of recent rows | read, zero padded]
     const int32_t rd_bytes = (read_len + kFastBand + 8 + 15) & ~15;
-    if (!fast_path_eligible(node_count, read_len, band, gap, mismatch, match) || smem_bytes < kRingBytes + rd_bytes)
+    const int32_t beta     = fast_path_beta(node_count, read_len, band, gap, mismatch, match);
+    if (beta < 0 || smem_bytes < kRingBytes + rd_bytes)
         return kFastNotTaken;
+    beta_out = beta;
     uint32_t* rows      = reinterpret_cast<uint32_t*>(scores);
     const uint32_t ring = smem;            // shared addresses from here on
     const uint32_t rd   = ring + kRingBytes;
@@ -444,6 +470,20 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
                     left_best           = max(left_best, hi16(lead.w));
                 }
                 min_d = min(min_d, d);
+                if (beta != 0 && d != 0)
+                {
+                    // rebased rows: the predecessor's scores are relative to its own band start, beta * d below this
+                    // row's.  Sentinel-class operands are lifted first so that the subtraction cannot wrap; real ones
+                    // (>= kRealLo) are above the lift for every shift at which the bands still overlap.
+                    const int32_t bd  = min(beta * d, 8000);
+                    const uint32_t fl = pack2(kNegT + bd, kNegT + bd);
+                    const uint32_t c2 = pack2(-bd, -bd);
+                    V0                = __vadd2(__vmaxs2(V0, fl), c2);
+                    V1                = __vadd2(__vmaxs2(V1, fl), c2);
+                    V2                = __vadd2(__vmaxs2(V2, fl), c2);
+                    V3                = __vadd2(__vmaxs2(V3, fl), c2);
+                    D0                = __vadd2(__vmaxs2(D0, fl), c2);
+                }
                 S[0]  = __viaddmax_s16x2(D0, Q[0], __viaddmax_s16x2(V0, gapv, S[0]));
                 S[1]  = __viaddmax_s16x2(V0, Q[1], __viaddmax_s16x2(V1, gapv, S[1]));
                 S[2]  = __viaddmax_s16x2(V1, Q[2], __viaddmax_s16x2(V2, gapv, S[2]));
@@ -500,6 +540,22 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
             out.y = __vimax3_s16x2(S[1], cb, tl);
             out.z = __vimax3_s16x2(S[2], cb, tl);
             out.w = __vimax3_s16x2(S[3], cb, tl);
+            if (beta != 0)
+            {
+                // rebased rows carry no a-priori range: every stored cell must be sentinel class or inside
+                // [kRealLo, kRealHi].  Cells grow along the row, so the lane's first and last cell decide the common case.
+                const bool lane_ok = lo16(out.x) >= kRealLo && hi16(out.w) <= kRealHi;
+                if (!__all_sync(kFull, lane_ok))
+                {
+                    auto bad = [](uint32_t reg) {
+                        const int32_t lo = lo16(reg), hi = hi16(reg);
+                        return (lo > kNegThreshold && lo < kRealLo) || lo > kRealHi || (hi > kNegThreshold && hi < kRealLo) ||
+                               hi > kRealHi;
+                    };
+                    if (__any_sync(kFull, bad(out.x) || bad(out.y) || bad(out.z) || bad(out.w)))
+                        return kFastNotTaken;
+                }
+            }
             uint4* this_row      = reinterpret_cast<uint4*>(rows + r * kFastRowWords);
             const uint32_t rrow  = ring + static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
             __stcg(this_row + 1 + lane, out);
@@ -519,12 +575,16 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
 
     // sink selection: first strict maximum in row order over rows of nodes without out-edges, column read_len.
     // All candidates share the column, so tilted scores compare like the scores themselves.
-    int32_t best = INT16_MIN, best_row = 0;
+    // (rebased rows: offsets added back; a sink row whose band misses that column cannot be ranked here)
+    const int32_t best_floor = (beta == 0) ? INT16_MIN : INT32_MIN;
+    int32_t best = best_floor, best_row = 0;
+    bool unranked = false;
     for (int32_t r = 1 + lane; r <= node_count; r += 32)
     {
         if (desc.d0[r] & (1u << 14))
         {
-            const int32_t s = tilted_score_global(rows, r, read_len);
+            const int32_t s = tilted_score_abs(rows, r, read_len, beta);
+            unranked |= (beta != 0 && s == kNegAbs);
             if (s > best)
             {
                 best     = s;
@@ -545,11 +605,13 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
         }
     }
 
-    const int32_t i0 = (best > INT16_MIN) ? best_row : 0;
+    if (__any_sync(kFull, unranked))
+        return kFastNotTaken;
+    const int32_t i0 = (best > best_floor) ? best_row : 0;
     if (tilted_score_global(rows, i0, read_len) <= kNegThreshold)
         return kFastNotTaken;
     if (score_out != nullptr) // alignment score, un-tilted (the start cell is a real score here)
-        *score_out = tilted_score_global(rows, i0, read_len) + gap * read_len;
+        *score_out = tilted_score_abs(rows, i0, read_len, beta) + gap * read_len;
     start_row = i0;
     return 0;
 }
@@ -562,11 +624,13 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
 // "T[i][j] == T[i][j-1]".  This is the reference's decision as long as the cell the walk stands on is a real
 // score (see tilted_score_global); it is from the first cell on, or the exact path took over.
 // g.aln_node[] first receives ROW indices (0: inserted base); they become node ids in a parallel pass below.
+// REBASED (beta > 0, see fast_path_beta): stored scores are relative to beta * band start of their row; the walk adds
+// the offset back (kept in the first bytes of every tile row) and compares int32 values, sentinel class = kNegAbs.
 // Returns the alignment length, or -1 when the walk exceeds the reference's step limit.
-template <typename IdT>
-__device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
-                                  int16_t* scores, int32_t gap, int32_t mismatch, int32_t match, uint32_t tile,
-                                  uint32_t rd, int32_t start_row, int32_t lane)
+template <typename IdT, bool REBASED>
+__device__ int32_t fast_traceback_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                                       int16_t* scores, int32_t gap, int32_t mismatch, int32_t match, uint32_t tile,
+                                       uint32_t rd, int32_t start_row, int32_t lane, int32_t beta)
 {
     uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
     asm volatile("" : "+l"(rows)); // keep the pointer in registers: recomputing it inside the walk costs more
@@ -593,7 +657,7 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
     {
         const int32_t tile_r0 = i - (kTileRows - 1);
         const int32_t tile_c0 = ((j + 3) & ~3) + 1 - kTileCols; // columns tile_c0 .. tile_c0 + 47 include j
-        load_tile(rows, desc, tile, tile_desc, tile_r0, tile_c0, gradient, max_column, lane);
+        load_tile(rows, desc, tile, tile_desc, tile_r0, tile_c0, gradient, max_column, lane, REBASED ? beta : 0);
         if (lane == 0)
         {
             const int32_t row_floor = (tile_r0 <= 0) ? 0 : tile_r0 + 12; // leave before predecessors fall out
@@ -601,8 +665,14 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
             auto cell = [&](int32_t row, int32_t column) -> int32_t {
                 const int32_t tr = row - tile_r0;
                 if (tr >= 0)
-                    return lds_s16(tile + static_cast<uint32_t>(tr * kTileRowBytes + 2 * (column - tile_c0 + 8)));
-                return tilted_score_global(rows, row, column);
+                {
+                    const int32_t raw = lds_s16(tile + static_cast<uint32_t>(tr * kTileRowBytes + 2 * (column - tile_c0 + 8)));
+                    if (!REBASED)
+                        return raw;
+                    return (raw <= kNegThreshold) ? kNegAbs
+                                                  : raw + static_cast<int32_t>(lds_u32(tile + static_cast<uint32_t>(tr * kTileRowBytes)));
+                }
+                return tilted_score_abs(rows, row, column, REBASED ? beta : 0);
             };
             int32_t sij = cell(i, j);
             // addresses of descriptor(row) and cell(row, column) as base + 8 * row and base + kTileRowBytes * row +
@@ -610,6 +680,7 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
             const uint32_t desc_base = tile_desc - 8u * static_cast<uint32_t>(tile_r0);
             const uint32_t cell_base = tile + 2u * static_cast<uint32_t>(8 - tile_c0) -
                                        static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(tile_r0);
+            const uint32_t row_base = tile - static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(tile_r0);
             const int32_t fast_row_floor = max(row_floor, 1);
             const int32_t fast_col_floor = max(tile_c0, 0);
             while (!(i == 0 && j == 0) && loops < limit && i >= row_floor && j > tile_c0)
@@ -627,8 +698,14 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
                         if (p0 < tile_r0)
                             break;
                         const int32_t cost = ((meta & 0xff) == lds_u8(rd + fj - 1)) ? pd_m : pd_x;
-                        const int32_t h    = lds_s16(cell_base + static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(p0) +
-                                                  2u * static_cast<uint32_t>(fj - 1));
+                        int32_t h          = lds_s16(cell_base + static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(p0) +
+                                            2u * static_cast<uint32_t>(fj - 1));
+                        if (REBASED)
+                        {
+                            if (h <= kNegThreshold)
+                                break;
+                            h += static_cast<int32_t>(lds_u32(row_base + static_cast<uint32_t>(kTileRowBytes) * static_cast<uint32_t>(p0)));
+                        }
                         if (fs != h + cost)
                             break;
                         *out-- = static_cast<IdT>(fi);
@@ -739,6 +816,19 @@ __device__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const
     return aligned;
 }
 
+template <typename IdT>
+__device__ __forceinline__ int32_t fast_traceback(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
+                                                  int32_t read_len, int16_t* scores, int32_t gap, int32_t mismatch,
+                                                  int32_t match, uint32_t tile, uint32_t rd, int32_t start_row,
+                                                  int32_t lane, int32_t beta)
+{
+    if (beta != 0)
+        return fast_traceback_impl<IdT, true>(g, node_count, read, read_len, scores, gap, mismatch, match, tile, rd,
+                                              start_row, lane, beta);
+    return fast_traceback_impl<IdT, false>(g, node_count, read, read_len, scores, gap, mismatch, match, tile, rd,
+                                           start_row, lane, 0);
+}
+
 // Both halves back to back (the single-launch kernel): the tile reuses the ring's memory.
 template <typename IdT>
 __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
@@ -746,19 +836,19 @@ __device__ int32_t align_fast_banded16(const Graph<IdT>& g, int32_t node_count, 
                                        int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
                                        int32_t lane, int32_t* score_out = nullptr)
 {
-    int32_t start_row = 0;
+    int32_t start_row = 0, beta = 0;
     if (fast_fill<IdT>(g, node_count, read, read_len, scores, band, gap, mismatch, match, smem, smem_bytes, lane,
-                       start_row, score_out) == kFastNotTaken)
+                       start_row, beta, score_out) == kFastNotTaken)
         return kFastNotTaken;
     // the tile reuses the ring's memory; the read stays where the fill staged it unless the tile would cover it
     if (kTileAndDescBytes <= kRingBytes)
         return fast_traceback<IdT>(g, node_count, nullptr, read_len, scores, gap, mismatch, match, smem,
-                                   smem + kRingBytes, start_row, lane);
+                                   smem + kRingBytes, start_row, lane, beta);
     if (smem_bytes < kTileAndDescBytes + read_len)
         return kFastNotTaken;
     __syncwarp();
     return fast_traceback<IdT>(g, node_count, read, read_len, scores, gap, mismatch, match, smem,
-                               smem + kTileAndDescBytes, start_row, lane);
+                               smem + kTileAndDescBytes, start_row, lane, beta);
 }
 
 } // namespace poa_b200

@@ -66,6 +66,8 @@ struct PhaseState
     uint32_t rows, exact;
     unsigned long long cells;
     int64_t seq_off;    // offset of the current read's first base from the window's first base
+    int32_t beta;       // row-offset slope of the packed fill that produced the pending alignment (0: none)
+    int32_t reserved;
 };
 constexpr int32_t kAlnPendingTraceback = -3;
 constexpr int32_t kClassMargin         = 64;  // nodes one fusion is allowed to add before the scratch is outgrown

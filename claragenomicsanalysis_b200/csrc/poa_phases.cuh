@@ -86,8 +86,9 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 int32_t aln_len     = kFastNotTaken;
                 int32_t aln_score   = 0;
                 int32_t start_row   = 0;
+                int32_t beta        = 0;
                 if (fast_fill<IdT>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.band, P.gap,
-                                   P.mismatch, P.match, smem, P.smem_per_warp, lane, start_row, &aln_score) == 0)
+                                   P.mismatch, P.match, smem, P.smem_per_warp, lane, start_row, beta, &aln_score) == 0)
                 {
                     aln_len = kAlnPendingTraceback;
                 }
@@ -99,6 +100,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 }
                 st.aln_len   = aln_len;
                 st.start_row = start_row;
+                st.beta      = beta;
                 st.rows += static_cast<uint32_t>(st.node_count);
                 st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(P.band);
             }
@@ -152,7 +154,7 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
                 int16_t* scores = reinterpret_cast<int16_t*>(static_cast<ScoreT*>(P.scores) +
                                                              static_cast<int64_t>(w) * P.banded_score_stride);
                 aln_len = fast_traceback<IdT>(g, st.node_count, seq, len, scores, P.gap, P.mismatch, P.match, smem,
-                                              smem + kTileBytes, st.start_row, lane);
+                                              smem + kTileBytes, st.start_row, lane, st.beta);
             }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {

@@ -37,6 +37,13 @@ CASES = {
     "banded32_msa": dict(
         gen=dict(template_length=1600, n_reads=6), n=4, start=7500,
         engine=dict(max_seq=2048, max_reads=6, band=256, banded=True, output="msa")),
+    # config 4 lengths: the packed fill stores these rows relative to a per-row offset (poa_fast.cuh, fast_path_beta)
+    "banded32_long": dict(
+        gen=dict(template_length=4000, n_reads=10), n=3, start=11000,
+        engine=dict(max_seq=5120, max_reads=10, band=256, banded=True, output="consensus")),
+    "banded32_long_noisy": dict(  # slow score growth: the offset slope overshoots, scores drift downwards
+        gen=dict(template_length=2500, n_reads=8, read_error=0.25, backbone_error=0.15), n=3, start=12000,
+        engine=dict(max_seq=3584, max_reads=8, band=256, banded=True, output="consensus")),
     "full32_consensus": dict(
         gen=dict(template_length=1550, n_reads=5), n=4, start=8000,
         engine=dict(max_seq=2048, max_reads=5, band=256, banded=False, output="consensus")),
