@@ -177,6 +177,7 @@ public:
     int32_t max_poas() const override { return max_poas_; }
     double relaunch(int32_t iterations) override;
     int32_t relaunch_phases(double* fill_ms, double* graph_ms) override;
+    void set_overlapped(bool overlapped) override { overlapped_ = overlapped; }
 
 private:
     void allocate(size_t max_mem);
@@ -251,6 +252,7 @@ private:
     bool launched_          = false;
     int64_t kernel_launches_ = 0; // kernels enqueued by the last generate_poa / relaunch
     PhaseTimeline* timeline_ = nullptr; // set while relaunch_phases() is timing the launches
+    bool overlapped_         = false;   // other batches are in flight on this device (set_overlapped)
     bool timed_             = false;
     int32_t timed_iters_    = 1;
 
@@ -571,6 +573,11 @@ bool B200Batch::launch_split(KernelParams& P)
     }();
     const int32_t mode = g_schedule_override.load();
     if (!banded_ || adaptive_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
+        return false;
+    // A lone batch that does not fill the device about twice over is latency-bound either way, and then one launch
+    // (no per-launch tails) is ~10 % faster; measured crossover on a B200 between 4 736 and 9 472 cfg 2 windows
+    // (tools/schedule_crossover.py).
+    if (mode == 0 && !overlapped_ && poa_count_ < 2 * 16 * sm_count_ + sm_count_)
         return false;
     int32_t max_reads = 1;
     for (int32_t i = 0; i < poa_count_; i++)

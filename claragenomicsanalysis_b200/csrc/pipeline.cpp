@@ -108,6 +108,8 @@ cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int3
                                             static_cast<poa::BandMode>(std::min(std::max(cuda_banded_alignment, 0), 2)));
                 auto* src  = dynamic_cast<poa::EngineStatsSource*>(w.batch.get());
                 w.capacity = src != nullptr ? src->max_poas() : 0;
+                if (src != nullptr)
+                    src->set_overlapped(workers_per_device > 1); // several batches share the device
                 p->workers.push_back(std::move(w));
             }
         }

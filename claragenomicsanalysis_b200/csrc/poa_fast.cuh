@@ -233,18 +233,14 @@ __device__ __forceinline__ int32_t fast_fill_smem_bytes(int32_t read_len)
 // First half of the packed alignment: row descriptors, the fill (every row streamed to the score matrix) and the
 // sink selection.  Returns kFastNotTaken, or 0 with the row the traceback starts from in start_row (uniform over
 // the warp).  The read stays staged at smem + kRingBytes.
-template <typename IdT>
-__device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
-                             int16_t* scores, int32_t band, int32_t gap, int32_t mismatch, int32_t match,
-                             uint32_t smem, int32_t smem_bytes, int32_t lane, int32_t& start_row, int32_t& beta_out,
-                             int32_t* score_out = nullptr)
+template <typename IdT, bool REBASED>
+__device__ int32_t fast_fill_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                                  int16_t* scores, int32_t gap, int32_t mismatch, int32_t match, uint32_t smem,
+                                  int32_t lane, int32_t& start_row, int32_t beta_arg, int32_t* score_out)
 {
     // shared-memory scratch: [ring of recent rows | read, zero padded]
     const int32_t rd_bytes = (read_len + kFastBand + 8 + 15) & ~15;
-    const int32_t beta     = fast_path_beta(node_count, read_len, band, gap, mismatch, match);
-    if (beta < 0 || smem_bytes < kRingBytes + rd_bytes)
-        return kFastNotTaken;
-    beta_out = beta;
+    const int32_t beta     = REBASED ? beta_arg : 0; // a compile-time zero in the instance the short windows use
     uint32_t* rows      = reinterpret_cast<uint32_t*>(scores);
     const uint32_t ring = smem;            // shared addresses from here on
     const uint32_t rd   = ring + kRingBytes;
@@ -614,6 +610,24 @@ __device__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint
         *score_out = tilted_score_abs(rows, i0, read_len, beta) + gap * read_len;
     start_row = i0;
     return 0;
+}
+
+template <typename IdT>
+__device__ __forceinline__ int32_t fast_fill(const Graph<IdT>& g, int32_t node_count, const uint8_t* read,
+                                             int32_t read_len, int16_t* scores, int32_t band, int32_t gap,
+                                             int32_t mismatch, int32_t match, uint32_t smem, int32_t smem_bytes,
+                                             int32_t lane, int32_t& start_row, int32_t& beta_out,
+                                             int32_t* score_out = nullptr)
+{
+    const int32_t beta = fast_path_beta(node_count, read_len, band, gap, mismatch, match);
+    if (beta < 0 || smem_bytes < fast_fill_smem_bytes(read_len))
+        return kFastNotTaken;
+    beta_out = beta;
+    if (beta != 0)
+        return fast_fill_impl<IdT, true>(g, node_count, read, read_len, scores, gap, mismatch, match, smem, lane,
+                                         start_row, beta, score_out);
+    return fast_fill_impl<IdT, false>(g, node_count, read, read_len, scores, gap, mismatch, match, smem, lane,
+                                      start_row, 0, score_out);
 }
 
 // Second half: traceback (cudapoa_nw_banded.cuh:386-480) from (start_row, read_len): lane 0 walks, the warp reloads
