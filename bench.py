@@ -465,9 +465,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--windows", type=int, default=18944, help="windows per step per GPU (8 waves of 148 x 16)")
-    ap.add_argument("--chunk", type=int, default=2368, help="end-to-end leg: windows per batch round")
-    ap.add_argument("--workers", type=int, default=6, help="end-to-end leg: host threads / streams / batches")
-    ap.add_argument("--worker-mem-gb", type=float, default=8.0)
+    ap.add_argument("--chunk", type=int, default=1184, help="end-to-end leg: windows per batch round")
+    ap.add_argument("--workers", type=int, default=8, help="end-to-end leg: host threads / streams / batches")
+    ap.add_argument("--worker-mem-gb", type=float, default=6.0)
     ap.add_argument("--distinct", type=int, default=1024, help="distinct generated windows (tiled to --windows)")
     ap.add_argument("--max-mem-gb", type=float, default=64.0)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

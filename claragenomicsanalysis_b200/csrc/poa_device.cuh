@@ -741,12 +741,10 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 }
 
 // The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first three
-// out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency, all lanes write sorted[] and
-// node_id_to_pos[] back.  Returns false (nothing written) when the graph does not fit the scratch; the caller then
-// uses topsort_kahn.  All 32 lanes call this.
-#ifndef POA_AB
-#define POA_AB 0
-#endif
+// out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency and writes sorted[] and
+// node_id_to_pos[] as nodes leave the queue.  Returns false when the graph does not fit the scratch or the queue
+// ring is overrun (sorted[] / node_id_to_pos[] may then be partly written); the caller then runs topsort_kahn, which
+// rewrites both.  All 32 lanes call this.
 constexpr int32_t kKahnBytesPerNode = 8;   // record {edge0, edge1, edge2, out-degree, remaining in-degree}
 constexpr int32_t kKahnQueueEntries = 128; // the FIFO is a ring: a POA graph's frontier is a handful of nodes
 
