@@ -49,7 +49,8 @@ def main():
             doc["coverage"] = [list(map(int, c)) for c in r["coverage"]]
         else:
             doc["msa"] = r["msa"]
-        doc["graph_nodes"] = [g[0].decode("latin1") for g in r["graphs"]]
+        doc["graph_nodes"] = [g[0].decode("latin1") for g in r["graphs"][:4]]
+        doc["graph_node_count"] = [len(g[0]) for g in r["graphs"]]
         doc["graph_edges"] = [[list(e) for e in g[1]] for g in r["graphs"][:4]]
         doc["graph_edge_count"] = [len(g[1]) for g in r["graphs"]]
         path = os.path.join(out_dir, "reference_%s.json" % name)
