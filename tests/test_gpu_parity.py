@@ -93,6 +93,31 @@ def test_single_launch_and_phase_split_agree(lib, schedule, name):
         assert [s[key] for s in got[1]["stats"]] == [s[key] for s in got[2]["stats"]]
 
 
+@pytest.mark.parametrize("output", ["consensus", "msa"])
+def test_ragged_batch_both_schedules(lib, schedule, output):
+    """Windows of one batch finish at different launches of the phase-split schedule: read counts 1 .. 14 mixed with
+    lengths 60 .. 600, a window whose graph outgrows max_nodes (status 4) and one that only has a backbone.  Both
+    schedules must reproduce the oracle window by window."""
+    rng = random.Random(20261105)
+    pool = generate_windows(40, start_index=15000, template_length=(60, 600), n_reads=14)
+    wins = []
+    for i in range(len(pool)):
+        reads = pool.window(i)
+        wins.append(reads[:rng.choice([1, 2, 3, 5, 9, 14])])
+    # reads over disjoint alphabets: every base becomes a new node, the node limit is reached before the last read
+    junk = ["".join(rng.choice("ACGTEFHIJKLMNOPQRSUVWXYZ"[4 * (k % 6):4 * (k % 6) + 4]) for _ in range(500)) for k in range(12)]
+    wins.insert(7, junk)
+    ws = WindowSet.from_lists(wins)
+    eng = dict(max_seq=640, max_reads=14, band=256, banded=True, output=output)
+    o = parity.run_oracle(ws, want_graphs=True, **eng)
+    assert len(set(o["status"])) > 1  # the case does contain a failing window
+    for mode in (1, 2):
+        schedule(mode)
+        n = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+        assert parity.compare(n, o, output) == []
+        assert [int(s) for s in n["status"]] == [int(s) for s in o["status"]]
+
+
 def test_phase_split_many_windows_property(lib, schedule):
     """Size-independent property at a size the oracle does not reach: 4096 windows, every 512th input repeated, give
     identical outputs for identical inputs whatever warp, launch class or schedule handled them."""
