@@ -59,6 +59,7 @@ class ClockSampler:
     def __init__(self, device):
         self.device = device
         self.rows = []
+        self.stamps = []
         self.proc = None
         self.thread = None
 
@@ -78,25 +79,40 @@ class ClockSampler:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) >= 8:
                 self.rows.append(parts)
+                self.stamps.append(time.time())
+
+    def mark(self):
+        """The timed region starts now (the sampler itself is started earlier: nvidia-smi takes a second or more to
+        produce its first line on a box with many GPUs)."""
+        self.t_begin = time.time()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t_end = time.time()
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
-        pw = [float(r[3]) for r in self.rows if r[3].replace(".", "").isdigit()]
+        t_begin = getattr(self, "t_begin", 0.0)
+        rows = [r for r, t in zip(self.rows, self.stamps) if t_begin <= t <= t_end + 0.05]
+        window = "timed region"
+        if not rows:  # region shorter than the sampling period: the warm-up steps just before ran the same load
+            rows = [r for r, t in zip(self.rows, self.stamps) if t >= t_begin - 2.0]
+            window = "last 2 s of warm-up + timed region (same load; no sample fell inside the timed region)"
+        sm = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
+        pw = [float(r[3]) for r in rows if r[3].replace(".", "").isdigit()]
         reasons = set()
-        for r in self.rows:
+        self.window = window
+        for r in rows:
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons),
+                "window": self.window}
 
 
 def measured_peaks():
@@ -233,6 +249,8 @@ def run_native(args, rank, world, local_rank):
         batch.generate_poa()
         batch.fetch("consensus")
 
+    sampler = ClockSampler(device)
+    sampler.start()  # early: nvidia-smi needs seconds to start on a box with many GPUs; samples are windowed below
     # first pass: stage, run, fetch -- also the correctness gate of this run
     e2e_step()
     statuses = batch.result_statuses()
@@ -243,12 +261,11 @@ def run_native(args, rank, world, local_rank):
     if n_ok != n_win:
         raise RuntimeError("only %d of %d windows succeeded" % (n_ok, n_win))
 
-    sampler = ClockSampler(device)
     # ---- resident leg: inputs already in HBM, K launches timed with CUDA events on the batch's stream ----
     for _ in range(max(args.warmup, 3)):
         dll.cudapoa_b200_bench_relaunch(batch._handle, 1)
     barrier()
-    sampler.start()
+    sampler.mark()
     ms_total = dll.cudapoa_b200_bench_relaunch(batch._handle, args.steps)
     barrier()
     clocks = sampler.stop()
