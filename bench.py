@@ -215,9 +215,9 @@ def run_native(args, rank, world, local_rank):
     dll.cudapoa_b200_bench_relaunch.argtypes = [ctypes.c_void_p, ctypes.c_int32]
     dll.cudapoa_b200_debug_dpx_peak.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_double),
                                                 ctypes.POINTER(ctypes.c_double)]
-    dll.cudapoa_b200_bench_relaunch_phases.restype = ctypes.c_int32
-    dll.cudapoa_b200_bench_relaunch_phases.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
-                                                       ctypes.POINTER(ctypes.c_double)]
+    dll.cudapoa_b200_bench_relaunch_timed.restype = ctypes.c_double
+    dll.cudapoa_b200_bench_relaunch_timed.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_double),
+                                                      ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int32)]
 
     device = local_rank
     torch.cuda.set_device(device)
@@ -266,18 +266,21 @@ def run_native(args, rank, world, local_rank):
         dll.cudapoa_b200_bench_relaunch(batch._handle, 1)
     barrier()
     sampler.mark()
-    ms_total = dll.cudapoa_b200_bench_relaunch(batch._handle, args.steps)
+    # the timed region: K steps, CUDA events on the batch's stream around the whole region and between its launches
+    fill_ms = ctypes.c_double(0)
+    graph_ms = ctypes.c_double(0)
+    n_launches = ctypes.c_int32(0)
+    ms_total = dll.cudapoa_b200_bench_relaunch_timed(batch._handle, args.steps, ctypes.byref(fill_ms),
+                                                     ctypes.byref(graph_ms), ctypes.byref(n_launches))
     barrier()
     clocks = sampler.stop()
     if ms_total <= 0:
         raise RuntimeError("relaunch failed: " + lib.error())
     ms_step = max_over_ranks(ms_total / args.steps)
-    # the same step once more with a CUDA event between its launches: time per kernel (outside the timed region)
-    fill_ms = ctypes.c_double(0)
-    graph_ms = ctypes.c_double(0)
-    launches_per_step = dll.cudapoa_b200_bench_relaunch_phases(batch._handle, ctypes.byref(fill_ms), ctypes.byref(graph_ms))
-    if launches_per_step <= 0:
-        raise RuntimeError("relaunch_phases failed: " + lib.error())
+    # per-kernel times of the timed region, per step
+    launches_per_step = n_launches.value // args.steps
+    fill_ms = ctypes.c_double(fill_ms.value / args.steps)
+    graph_ms = ctypes.c_double(graph_ms.value / args.steps)
     batch.fetch("consensus")
     if batch.result_digest() != digest0:
         raise RuntimeError("results changed between launches")
@@ -367,7 +370,7 @@ def run_native(args, rank, world, local_rank):
             "poa_graph_kernel": {"launches": int(launches_per_step) - n_fill, "ms_per_step": graph_ms.value,
                                  "share_of_step": graph_ms.value / phase_ms if phase_ms > 0 else None,
                                  "dram_gb_per_s": (graph_traffic * n_win / (graph_ms.value * 1e-3) / 1e9) if graph_traffic else None},
-            "note": "one extra pass of the step with a CUDA event between launches, rank 0's GPU",
+            "note": "CUDA events between the launches of the timed region, this rank's GPU",
         },
         "roofline": {"bound": "hbm", "kernel": "poa_fill_kernel", "achieved": achieved_gbs, "peak": hbm_peak,
                      "unit": "GB/s", "frac": achieved_gbs / hbm_peak,

@@ -555,6 +555,20 @@ double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations
     return rc == 0 ? ms : -1.0;
 }
 
+double cudapoa_b200_bench_relaunch_timed(cudapoa_b200_batch* batch, int32_t iterations, double* fill_ms,
+                                         double* graph_ms, int32_t* launches)
+{
+    double ms  = -1.0;
+    int32_t rc = guarded([&]() {
+        auto* src = dynamic_cast<poa::EngineStatsSource*>(batch->impl.get());
+        if (src == nullptr)
+            return -1;
+        ms = src->relaunch_timed(iterations, fill_ms, graph_ms, launches);
+        return 0;
+    });
+    return rc == 0 ? ms : -1.0;
+}
+
 int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fill_ms, double* graph_ms)
 {
     int32_t n  = -1;

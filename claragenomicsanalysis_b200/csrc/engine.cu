@@ -177,6 +177,7 @@ public:
     int32_t max_poas() const override { return max_poas_; }
     double relaunch(int32_t iterations) override;
     int32_t relaunch_phases(double* fill_ms, double* graph_ms) override;
+    double relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches) override;
     void set_overlapped(bool overlapped) override { overlapped_ = overlapped; }
 
 private:
@@ -497,11 +498,12 @@ static int32_t consensus_scratch_nodes(int32_t smem)
     return ((smem - kConsStageBytes) / 6) & ~7;
 }
 
-// Optional CUDA events between the launches of one batch (relaunch_phases): kinds[i] tells what ran before events[i + 1].
+// Optional CUDA events between the launches of a batch (relaunch_timed): kinds[i] tells what ran between events[i - 1]
+// and events[i] (0 fill launch, 1 graph launch, -1 anything else: counter reset, the gap between two steps).
 struct PhaseTimeline
 {
     std::vector<cudaEvent_t> events;
-    std::vector<int8_t> kinds; // 0 fill, 1 graph
+    std::vector<int8_t> kinds;
     size_t used = 0;
     void mark(cudaStream_t stream, int kind)
     {
@@ -512,8 +514,7 @@ struct PhaseTimeline
             events.push_back(e);
         }
         GW_CU_CHECK_ERR(cudaEventRecord(events[used++], stream));
-        if (kind >= 0)
-            kinds.push_back(static_cast<int8_t>(kind));
+        kinds.push_back(static_cast<int8_t>(kind));
     }
     ~PhaseTimeline()
     {
@@ -745,39 +746,48 @@ double B200Batch::relaunch(int32_t iterations)
     return static_cast<double>(ms);
 }
 
-int32_t B200Batch::relaunch_phases(double* fill_ms, double* graph_ms)
+double B200Batch::relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches)
 {
     scoped_device_switch dev(device_id_);
-    if (!launched_ || poa_count_ == 0)
-        return -1;
+    if (!launched_ || poa_count_ == 0 || iterations <= 0)
+        return -1.0;
     PhaseTimeline timeline;
     timeline_        = &timeline;
     kernel_launches_ = 0;
     GW_CU_CHECK_ERR(cudaEventRecord(ev_start_, stream_));
-    launch();
+    for (int32_t i = 0; i < iterations; i++)
+        launch();
     GW_CU_CHECK_ERR(cudaEventRecord(ev_stop_, stream_));
     timeline_ = nullptr;
     GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
+    float total = 0.f;
+    GW_CU_CHECK_ERR(cudaEventElapsedTime(&total, ev_start_, ev_stop_));
     double fill = 0.0, graph = 0.0;
     if (timeline.used < 2) // single launch: everything is one kernel
+        fill = total;
+    for (size_t i = 1; i < timeline.used; i++)
     {
+        if (timeline.kinds[i] < 0)
+            continue;
         float ms = 0.f;
-        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, ev_start_, ev_stop_));
-        fill = ms;
-    }
-    for (size_t i = 0; i + 1 < timeline.used; i++)
-    {
-        float ms = 0.f;
-        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, timeline.events[i], timeline.events[i + 1]));
+        GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, timeline.events[i - 1], timeline.events[i]));
         (timeline.kinds[i] == 0 ? fill : graph) += ms;
     }
     if (fill_ms)
         *fill_ms = fill;
     if (graph_ms)
         *graph_ms = graph;
-    timed_       = false;
-    timed_iters_ = 1;
-    return static_cast<int32_t>(kernel_launches_);
+    if (launches)
+        *launches = static_cast<int32_t>(kernel_launches_);
+    timed_       = false; // the next get_* refreshes kernel_ms from these events
+    timed_iters_ = iterations;
+    return static_cast<double>(total);
+}
+
+int32_t B200Batch::relaunch_phases(double* fill_ms, double* graph_ms)
+{
+    int32_t launches = 0;
+    return relaunch_timed(1, fill_ms, graph_ms, &launches) < 0 ? -1 : launches;
 }
 
 void B200Batch::fill_stats(cudapoa_b200_stats* out) const

@@ -25,6 +25,9 @@ public:
     // in the graph launches of the phase-split schedule (a batch on the single launch reports everything as fill_ms).
     // Returns the number of launches timed, < 0 if nothing has been staged.
     virtual int32_t relaunch_phases(double* fill_ms, double* graph_ms) = 0;
+    // relaunch() and relaunch_phases() in one: `iterations` passes with events between the launches; returns the
+    // CUDA-event time of all of them, the sums per kernel in *fill_ms / *graph_ms, the launch count in *launches.
+    virtual double relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches) = 0;
     // Scheduling hint: this batch shares its device with other batches in flight (several streams).  A lone batch of
     // less than about two waves of windows is served faster by the single launch; overlapping batches by the
     // phase-split schedule whatever their size.

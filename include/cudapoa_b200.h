@@ -210,6 +210,12 @@ void cudapoa_b200_debug_set_schedule(int32_t mode);
  * topological sort, consensus) of the phase-split schedule; returns the number of launches, negative on error. */
 int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fill_ms, double* graph_ms);
 
+/* Native library only: bench_relaunch and bench_relaunch_phases in one -- `iterations` passes with a CUDA event between
+ * the launches.  Returns the event time of all passes in milliseconds (negative on error), the time spent in the fill
+ * and in the graph launches in *fill_ms / *graph_ms (sums over the passes) and the number of launches in *launches. */
+double cudapoa_b200_bench_relaunch_timed(cudapoa_b200_batch* batch, int32_t iterations, double* fill_ms,
+                                         double* graph_ms, int32_t* launches);
+
 /* ---- Window pipeline (native library only; no reference counterpart) ------------------------------------------
  * The stream scheduler / sharding layer above the Batch interface (the reference drives several Batch objects from
  * std::async tasks in cudapoa/benchmarks/multi_batch.hpp:157-170; it has no multi-GPU code).  Each worker thread owns

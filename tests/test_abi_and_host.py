@@ -28,7 +28,7 @@ def test_header_symbols_all_exported(lib):
     dll = ctypes.CDLL(_cabi.NATIVE_LIB_PATH)
     for name in sorted(declared):
         assert getattr(dll, "cudapoa_b200_" + name) is not None
-    for extra in ("debug_rcp_table", "debug_dpx_peak", "debug_set_schedule", "bench_relaunch", "bench_relaunch_phases"):
+    for extra in ("debug_rcp_table", "debug_dpx_peak", "debug_set_schedule", "bench_relaunch", "bench_relaunch_phases", "bench_relaunch_timed"):
         assert getattr(dll, "cudapoa_b200_" + extra) is not None
     assert lib.implementation() == b"b200-native"
 
