@@ -70,6 +70,7 @@ struct PhaseState
     int32_t reserved;
 };
 constexpr int32_t kAlnPendingTraceback = -3;
+constexpr int32_t kAlnNeedsExact       = -4;  // the packed fill declined: poa_exact_kernel aligns this read
 constexpr int32_t kClassMargin         = 64;  // nodes one fusion is allowed to add before the scratch is outgrown
 constexpr int32_t kPhaseCounters       = 512; // one window counter per launch of a batch
 

@@ -94,9 +94,9 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 }
                 else
                 {
-                    aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, len, scores, P.band + kBandRowPad,
-                                                             P.band, P.gap, P.mismatch, P.match, lane, &aln_score);
-                    st.exact++;
+                    // the exact-arithmetic alignment runs in a launch of its own (poa_exact_kernel): kept out of this
+                    // kernel, whose registers and instruction cache belong to the packed fill
+                    aln_len = kAlnNeedsExact;
                 }
                 st.aln_len   = aln_len;
                 st.start_row = start_row;
@@ -108,6 +108,44 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
         if (lane == 0)
             *ps = st;
         __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// The reads the packed fill declined (other band widths, scores outside its range, rows decided by sentinel
+// arithmetic): the exact-arithmetic alignment, traceback included.  Launched after every fill launch; a warp that
+// finds nothing to do for a window moves on after one 48-byte load.
+template <typename ScoreT, typename IdT>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(const KernelParams P)
+{
+    int32_t lane = threadIdx.x & 31;
+    asm volatile("" : "+r"(lane));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        if (ps->aln_len != kAlnNeedsExact)
+            continue;
+        PhaseState st       = *ps;
+        const WindowDesc wd = P.windows[w];
+        if (st.status != kStSuccess || st.finalized || s >= wd.n_reads)
+            continue;
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t* rlen = P.read_len + wd.read_off;
+        const uint8_t* seq  = P.bases + wd.base_off + st.seq_off;
+        ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
+        int32_t aln_score   = 0;
+        st.aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, rlen[s], scores, P.band + kBandRowPad, P.band,
+                                                    P.gap, P.mismatch, P.match, lane, &aln_score);
+        st.exact++;
+        if (lane == 0)
+            *ps = st;
+        __syncwarp();
     }
 }
 
