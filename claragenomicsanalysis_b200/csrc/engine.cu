@@ -537,16 +537,19 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
     for (int32_t s = 1; s <= steps; s++)
     {
         P.step          = s;
-        P.next_window   = counters + 4 * (s - 1);
+        P.next_window   = counters + 5 * (s - 1);
         P.smem_per_warp = fill_smem;
         launch_phase(poa_fill_kernel<ScoreT, IdT, MSA>, P, kFillWarpsPerBlock, sm_count, stream);
-        P.next_window   = counters + 4 * (s - 1) + 3;
+        P.next_window   = counters + 5 * (s - 1) + 4;
+        launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
+        launches++;
+        P.next_window   = counters + 5 * (s - 1) + 3;
         P.smem_per_warp = 0;
         launch_phase(poa_exact_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
         launches++;
         if (timeline)
             timeline->mark(stream, 0);
-        P.next_window   = counters + 4 * (s - 1) + 1;
+        P.next_window   = counters + 5 * (s - 1) + 1;
         P.smem_per_warp = graph_smem;
         P.phase_class   = 0;
         launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
@@ -555,7 +558,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
         launches += 2;
         if (two)
         {
-            P.next_window   = counters + 4 * (s - 1) + 2;
+            P.next_window   = counters + 5 * (s - 1) + 2;
             P.smem_per_warp = graph_smem_large;
             P.phase_class   = 1;
             launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
@@ -588,7 +591,7 @@ bool B200Batch::launch_split(KernelParams& P)
     for (int32_t i = 0; i < poa_count_; i++)
         max_reads = std::max(max_reads, windows_h_[i].n_reads);
     const int32_t steps = std::max(max_reads - 1, 1);
-    if (4 * steps > kPhaseCounters)
+    if (5 * steps > kPhaseCounters)
         return false;
     // shared memory per window: the fill needs the row ring and the padded read, the graph phases the traceback
     // tile and the read (the topological sort and the consensus reuse that scratch)

@@ -71,8 +71,9 @@ struct PhaseState
 };
 constexpr int32_t kAlnPendingTraceback = -3;
 constexpr int32_t kAlnNeedsExact       = -4;  // the packed fill declined: poa_exact_kernel aligns this read
+constexpr int32_t kAlnNeedsRebased     = -5;  // long window: poa_fill_rebased_kernel fills this read
 constexpr int32_t kClassMargin         = 64;  // nodes one fusion is allowed to add before the scratch is outgrown
-constexpr int32_t kPhaseCounters       = 512; // one window counter per launch of a batch
+constexpr int32_t kPhaseCounters       = 1024; // one window counter per launch of a batch
 
 struct KernelParams
 {

@@ -86,24 +86,76 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 int32_t aln_len     = kFastNotTaken;
                 int32_t aln_score   = 0;
                 int32_t start_row   = 0;
-                int32_t beta        = 0;
-                if (fast_fill<IdT>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.band, P.gap,
-                                   P.mismatch, P.match, smem, P.smem_per_warp, lane, start_row, beta, &aln_score) == 0)
-                {
+                // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
+                // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
+                // registers and instruction cache of this one belong to the loop the benchmark spends half its time in.
+                const int32_t beta = (P.smem_per_warp >= fast_fill_smem_bytes(len))
+                                         ? fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match)
+                                         : -1;
+                if (beta > 0)
+                    aln_len = kAlnNeedsRebased;
+                else if (beta == 0 &&
+                         fast_fill_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.gap,
+                                                    P.mismatch, P.match, smem, lane, start_row, 0, &aln_score) == 0)
                     aln_len = kAlnPendingTraceback;
-                }
                 else
-                {
-                    // the exact-arithmetic alignment runs in a launch of its own (poa_exact_kernel): kept out of this
-                    // kernel, whose registers and instruction cache belong to the packed fill
                     aln_len = kAlnNeedsExact;
-                }
                 st.aln_len   = aln_len;
                 st.start_row = start_row;
-                st.beta      = beta;
+                st.beta      = 0;
                 st.rows += static_cast<uint32_t>(st.node_count);
                 st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(P.band);
             }
+        }
+        if (lane == 0)
+            *ps = st;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// The packed fill of long windows (rows stored relative to a per-row offset, poa_fast.cuh fast_path_beta), for the
+// reads poa_fill_kernel marked kAlnNeedsRebased.
+template <typename ScoreT, typename IdT>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_rebased_kernel(const KernelParams P)
+{
+    extern __shared__ __align__(16) uint8_t smem_block[];
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        if (ps->aln_len != kAlnNeedsRebased)
+            continue;
+        PhaseState st       = *ps;
+        const WindowDesc wd = P.windows[w];
+        if (st.status != kStSuccess || st.finalized || s >= wd.n_reads)
+            continue;
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t len   = P.read_len[wd.read_off + s];
+        const uint8_t* seq  = P.bases + wd.base_off + st.seq_off;
+        ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
+        int32_t aln_score   = 0;
+        int32_t start_row   = 0;
+        const int32_t beta  = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
+        if (beta > 0 && fast_fill_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.gap,
+                                                  P.mismatch, P.match, smem, lane, start_row, beta, &aln_score) == 0)
+        {
+            st.aln_len   = kAlnPendingTraceback;
+            st.start_row = start_row;
+            st.beta      = beta;
+        }
+        else
+        {
+            st.aln_len = kAlnNeedsExact;
         }
         if (lane == 0)
             *ps = st;
