@@ -533,6 +533,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
         timeline->mark(stream, -1);
     const bool two   = graph_smem_large > graph_smem;
     P.class_cap       = two ? kahn_smem_nodes(graph_smem) : INT32_MAX - kClassMargin;
+    P.lean_class0     = two ? 1 : 0;
     P.class_cap_final = two ? std::min(kahn_smem_nodes(graph_smem), consensus_scratch_nodes(graph_smem)) : P.class_cap;
     for (int32_t s = 1; s <= steps; s++)
     {
@@ -552,7 +553,10 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
         P.next_window   = counters + 5 * (s - 1) + 1;
         P.smem_per_warp = graph_smem;
         P.phase_class   = 0;
-        launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+        if (two)
+            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, true>, P, kGraphWarpsPerBlock, sm_count, stream);
+        else
+            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, false>, P, kGraphWarpsPerBlock, sm_count, stream);
         if (timeline)
             timeline->mark(stream, 1);
         launches += 2;
@@ -561,7 +565,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
             P.next_window   = counters + 5 * (s - 1) + 2;
             P.smem_per_warp = graph_smem_large;
             P.phase_class   = 1;
-            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, false>, P, kGraphWarpsPerBlock, sm_count, stream);
             if (timeline)
                 timeline->mark(stream, 1);
             launches++;

@@ -201,7 +201,9 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
     }
 }
 
-template <typename ScoreT, typename IdT, bool MSA>
+// LEAN: the instance of the small-scratch launch.  It leaves the windows with rebased score rows and the
+// SPOA_ACCURATE order to the other launch (class 1) and does not carry their code.
+template <typename ScoreT, typename IdT, bool MSA, bool LEAN>
 __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
@@ -228,7 +230,9 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
         // the scratch is legal, the sort and the consensus then run out of global memory)
         const WindowDesc wd = P.windows[w];
         const int32_t fits  = (s >= wd.n_reads - 1) ? P.class_cap_final : P.class_cap; // last read: consensus too
-        if ((st.node_count + kClassMargin > fits) != (P.phase_class == 1))
+        const bool other   = st.node_count + kClassMargin > fits ||
+                           (P.lean_class0 && (P.spoa_accurate || (st.aln_len == kAlnPendingTraceback && st.beta != 0)));
+        if (other != (P.phase_class == 1))
             continue;
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         const int32_t* rlen = P.read_len + wd.read_off;
@@ -243,8 +247,12 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
             {
                 int16_t* scores = reinterpret_cast<int16_t*>(static_cast<ScoreT*>(P.scores) +
                                                              static_cast<int64_t>(w) * P.banded_score_stride);
-                aln_len = fast_traceback<IdT>(g, st.node_count, seq, len, scores, P.gap, P.mismatch, P.match, smem,
-                                              smem + kTileBytes, st.start_row, lane, st.beta);
+                if (LEAN)
+                    aln_len = fast_traceback_impl<IdT, false>(g, st.node_count, seq, len, scores, P.gap, P.mismatch,
+                                                              P.match, smem, smem + kTileBytes, st.start_row, lane, 0);
+                else
+                    aln_len = fast_traceback<IdT>(g, st.node_count, seq, len, scores, P.gap, P.mismatch, P.match, smem,
+                                                  smem + kTileBytes, st.start_row, lane, st.beta);
             }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {
@@ -259,7 +267,7 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
                 __syncwarp();
                 if (rc == kStSuccess)
                 {
-                    if (P.spoa_accurate)
+                    if (!LEAN && P.spoa_accurate)
                     {
                         if (lane == 0 && !topsort_spoa_order<IdT>(g, st.node_count))
                             rc = kStGenericError;
