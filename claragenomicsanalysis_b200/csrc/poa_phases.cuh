@@ -24,7 +24,7 @@ constexpr int32_t kFillWarpsPerBlock  = 4;
 constexpr int32_t kGraphWarpsPerBlock = 4;
 constexpr int32_t kTileBytes          = kTileAndDescBytes; // traceback tile + its row descriptors
 #ifndef POA_FILL_MIN_BLOCKS
-#define POA_FILL_MIN_BLOCKS 6
+#define POA_FILL_MIN_BLOCKS 7
 #endif
 
 template <typename ScoreT, typename IdT, bool MSA>
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
 // The packed fill of long windows (rows stored relative to a per-row offset, poa_fast.cuh fast_path_beta), for the
 // reads poa_fill_kernel marked kAlnNeedsRebased.
 template <typename ScoreT, typename IdT>
-__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_rebased_kernel(const KernelParams P)
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
     int32_t lane  = threadIdx.x & 31;
