@@ -16,6 +16,9 @@
 #include <cstring>
 #include <iomanip>
 #include <iostream>
+#include <map>
+#include <mutex>
+#include <tuple>
 #include <string>
 #include <vector>
 
@@ -478,17 +481,36 @@ static void launch_typed(const KernelParams& P, bool banded, bool msa, int32_t s
 // process: it is only ever set to one value, the most any launch uses.
 constexpr int kPhaseSmemLimit = 200 * 1024;
 
+// Resident CTAs per SM of a phase kernel at a given scratch size, looked up once per (kernel, device, size): a batch
+// makes well over a hundred launches and several host threads launch batches, so the two driver calls per launch this
+// replaces were a measurable share of a staging thread's time.
+static int32_t phase_blocks_per_sm(const void* kernel, int32_t threads, size_t smem)
+{
+    static std::mutex mu;
+    static std::map<std::tuple<const void*, int, size_t>, int32_t> cache;
+    int device = 0;
+    GW_CU_CHECK_ERR(cudaGetDevice(&device));
+    const auto key = std::make_tuple(kernel, device, smem);
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end())
+        return it->second;
+    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPhaseSmemLimit));
+    int per_sm = 1;
+    GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+    cache.emplace(key, std::max(per_sm, 1));
+    return std::max(per_sm, 1);
+}
+
 template <typename Kernel>
 static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per_block, int32_t sm_count,
                          cudaStream_t stream)
 {
     const dim3 block(warps_per_block * 32);
-    const size_t smem = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
-    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPhaseSmemLimit));
+    const size_t smem    = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
+    const int32_t per_sm = phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem);
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
-    int per_sm           = 1;
-    GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
-    const dim3 grid(std::max(1, std::min(needed, sm_count * std::max(per_sm, 1))));
+    const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
     kernel<<<grid, block, smem, stream>>>(P);
 }
 
