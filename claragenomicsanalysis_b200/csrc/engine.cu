@@ -557,12 +557,17 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
     P.class_cap       = two ? kahn_smem_nodes(graph_smem) : INT32_MAX - kClassMargin;
     P.lean_class0     = two ? 1 : 0;
     P.class_cap_final = two ? std::min(kahn_smem_nodes(graph_smem), consensus_scratch_nodes(graph_smem)) : P.class_cap;
+    {
+        const int32_t blocks = std::max(1, std::min((P.n_windows + kFillWarpsPerBlock - 1) / kFillWarpsPerBlock, sm_count * 16));
+        poa_init_kernel<IdT, MSA><<<blocks, kFillWarpsPerBlock * 32, 0, stream>>>(P);
+        launches++;
+    }
     for (int32_t s = 1; s <= steps; s++)
     {
         P.step          = s;
         P.next_window   = counters + 5 * (s - 1);
         P.smem_per_warp = fill_smem;
-        launch_phase(poa_fill_kernel<ScoreT, IdT, MSA>, P, kFillWarpsPerBlock, sm_count, stream);
+        launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
         P.next_window   = counters + 5 * (s - 1) + 4;
         launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
         launches++;

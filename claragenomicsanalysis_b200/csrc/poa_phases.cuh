@@ -27,7 +27,35 @@ constexpr int32_t kTileBytes          = kTileAndDescBytes; // traceback tile + i
 #define POA_FILL_MIN_BLOCKS 7
 #endif
 
-template <typename ScoreT, typename IdT, bool MSA>
+// First launch of a batch: per-window state and the backbone from read 0 (cudapoa_kernels.cuh:171-209).
+template <typename IdT, bool MSA>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32) poa_init_kernel(const KernelParams P)
+{
+    const int32_t lane = threadIdx.x & 31;
+    for (int32_t w = blockIdx.x * kFillWarpsPerBlock + (threadIdx.x >> 5); w < P.n_windows;
+         w += gridDim.x * kFillWarpsPerBlock)
+    {
+        const WindowDesc wd = P.windows[w];
+        const int32_t* rlen = P.read_len + wd.read_off;
+        PhaseState st       = PhaseState{};
+        st.status           = kStSuccess;
+        if (wd.n_reads <= 0 || rlen[0] <= 0)
+            st.status = kStGenericError; // the reference has no defined behaviour for an empty backbone
+        else if (rlen[0] > P.layout.M)
+            st.status = kStNodeCountExceeded;
+        else
+        {
+            const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+            st.node_count      = rlen[0];
+            init_backbone<IdT, MSA>(g, P.bases + wd.base_off, P.weights ? P.weights + wd.base_off : nullptr,
+                                    st.node_count, lane);
+        }
+        if (lane == 0)
+            P.phase[w] = st;
+    }
+}
+
+template <typename ScoreT, typename IdT>
 __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_kernel(const KernelParams P)
 {
     extern __shared__ __align__(16) uint8_t smem_block[];
@@ -50,27 +78,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         const int32_t* rlen = P.read_len + wd.read_off;
         PhaseState* ps      = P.phase + w;
-        PhaseState st;
-        if (s == 1) // first launch of the batch: backbone from read 0 (cudapoa_kernels.cuh:171-209)
-        {
-            st            = PhaseState{};
-            st.status     = kStSuccess;
-            if (wd.n_reads <= 0 || rlen[0] <= 0)
-                st.status = kStGenericError; // the reference has no defined behaviour for an empty backbone
-            else if (rlen[0] > P.layout.M)
-                st.status = kStNodeCountExceeded;
-            else
-            {
-                st.node_count = rlen[0];
-                init_backbone<IdT, MSA>(g, P.bases + wd.base_off, P.weights ? P.weights + wd.base_off : nullptr,
-                                        st.node_count, lane);
-            }
-            __syncwarp();
-        }
-        else
-        {
-            st = *ps;
-        }
+        PhaseState st       = *ps;
         if (st.status == kStSuccess && s < wd.n_reads)
         {
             st.seq_off += rlen[s - 1];
@@ -84,7 +92,6 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
             {
                 ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
                 int32_t aln_len     = kFastNotTaken;
-                int32_t aln_score   = 0;
                 int32_t start_row   = 0;
                 // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
                 // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
@@ -96,7 +103,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                     aln_len = kAlnNeedsRebased;
                 else if (beta == 0 &&
                          fast_fill_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.gap,
-                                                    P.mismatch, P.match, smem, lane, start_row, 0, &aln_score) == 0)
+                                                    P.mismatch, P.match, smem, lane, start_row, 0, nullptr) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
