@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
 
 // The reads the packed fill declined (other band widths, scores outside its range, rows decided by sentinel
 // arithmetic): the exact-arithmetic alignment, traceback included.  Launched after every fill launch; a warp that
-// finds nothing to do for a window moves on after one 48-byte load.
+// finds nothing to do for a window moves on after one 4-byte load.
 template <typename ScoreT, typename IdT>
 __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(const KernelParams P)
 {
