@@ -12,7 +12,7 @@ BIN_DIR = os.path.join(HERE, "bin")
 CLI = os.path.join(BIN_DIR, "cudapoa")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-SOURCES = ["engine.cu", "c_api.cpp", "pipeline.cpp"]
+SOURCES = ["engine.cu", "c_api.cpp", "pipeline.cpp", "no_alloc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-DCUDAPOA_B200_NATIVE", "-Xptxas", "-v",

@@ -194,6 +194,35 @@ int32_t cudapoa_b200_debug_rcp_table(int32_t device_id, float* out, int32_t n);
  * SM of `device_id` and returns thread-level instructions per second in *instr_per_s and the kernel time in *ms. */
 int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* instr_per_s, double* ms);
 
+/* Native library only.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Banded consensus (what create_batch(..., OutputType::consensus, BatchSize(max_sequence_size, max_sequences_per_poa,
+ * alignment_band_width), gap, mismatch, match, true) + add_poa_group + generate_poa + get_consensus compute) for
+ * n_windows windows whose inputs and outputs the CALLER holds in device memory; the function allocates nothing -- no
+ * cudaMalloc, cudaFree or allocating library call -- and only enqueues work on `stream` (no synchronisation).
+ * All per-window state lives in one file-scope device array of CUDAPOA_B200_NOALLOC_SCRATCH_BYTES that every GPU
+ * loading the library holds until the process exits.  Consequences:
+ *   - a request whose state exceeds that size is refused (-3; the message names the bytes needed, the maximum and the
+ *     bytes per window): 12 windows of BatchSize(640, 30, 256), 32 of BatchSize(256, 8, 256);
+ *   - the array is shared by all calls and keeps the last call's contents (what must start at zero is cleared by every
+ *     call): calls that overlap on the GPU -- two streams, two host threads -- RACE; serialise them;
+ *   - int16 configurations only (max_sequence_size below ~1490 with scores 8/-6/-8): others are refused (-2).
+ * Inputs (device): bases_d = the reads of all windows back to back; read_lengths_d = one int32 per read;
+ * window_n_reads_d = one int32 per window.  No weights (every base weighs 1).  A window with no reads, more reads than
+ * max_sequences_per_poa or a read longer than max_sequence_size gets status generic_error (9).
+ * Outputs (device), C = 2 * max_sequence_size: consensus_d[n_windows * C] (start -> end, NUL terminated when shorter
+ * than C), coverage_d[n_windows * C], length_d[n_windows], status_d[n_windows] (StatusType values).
+ * Returns 0, or a negative code with a message in error_msg (may be NULL): -1 bad argument, -2 needs 32-bit scores,
+ * -3 scratch too small, -4 CUDA error. */
+#define CUDAPOA_B200_NOALLOC_SCRATCH_BYTES (32 * 1024 * 1024)
+int32_t cudapoa_b200_consensus_noalloc(int32_t device_id, void* stream, const uint8_t* bases_d,
+                                       const int32_t* read_lengths_d, const int32_t* window_n_reads_d,
+                                       int32_t n_windows, int32_t max_sequences_per_poa, int32_t max_sequence_size,
+                                       int32_t alignment_band_width, int16_t gap_score, int16_t mismatch_score,
+                                       int16_t match_score, uint8_t* consensus_d, uint16_t* coverage_d,
+                                       int32_t* length_d, int32_t* status_d, char* error_msg, int32_t error_msg_cap);
+
 /* Native library only: benchmark hook.  Re-runs the device work of the last generate_poa() `iterations` times on
  * the inputs already resident in device memory (no host<->device copies) and returns the CUDA-event time of all
  * iterations in milliseconds, measured on the batch's own stream; negative if nothing has been staged. */
