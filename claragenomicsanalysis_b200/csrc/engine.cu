@@ -454,7 +454,7 @@ static void launch_one(const KernelParams& P, int32_t sm_count, cudaStream_t str
     int per_sm           = 1;
     GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
     const dim3 grid(std::max(1, std::min(needed, sm_count * std::max(per_sm, 1))));
-    kernel<<<grid, block, smem, stream>>>(P);
+    POA_LAUNCH(kernel, grid, block, smem, stream, P);
 }
 
 template <typename ScoreT, typename IdT>
@@ -511,7 +511,7 @@ static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per
     const int32_t per_sm = phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem);
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
     const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
-    kernel<<<grid, block, smem, stream>>>(P);
+    POA_LAUNCH(kernel, grid, block, smem, stream, P);
 }
 
 // Nodes a graph may have for the consensus (staging area + 6 bytes per node) to run out of `smem` bytes of scratch.
@@ -559,7 +559,8 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
     P.class_cap_final = two ? std::min(kahn_smem_nodes(graph_smem), consensus_scratch_nodes(graph_smem)) : P.class_cap;
     {
         const int32_t blocks = std::max(1, std::min((P.n_windows + kFillWarpsPerBlock - 1) / kFillWarpsPerBlock, sm_count * 16));
-        poa_init_kernel<IdT, MSA><<<blocks, kFillWarpsPerBlock * 32, 0, stream>>>(P);
+        auto init_kernel = poa_init_kernel<IdT, MSA>;
+        POA_LAUNCH(init_kernel, dim3(blocks), dim3(kFillWarpsPerBlock * 32), 0, stream, P);
         launches++;
     }
     for (int32_t s = 1; s <= steps; s++)
@@ -1066,6 +1067,7 @@ void get_multi_batch_sizes(std::vector<BatchSize>& list_of_batch_sizes,
 } // namespace genomeworks
 } // namespace claraparabricks
 
+#ifndef POA_EMU // device micro-benchmarks and tables: nothing to emulate
 namespace
 {
 __global__ void rcp_table_kernel(float* out, int32_t n)
@@ -1166,6 +1168,8 @@ extern "C" int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, 
         *ms_out = best;
     return static_cast<int32_t>(e);
 }
+
+#endif // POA_EMU
 
 extern "C" void cudapoa_b200_debug_set_schedule(int32_t mode)
 {

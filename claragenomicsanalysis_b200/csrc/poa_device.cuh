@@ -13,6 +13,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Kernel launch: `kernel` is a function pointer or the name of a non-template kernel.
+#ifdef POA_EMU
+#define POA_LAUNCH(kernel, grid, block, smem, stream, ...) POA_EMU_LAUNCH(kernel, grid, block, smem, stream, __VA_ARGS__)
+#else
+#define POA_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
+
 namespace poa_b200
 {
 
@@ -21,6 +28,53 @@ constexpr unsigned kFull = 0xffffffffu;
 // ---- explicit shared-memory accessors -----------------------------------------------------------------------
 // The per-warp scratch is reached through a pointer computed at run time, which the compiler treats as a generic
 // 64-bit address; these wrappers keep shared-memory traffic on 32-bit shared addresses (LDS/STS).
+#ifdef POA_EMU
+// Emulator build (tests/emu, test infrastructure): shared addresses are bounds- and alignment-checked offsets into the
+// emulated block's shared memory.
+#define POA_DYNAMIC_SMEM(name) uint8_t* name = poa_emu::smem_base()
+template <typename T>
+inline T* emu_shared(uint32_t a, int line)
+{
+    const uint32_t off = a - 0x100u;
+    if (a < 0x100u || off + sizeof(T) > poa_emu::smem_size() || (a % sizeof(T)) != 0)
+        poa_emu::fail("shared-memory access out of bounds or misaligned", line);
+    return reinterpret_cast<T*>(poa_emu::smem_base() + off);
+}
+inline uint32_t smem_u32(const void* p)
+{
+    return static_cast<uint32_t>(static_cast<const uint8_t*>(p) - poa_emu::smem_base()) + 0x100u;
+}
+inline uint32_t lds_u32(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<uint32_t>(a, line); }
+inline uint32_t lds_u16(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<uint16_t>(a, line); }
+inline uint32_t lds_u8(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<uint8_t>(a, line); }
+inline int32_t lds_s16(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<int16_t>(a, line); }
+inline uint2 lds_v2(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<uint2>(a, line); }
+inline uint4 lds_v4(uint32_t a, int line = __builtin_LINE()) { return *emu_shared<uint4>(a, line); }
+inline void sts_u32(uint32_t a, uint32_t v, int line = __builtin_LINE()) { *emu_shared<uint32_t>(a, line) = v; }
+inline void sts_u16(uint32_t a, uint32_t v, int line = __builtin_LINE())
+{
+    *emu_shared<uint16_t>(a, line) = static_cast<uint16_t>(v);
+}
+inline void sts_u8(uint32_t a, uint32_t v, int line = __builtin_LINE())
+{
+    *emu_shared<uint8_t>(a, line) = static_cast<uint8_t>(v);
+}
+inline void sts_u16_if(uint32_t a, uint32_t v, bool on, int line = __builtin_LINE())
+{
+    if (on)
+        sts_u16(a, v, line);
+}
+inline void sts_u8_if(uint32_t a, uint32_t v, bool on, int line = __builtin_LINE())
+{
+    if (on)
+        sts_u8(a, v, line);
+}
+inline void sts_v2(uint32_t a, uint2 v, int line = __builtin_LINE()) { *emu_shared<uint2>(a, line) = v; }
+inline void sts_v4(uint32_t a, uint4 v, int line = __builtin_LINE()) { *emu_shared<uint4>(a, line) = v; }
+// prmt.b32 with the sign-replication bit of the selector nibbles honoured
+inline uint32_t prmt(uint32_t x, uint32_t y, uint32_t s) { return poa_emu_prmt(x, y, s); }
+#else
+#define POA_DYNAMIC_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -92,6 +146,13 @@ __device__ __forceinline__ void sts_v4(uint32_t a, uint4 v)
 {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w));
 }
+__device__ __forceinline__ uint32_t prmt(uint32_t x, uint32_t y, uint32_t s)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(y), "r"(s));
+    return r;
+}
+#endif // POA_EMU
 
 enum : int32_t
 {
@@ -197,10 +258,15 @@ __device__ __forceinline__ float band_gradient(int32_t read_len, int32_t node_co
 {
     float r;
     float d = static_cast<float>(node_count + 1);
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
     float q;
     float n = static_cast<float>(read_len + 1);
+#ifdef POA_EMU
+    r = poa_emu::rcp_approx(d);
+    q = n * r;
+#else
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
     asm("mul.ftz.f32 %0, %1, %2;" : "=f"(q) : "f"(n), "f"(r));
+#endif
     return q;
 }
 
@@ -209,7 +275,11 @@ __device__ __forceinline__ int32_t band_start(int32_t row, float gradient, int32
 {
     float p;
     float fr = static_cast<float>(row);
+#ifdef POA_EMU
+    p = fr * gradient;
+#else
     asm("mul.ftz.f32 %0, %1, %2;" : "=f"(p) : "f"(fr), "f"(gradient));
+#endif
     int32_t start = __float2int_rz(p) - band / 2;
     start         = max(start, 0);
     if (start + band > max_column)

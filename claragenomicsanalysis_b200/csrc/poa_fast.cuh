@@ -647,7 +647,9 @@ __device__ int32_t fast_traceback_impl(const Graph<IdT>& g, int32_t node_count, 
                                        uint32_t rd, int32_t start_row, int32_t lane, int32_t beta)
 {
     uint32_t* rows = reinterpret_cast<uint32_t*>(scores);
+#ifndef POA_EMU
     asm volatile("" : "+l"(rows)); // keep the pointer in registers: recomputing it inside the walk costs more
+#endif
     RowDesc desc;
     desc.d0 = g.rowinfo;
     desc.d1 = desc.d0 + (g.M + 40);

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32) poa_init_kernel(const
 template <typename ScoreT, typename IdT>
 __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_kernel(const KernelParams P)
 {
-    extern __shared__ __align__(16) uint8_t smem_block[];
+    POA_DYNAMIC_SMEM(smem_block);
     int32_t lane  = threadIdx.x & 31;
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
 template <typename ScoreT, typename IdT>
 __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_kernel(const KernelParams P)
 {
-    extern __shared__ __align__(16) uint8_t smem_block[];
+    POA_DYNAMIC_SMEM(smem_block);
     int32_t lane  = threadIdx.x & 31;
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
 template <typename ScoreT, typename IdT, bool MSA, bool LEAN>
 __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(const KernelParams P)
 {
-    extern __shared__ __align__(16) uint8_t smem_block[];
+    POA_DYNAMIC_SMEM(smem_block);
     int32_t lane  = threadIdx.x & 31;
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));

@@ -16,7 +16,7 @@ constexpr int32_t kSmemPerWarp   = 14 * 1024; // 4 blocks x 4 warps x 14 KB per 
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(const KernelParams P)
 {
-    extern __shared__ __align__(16) uint8_t smem_block[];
+    POA_DYNAMIC_SMEM(smem_block);
     int32_t lane = threadIdx.x & 31;
     // this warp's scratch as a 32-bit shared address; both values are made opaque so that they live in registers
     // instead of being recomputed from the special registers all over the kernel

@@ -1,0 +1,81 @@
+"""The engine's device code run on the CPU through the SIMT emulator in tests/emu (test infrastructure: g++ build of
+csrc/engine.cu + csrc/c_api.cpp against stand-in CUDA headers, warps as fibers) and compared bit for bit with the
+oracle and the reference goldens.  Catches kernel-logic regressions where no GPU is available; the GPU parity tests
+(test_gpu_parity.py) remain the proof for the product library."""
+import ctypes
+import os
+import sys
+
+import pytest
+
+import cases
+import oraclelib
+import parity
+from claragenomicsanalysis_b200 import _cabi
+from claragenomicsanalysis_b200.windows import generate_windows
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu"))
+import build as emu_build  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def emu():
+    os.environ["POA_EMU_RCP_TABLE"] = oraclelib.RCP_TABLE
+    lib = _cabi.CabiLibrary(emu_build.build(), "cudapoa_b200_")
+    lib.set_schedule = lib._dll.cudapoa_b200_debug_set_schedule
+    lib.set_schedule.argtypes = [ctypes.c_int32]
+    lib.set_schedule.restype = None
+    yield lib
+    lib.set_schedule(0)
+
+
+def _check(lib, ws, eng, output="consensus", graphs=True):
+    n = parity.run_abi(lib, ws, want_graphs=graphs, max_mem=1 << 30, **eng)
+    o = parity.run_oracle(ws, want_graphs=graphs, **eng)
+    assert parity.compare(n, o, output) == []
+    if graphs:
+        for w in range(len(ws)):
+            assert n["graphs"][w] == o["graphs"][w], "graph %d" % w
+    return n
+
+
+@pytest.mark.parametrize("schedule", [1, 2])  # single launch, phase-split
+def test_emulated_banded_consensus_matches_oracle(emu, schedule):
+    emu.set_schedule(schedule)
+    ws = generate_windows(6, start_index=42, template_length=200, n_reads=8)
+    n = _check(emu, ws, dict(max_seq=256, max_reads=8, band=256, banded=True, output="consensus"))
+    assert sum(s["exact_path"] for s in n["stats"]) == 0  # the packed path served every alignment
+
+
+@pytest.mark.parametrize("schedule", [1, 2])
+def test_emulated_msa_matches_oracle(emu, schedule):
+    emu.set_schedule(schedule)
+    ws = generate_windows(3, start_index=77, template_length=150, n_reads=6)
+    _check(emu, ws, dict(max_seq=256, max_reads=6, band=256, banded=True, output="msa"), output="msa", graphs=False)
+
+
+def test_emulated_noisy_reads_phase_split(emu):
+    """25 % errors: bubbles, far predecessors (beyond the shared-memory ring), rows with several predecessors."""
+    emu.set_schedule(2)
+    ws = generate_windows(3, start_index=4000, template_length=300, n_reads=10, read_error=0.25, backbone_error=0.15)
+    _check(emu, ws, dict(max_seq=448, max_reads=10, band=256, banded=True, output="consensus"))
+
+
+def test_emulated_long_window_rebased_rows(emu):
+    """Reference int32-score range (L >= 1490): the packed fill stores rows relative to a per-row offset."""
+    emu.set_schedule(2)
+    ws = generate_windows(1, start_index=7000, template_length=1600, n_reads=4)
+    n = _check(emu, ws, dict(max_seq=2048, max_reads=4, band=256, banded=True, output="consensus"))
+    assert sum(s["exact_path"] for s in n["stats"]) == 0
+
+
+def test_emulated_cfg2_window_matches_reference_golden(emu):
+    """One full-size cfg 2 window (500 bp x 30 reads) against the golden produced by the unmodified reference."""
+    emu.set_schedule(2)
+    g = parity.load_golden("reference_cfg2_banded16_consensus.json")
+    if g is None:
+        pytest.skip("golden file missing")
+    c = cases.CASES["cfg2_banded16_consensus"]
+    ws = cases.case_windows("cfg2_banded16_consensus").slice(0, 1)
+    n = parity.run_abi(emu, ws, max_mem=1 << 30, **c["engine"])
+    assert parity.digests(n, "consensus") == g["digest"][:1]
