@@ -984,8 +984,14 @@ StatusType Init()
     return StatusType::success;
 }
 
-// utils.cu:24-138 with estimate_max_poas (allocate_block.hpp:364-401) evaluated with this engine's footprint and
-// cudaMemGetInfo queried once instead of once per group.
+// Groups -> batches (cudapoa/include/.../utils.hpp:48-58; the reference's binning is cudapoa/src/utils.cu:24-138).
+// Same contract: groups are classed by how many windows of their shape one batch holds under the memory quota, in
+// power-of-two classes (or the caller's `bins_capacity`); a class of large windows also takes the following classes of
+// smaller windows while they are no more numerous than its capacity.  Differences, deliberate:
+//   * capacity comes from this engine's footprint (make_plan), and cudaMemGetInfo is asked once, not once per group;
+//   * a batch's BatchSize covers the longest read AND the largest read count among ALL the groups it received (the
+//     reference takes the group with the largest length x reads product of the first class only, so a merged group can
+//     be rejected by its own batch: allocate_block.hpp:364-401, utils.cu:86-91,117).
 void get_multi_batch_sizes(std::vector<BatchSize>& list_of_batch_sizes,
                            std::vector<std::vector<int32_t>>& list_of_groups_per_batch,
                            const std::vector<Group>& poa_groups, bool banded_alignment, bool msa_flag,
@@ -994,72 +1000,73 @@ void get_multi_batch_sizes(std::vector<BatchSize>& list_of_batch_sizes,
 {
     size_t total = 0, free_mem = 0;
     GW_CU_CHECK_ERR(cudaMemGetInfo(&free_mem, &total));
-    const double mem_per_batch = static_cast<double>(gpu_memory_usage_quota) * static_cast<double>(free_mem);
+    const double budget = static_cast<double>(gpu_memory_usage_quota) * static_cast<double>(free_mem);
 
-    const int32_t num_groups = get_size<int32_t>(poa_groups);
-    std::vector<int64_t> max_poas(num_groups);
-    std::vector<int32_t> max_lengths(num_groups);
-    for (int32_t i = 0; i < num_groups; i++)
+    std::vector<int32_t> pow2;
+    if (bins_capacity == nullptr)
+    {
+        for (int32_t j = 0; j < 20; j++)
+            pow2.push_back(1 << j);
+        bins_capacity = &pow2;
+    }
+    const std::vector<int32_t>& cap = *bins_capacity;
+    const int32_t n_classes         = get_size<int32_t>(cap);
+    if (n_classes == 0)
+        return;
+
+    struct Class
+    {
+        std::vector<int32_t> groups;
+        int32_t longest = 0, most_reads = 0;
+    };
+    std::vector<Class> classes(n_classes);
+    // windows of one shape share one footprint: shapes repeat massively in real inputs
+    std::map<std::pair<int32_t, int32_t>, int32_t> class_of_shape;
+    const int32_t n_groups = get_size<int32_t>(poa_groups);
+    for (int32_t i = 0; i < n_groups; i++)
     {
         int32_t longest = 0;
         for (const Entry& e : poa_groups[i])
             longest = std::max(longest, e.length);
-        const BatchSize bs(longest, get_size<int32_t>(poa_groups[i]), band_width);
-        const MemoryPlan p = make_plan(bs, banded_alignment, msa_flag, gap_score, mismatch_score, match_score);
-        max_poas[i]        = static_cast<int64_t>(mem_per_batch / static_cast<double>(p.fixed_per_poa + p.score_per_poa));
-        max_lengths[i]     = longest;
-    }
-
-    int32_t num_bins = 20;
-    std::vector<int32_t> default_bins;
-    if (bins_capacity == nullptr)
-    {
-        default_bins.assign(num_bins, 1);
-        for (int32_t j = 1; j < num_bins; j++)
-            default_bins[j] = default_bins[j - 1] * 2;
-        bins_capacity = &default_bins;
-    }
-    else
-    {
-        num_bins = get_size<int32_t>(*bins_capacity);
-    }
-    std::vector<int32_t> frequency(num_bins, 0), bin_len(num_bins, 0), bin_reads(num_bins, 0);
-    std::vector<std::vector<int32_t>> members(num_bins);
-    for (int32_t i = 0; i < num_groups; i++)
-    {
-        const int64_t size_i = static_cast<int64_t>(max_lengths[i]) * get_size<int32_t>(poa_groups[i]);
-        for (int32_t j = 0; j < num_bins; j++)
+        const int32_t reads = get_size<int32_t>(poa_groups[i]);
+        auto it             = class_of_shape.find({longest, reads});
+        if (it == class_of_shape.end())
         {
-            if (max_poas[i] <= bins_capacity->at(j) || j == num_bins - 1)
-            {
-                frequency[j]++;
-                members[j].push_back(i);
-                if (static_cast<int64_t>(bin_len[j]) * bin_reads[j] < size_i)
-                {
-                    bin_len[j]   = max_lengths[i];
-                    bin_reads[j] = get_size<int32_t>(poa_groups[i]);
-                }
-                break;
-            }
+            const MemoryPlan plan = make_plan(BatchSize(longest, reads, band_width), banded_alignment, msa_flag,
+                                              gap_score, mismatch_score, match_score);
+            const int64_t fit = static_cast<int64_t>(budget / static_cast<double>(plan.fixed_per_poa + plan.score_per_poa));
+            // first class whose capacity covers `fit` (capacities ascend); the last class takes the rest
+            int32_t c = static_cast<int32_t>(std::lower_bound(cap.begin(), cap.end(), fit,
+                                                              [](int32_t capacity, int64_t v) { return capacity < v; }) -
+                                             cap.begin());
+            c  = std::min(c, n_classes - 1);
+            it = class_of_shape.emplace(std::make_pair(longest, reads), c).first;
         }
+        Class& k = classes[it->second];
+        k.groups.push_back(i);
+        k.longest    = std::max(k.longest, longest);
+        k.most_reads = std::max(k.most_reads, reads);
     }
-    // merge bins of smaller groups into the batch of a larger-group bin while they fit its capacity
-    for (int32_t j = 0; j < num_bins; j++)
+    for (int32_t j = 0; j < n_classes; j++)
     {
-        if (frequency[j] == 0)
+        Class& head = classes[j];
+        if (head.groups.empty())
             continue;
-        list_of_batch_sizes.emplace_back(bin_len[j], bin_reads[j], band_width);
-        list_of_groups_per_batch.push_back(members[j]);
-        for (int32_t k = j + 1; k < num_bins; k++)
+        for (int32_t k = j + 1; k < n_classes; k++)
         {
-            if (frequency[k] == 0)
+            Class& next = classes[k];
+            if (next.groups.empty())
                 continue;
-            if (bins_capacity->at(j) < frequency[k])
+            if (cap[j] < get_size<int32_t>(next.groups))
                 break;
-            std::vector<int32_t>& current = list_of_groups_per_batch.back();
-            current.insert(current.end(), members[k].begin(), members[k].end());
-            frequency[k] = 0;
+            head.groups.insert(head.groups.end(), next.groups.begin(), next.groups.end());
+            head.longest    = std::max(head.longest, next.longest);
+            head.most_reads = std::max(head.most_reads, next.most_reads);
+            next.groups.clear();
         }
+        list_of_batch_sizes.emplace_back(head.longest, head.most_reads, band_width);
+        list_of_groups_per_batch.push_back(std::move(head.groups));
+        head.groups.clear();
     }
 }
 

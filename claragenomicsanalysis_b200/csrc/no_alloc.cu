@@ -78,16 +78,22 @@ __global__ void noalloc_setup_kernel(WindowDesc* windows, int32_t* counter, cons
         return;
     int64_t base_off = 0;
     int32_t read_off = 0;
+    bool trusted     = true; // false once a read count was out of range: the offsets of later windows are unknown
     for (int32_t w = 0; w < n_windows; w++)
     {
         const int32_t nr = window_n_reads[w];
-        bool ok          = nr > 0 && nr <= max_reads;
-        int64_t bases    = 0;
-        for (int32_t r = 0; r < nr; r++)
+        bool ok          = trusted && nr > 0 && nr <= max_reads;
+        if (nr < 0 || nr > max_reads)
+            trusted = false; // never use a count that was not validated as a loop bound or an offset
+        int64_t bases = 0;
+        if (ok)
         {
-            const int32_t len = read_len[read_off + r];
-            ok                = ok && len >= 0 && len <= max_seq;
-            bases += len > 0 ? len : 0;
+            for (int32_t r = 0; r < nr; r++)
+            {
+                const int32_t len = read_len[read_off + r];
+                ok                = ok && len >= 0 && len <= max_seq;
+                bases += len > 0 ? len : 0;
+            }
         }
         WindowDesc wd{};
         wd.base_off     = base_off;
@@ -96,8 +102,11 @@ __global__ void noalloc_setup_kernel(WindowDesc* windows, int32_t* counter, cons
         wd.n_reads      = ok ? nr : 0;
         wd.scores_width = 0;
         windows[w]      = wd;
-        base_off += bases;
-        read_off += nr > 0 ? nr : 0;
+        if (trusted)
+        {
+            base_off += bases;
+            read_off += nr;
+        }
     }
     *counter = 0;
 }
@@ -227,6 +236,9 @@ extern "C" int32_t cudapoa_b200_consensus_noalloc(int32_t device_id, void* strea
         return fail(error_msg, error_msg_cap, -3, text);
     }
 
+    // an error some earlier call of this thread left pending must not be reported as this call's
+    if (cudaPeekAtLastError() != cudaSuccess)
+        return fail(error_msg, error_msg_cap, -4, "a CUDA error was already pending when the call was made");
     int previous = 0;
     cudaError_t e = cudaGetDevice(&previous);
     if (e == cudaSuccess)

@@ -207,7 +207,14 @@ int32_t cudapoa_b200_debug_dpx_peak(int32_t device_id, int32_t kind, double* ins
  *     bytes per window): 12 windows of BatchSize(640, 30, 256), 32 of BatchSize(256, 8, 256);
  *   - the array is shared by all calls and keeps the last call's contents (what must start at zero is cleared by every
  *     call): calls that overlap on the GPU -- two streams, two host threads -- RACE; serialise them;
- *   - int16 configurations only (max_sequence_size below ~1490 with scores 8/-6/-8): others are refused (-2).
+ *   - int16 configurations only (max_sequence_size below ~1490 with scores 8/-6/-8): others are refused (-2);
+ *   - the FIRST call per device looks up the array's device address and the launch limits (cudaGetSymbolAddress,
+ *     cudaFuncSetAttribute, an occupancy query; with lazy module loading it may also load the module, which is what
+ *     reserves the array): make one call per device OUTSIDE stream capture before using the entry point under capture;
+ *   - graph nodes are always ordered by the reference's default (Kahn) topological sort: the SPOA_ACCURATE build flag
+ *     and the CUDAPOA_B200_SPOA_ACCURATE environment switch of create_batch do not apply here;
+ *   - a window whose read count is negative or above max_sequences_per_poa makes the offsets of all LATER windows
+ *     unknowable: it and every window after it get status generic_error (9).
  * Inputs (device): bases_d = the reads of all windows back to back; read_lengths_d = one int32 per read;
  * window_n_reads_d = one int32 per window.  No weights (every base weighs 1).  A window with no reads, more reads than
  * max_sequences_per_poa or a read longer than max_sequence_size gets status generic_error (9).

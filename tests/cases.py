@@ -47,6 +47,23 @@ CASES = {
     "full32_consensus": dict(
         gen=dict(template_length=1550, n_reads=5), n=4, start=8000,
         engine=dict(max_seq=2048, max_reads=5, band=256, banded=False, output="consensus")),
+    # BASELINE.json config 4 at its real shape: 2-5 kb templates x 100 reads, BatchSize(6400, 100): int32 scores in the
+    # reference, 99 alignments per window, graphs of several thousand nodes
+    "cfg4_banded32_real": dict(
+        gen=dict(template_length=(2000, 5000), n_reads=100), n=2, start=20000,
+        engine=dict(max_seq=6400, max_reads=100, band=256, banded=True, output="consensus")),
+    # config 5B: mixed sizes in ONE batch -- templates 250/500/1000/2000 bp (p = .2/.5/.2/.1), 10..60 reads per window
+    "cfg5b_mixed": dict(
+        gen=dict(length_choices=[250, 500, 1000, 2000], length_probs=[0.2, 0.5, 0.2, 0.1], n_reads_range=(10, 60)),
+        n=64, start=30000,
+        engine=dict(max_seq=2560, max_reads=60, band=256, banded=True, output="consensus")),
+    # banded max_sequence_size >= 8192: int32 node ids and sizes as well (cudapoa_limits.hpp:39-53), <int32, int32>
+    "banded_size32": dict(
+        gen=dict(template_length=300, n_reads=5), n=3, start=40000,
+        engine=dict(max_seq=8192, max_reads=5, band=256, banded=True, output="consensus")),
+    "banded_size32_msa": dict(
+        gen=dict(template_length=200, n_reads=4), n=2, start=41000,
+        engine=dict(max_seq=8192, max_reads=4, band=256, banded=True, output="msa")),
     # more reads than max_sequences_per_poa and reads longer than max_sequence_size: per-sequence rejections
     "banded16_rejections": dict(
         gen=dict(template_length=(300, 500), n_reads=14), n=12, start=9000, long_read_at=3,

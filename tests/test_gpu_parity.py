@@ -46,7 +46,8 @@ def test_native_matches_oracle_and_reference_golden(lib, name):
 
 
 @pytest.mark.parametrize("name", ["cfg2_banded16_consensus", "cfg3_banded16_msa", "full16_consensus",
-                                  "banded32_consensus"])
+                                  "banded32_consensus", "cfg4_banded32_real", "cfg5b_mixed", "banded_size32",
+                                  "banded_size32_msa"])
 def test_native_matches_live_reference(lib, name):
     if not oraclelib.have_ref_cudapoa():
         pytest.skip("reference build not present on this box")
@@ -58,7 +59,8 @@ def test_native_matches_live_reference(lib, name):
 
 
 # ---- the two device schedules of a banded batch: one launch per window set, or one launch per phase and read ----------
-BANDED_CASES = sorted(n for n in CASES if CASES[n]["engine"].get("banded", True))
+# (batches with int32 node ids always take the single launch: nothing to compare)
+BANDED_CASES = sorted(n for n in CASES if CASES[n]["engine"].get("banded", True) and CASES[n]["engine"]["max_seq"] < 8192)
 
 
 @pytest.fixture
@@ -329,3 +331,76 @@ def test_pipeline_matches_single_batch_and_oracle(lib, output):
     p.run(ws, chunk_windows=0)  # automatic chunking, second run on the same pipeline
     assert p.digest() == d1
     p.close()
+
+
+# ---- get_multi_batch_sizes (cudapoa/include/.../utils.hpp:48-58, cudapoa/src/utils.cu:24-138) ------------------------
+def _multi_batch(lib, read_lengths, window_n_reads, banded=True, msa=False, band=256, quota=0.9):
+    import ctypes
+
+    n = len(window_n_reads)
+    out = (_cabi.BatchSizeC * 64)()
+    w2b = np.full(n, -2, dtype=np.int32)
+    rl = np.ascontiguousarray(read_lengths, dtype=np.int32)
+    wn = np.ascontiguousarray(window_n_reads, dtype=np.int32)
+    k = lib.get_multi_batch_sizes(rl.ctypes.data, wn.ctypes.data, n, int(banded), int(msa), band, ctypes.c_float(quota),
+                                  -6, -8, 8, out, 64, w2b.ctypes.data)
+    assert k >= 0, lib.error()
+    return [out[i].as_dict() for i in range(k)], w2b
+
+
+def test_get_multi_batch_sizes_partitions_and_fits(lib):
+    """Every group lands in exactly one batch, fits that batch's BatchSize (longest read and read count), batches come
+    out largest windows first, and a batch created from its BatchSize accepts its groups."""
+    ws = generate_windows(400, start_index=50000, length_choices=[100, 250, 500, 1000, 2000],
+                          length_probs=[0.2, 0.2, 0.3, 0.2, 0.1], n_reads_range=(2, 40))
+    sizes, w2b = _multi_batch(lib, ws.read_lengths, ws.window_n_reads)
+    assert len(sizes) >= 1 and w2b.min() >= 0 and w2b.max() == len(sizes) - 1
+    assert set(w2b.tolist()) == set(range(len(sizes)))
+    off = np.concatenate([[0], np.cumsum(ws.window_n_reads)])
+    for w in range(len(ws)):
+        bs = sizes[w2b[w]]
+        assert int(ws.read_lengths[off[w]:off[w + 1]].max()) <= bs["max_sequence_size"]
+        assert int(ws.window_n_reads[w]) <= bs["max_sequences_per_poa"]
+    longest = [s["max_sequence_size"] for s in sizes]
+    assert longest == sorted(longest, reverse=True)
+    # the first batch really takes its groups
+    members = [w for w in range(len(ws)) if w2b[w] == 0][:8]
+    sub = WindowSet.concat([ws.slice(w, w + 1) for w in members])
+    r = parity.run_abi(lib, sub, max_seq=sizes[0]["max_sequence_size"], max_reads=sizes[0]["max_sequences_per_poa"],
+                       max_mem=8 << 30)
+    assert r["status"] == [0] * len(members) and set(r["seq_status"]) == {0}
+
+
+def test_get_multi_batch_sizes_one_million_groups_fast(lib):
+    """O(windows) driver calls were the reference's cost (allocate_block.hpp:367-369); here one million mixed groups
+    are binned in about a second, and binning is monotone: more memory never means more batches."""
+    import time
+
+    rng = np.random.default_rng(5)
+    n = 1_000_000
+    wn = np.full(n, 2, dtype=np.int32)
+    lt = rng.choice(np.array([250, 500, 1000, 2000], dtype=np.int32), size=n, p=[0.2, 0.5, 0.2, 0.1])
+    rl = np.repeat(lt, 2).astype(np.int32)
+    t0 = time.perf_counter()
+    sizes, w2b = _multi_batch(lib, rl, wn)
+    dt = time.perf_counter() - t0
+    assert w2b.min() >= 0 and len(sizes) >= 1
+    assert dt < 3.0, "binning one million groups took %.2f s" % dt
+    fewer_mem, _ = _multi_batch(lib, rl[:20000], wn[:10000], quota=0.05)
+    more_mem, _ = _multi_batch(lib, rl[:20000], wn[:10000], quota=0.9)
+    assert len(more_mem) <= len(fewer_mem)
+
+
+def test_get_multi_batch_sizes_vs_reference_build(lib):
+    """The reference's binning on the same groups (its own footprint formula and one cudaMemGetInfo per group): both
+    partition the input; the native batches additionally guarantee the fit (documented difference, engine.cu)."""
+    if not oraclelib.have_ref_cudapoa():
+        pytest.skip("reference build not present on this box")
+    ws = generate_windows(300, start_index=51000, length_choices=[250, 500, 1000, 2000],
+                          length_probs=[0.2, 0.5, 0.2, 0.1], n_reads_range=(10, 60))
+    n_sizes, n_map = _multi_batch(lib, ws.read_lengths, ws.window_n_reads)
+    r_sizes, r_map = _multi_batch(parity.ref_lib(), ws.read_lengths, ws.window_n_reads)
+    assert n_map.min() >= 0 and r_map.min() >= 0
+    assert len(n_sizes) >= 1 and len(r_sizes) >= 1
+    # both put the longest windows into the first batch
+    assert n_sizes[0]["max_sequence_size"] == int(ws.read_lengths.max())

@@ -17,13 +17,24 @@ from claragenomicsanalysis_b200.windows import generate_windows
 SCRATCH_BYTES = 32 * 1024 * 1024  # CUDAPOA_B200_NOALLOC_SCRATCH_BYTES
 
 
+_ENTRY = None
+
+
 def _entry():
-    dll = ctypes.CDLL(_cabi.NATIVE_LIB_PATH)
-    f = dll.cudapoa_b200_consensus_noalloc
-    f.restype = ctypes.c_int32
-    f.argtypes = ([ctypes.c_int32, ctypes.c_void_p] + [ctypes.c_void_p] * 3 + [ctypes.c_int32] * 4 +
-                  [ctypes.c_int16] * 3 + [ctypes.c_void_p] * 4 + [ctypes.c_char_p, ctypes.c_int32])
-    return f
+    """The entry point, bound once.  The library only exists after an nvcc build: skip (not error) where it is absent."""
+    global _ENTRY
+    if _ENTRY is None:
+        import os
+
+        if not os.path.exists(_cabi.NATIVE_LIB_PATH):
+            pytest.skip("libcudapoa_b200.so has not been built on this machine")
+        dll = ctypes.CDLL(_cabi.NATIVE_LIB_PATH)
+        f = dll.cudapoa_b200_consensus_noalloc
+        f.restype = ctypes.c_int32
+        f.argtypes = ([ctypes.c_int32, ctypes.c_void_p] + [ctypes.c_void_p] * 3 + [ctypes.c_int32] * 4 +
+                      [ctypes.c_int16] * 3 + [ctypes.c_void_p] * 4 + [ctypes.c_char_p, ctypes.c_int32])
+        _ENTRY = f
+    return _ENTRY
 
 
 def test_noalloc_symbol_and_limits_without_gpu():
