@@ -1,0 +1,588 @@
+// Packed (DPX s16x2) banded fill, second formulation: the fill emits a MOVE CODE per cell instead of streaming every
+// score row to HBM, and the traceback (poa_trace2.cuh) follows the codes.
+//
+// Same alignment as align_exact<int16_t, IdT, true> / the first formulation (poa_fast.cuh, whose exactness argument,
+// tilted scores, row layout and band rules it keeps -- cudapoa_nw_banded.cuh:28-174,199-206,301-358 are the reference
+// rules): band 256, one warp per row, 8 cells per lane in four s16x2 registers (cell i, cell i + 4).  What changes:
+//   * per cell, the move the reference's traceback would take from it (cudapoa_nw_banded.cuh:386-474: diagonal through
+//     the first predecessor that explains the score, else vertical through the first such predecessor, else
+//     horizontal) is decided here, where all candidates are in registers: 4 bits per cell (2-bit kind, 2-bit
+//     predecessor slot), 128 B per row; rows with more than four predecessors store a byte per cell.  The score matrix
+//     itself never reaches HBM: score rows live in the 8-row shared-memory ring, and only rows that a LATER row names
+//     as a predecessor from beyond the ring (known from the descriptor pre-pass) are also spilled to global memory.
+//   * the substitution profile comes from shared memory: one int8 row per distinct base of the read (at most four,
+//     else the exact path takes the read), holding match - gap / mismatch - gap per read position; a lane fetches its
+//     eight values with two 4-byte loads and widens them with four sign-replicating byte permutes.
+//   * sink selection happens as the sink rows are produced.
+// Window's score area: [code rows: (M + 1) x 256 B][spill slots: 528 B each].
+#pragma once
+
+#include "poa_fast.cuh"
+
+namespace poa_b200
+{
+
+constexpr int32_t kCodeRowBytes  = 256; // nibble codes use the first 128 B, byte codes (wide rows) all of it
+constexpr int32_t kSpillRowBytes = 33 * 16; // lead block + 32 cell blocks
+constexpr int32_t kWidePreds     = 4;  // rows with more predecessors than this store one byte per cell
+constexpr int32_t kProfRows      = 4;  // distinct read bases the profile holds
+constexpr int32_t kMoveDiag      = 0;
+constexpr int32_t kMoveVert      = 1;
+constexpr int32_t kMoveHoriz     = 2;  // bit 1 set (3 also means horizontal)
+
+__host__ __device__ inline int32_t fill2_profile_stride(int32_t read_len)
+{
+    return (read_len + kFastBand + 8 + 15) & ~15;
+}
+// Shared memory the fill needs for a read of this length: the ring plus the profile.
+__host__ __device__ inline int32_t fill2_smem_bytes(int32_t read_len)
+{
+    return kRingBytes + kProfRows * fill2_profile_stride(read_len);
+}
+
+__device__ __forceinline__ uint32_t vminu2_1(uint32_t x) // per half: 0 if zero, else 1
+{
+    return __vminu2(x, 0x00010001u);
+}
+
+// Returns 0 and the row the traceback starts from in start_row, or kFastNotTaken (nothing the caller needs was
+// written: the exact path redoes the read).  All 32 lanes.
+template <typename IdT, bool REBASED>
+__device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
+                              uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
+                              int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t beta_arg)
+{
+    const int32_t beta = REBASED ? beta_arg : 0;
+    const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
+    const int32_t pd_x = mismatch - gap; // bases differ
+    if (sizeof(IdT) != 2 || pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128)
+        return kFastNotTaken;
+    const int64_t code_bytes  = static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
+    const int32_t spill_slots = static_cast<int32_t>(min(static_cast<long long>(65535),
+                                                         static_cast<long long>((area_bytes - code_bytes) / kSpillRowBytes)));
+    if (spill_slots < 2)
+        return kFastNotTaken;
+    uint8_t* codes      = area;
+    uint32_t* spill     = reinterpret_cast<uint32_t*>(area + code_bytes);
+    uint16_t* slot_of   = g.kahn;  // spill slot per row (scratch of the topological sort, idle during the fill)
+    uint8_t* far_mark   = g.marks; // per row: a later row reads it from beyond the ring
+
+    const uint32_t ring    = smem;
+    const uint32_t prof    = ring + kRingBytes;
+    const int32_t pstride  = fill2_profile_stride(read_len);
+    const unsigned lt      = (1u << lane) - 1u;
+    const uint32_t NEG2    = pack2(kNegT, kNegT);
+    const uint4 NEG4       = make_uint4(NEG2, NEG2, NEG2, NEG2);
+
+    // ---- the read's alphabet (at most kProfRows distinct bytes) and the profile ------------------------------------
+    uint32_t alpha = 0; // byte a = base of profile row a
+    int32_t nalpha = 0;
+    for (int32_t k0 = 0; k0 < read_len; k0 += 32)
+    {
+        const int32_t k   = k0 + lane;
+        const bool have   = k < read_len;
+        const uint32_t b  = have ? read[k] : 0u;
+        for (;;)
+        {
+            const uint32_t valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
+            const bool known     = (__vcmpeq4(alpha, b * 0x01010101u) & valid) != 0u;
+            const unsigned fresh = __ballot_sync(kFull, have && !known);
+            if (fresh == 0u)
+                break;
+            if (nalpha == kProfRows)
+                return kFastNotTaken; // a fifth distinct base: the exact path compares bytes
+            const uint32_t nb = __shfl_sync(kFull, b, __ffs(fresh) - 1);
+            alpha |= nb << (8 * nalpha);
+            nalpha++;
+        }
+    }
+    {
+        const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
+        for (int32_t k = lane; k < pstride; k += 32)
+        {
+            const uint32_t b  = (k < read_len) ? read[k] : 0u;
+            const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
+#pragma unroll
+            for (int a = 0; a < kProfRows; a++)
+                sts_u8(prof + static_cast<uint32_t>(a * pstride + k), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
+        }
+    }
+
+    RowDesc desc;
+    desc.d0 = g.rowinfo;
+    desc.d1 = desc.d0 + (g.M + 40);
+    desc.d2 = desc.d1 + (g.M + 40);
+    const int32_t max_column = read_len + 1;
+    const float gradient     = band_gradient(read_len, node_count);
+
+    // ---- pre-pass: descriptors, far marks, spill slots -----------------------------------------------------------------
+    for (int32_t r = lane; r <= node_count; r += 32)
+        far_mark[r] = 0;
+    __syncwarp();
+    {
+        const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
+        constexpr int32_t kPre     = 4;
+        for (int32_t rb = 1; rb <= node_count; rb += 32 * kPre)
+        {
+            int32_t node[kPre];
+            uint32_t pc[kPre], word[kPre];
+            int32_t pe[kPre][5];
+#pragma unroll
+            for (int u = 0; u < kPre; u++)
+            {
+                const int32_t r = min(rb + lane + 32 * u, node_count);
+                node[u]         = g.sorted[r - 1];
+            }
+#pragma unroll
+            for (int u = 0; u < kPre; u++)
+            {
+                pc[u]               = g.in_cnt[node[u]];
+                const uint32_t base = g.nodes[node[u]];
+                const uint32_t eq   = __vcmpeq4(alpha, base * 0x01010101u) & alpha_valid;
+                const uint32_t a    = eq ? static_cast<uint32_t>((__ffs(static_cast<int32_t>(eq)) - 1) >> 3) : 4u;
+                word[u]             = a | ((g.out_cnt[node[u]] == 0) ? (1u << 14) : 0u);
+#pragma unroll
+                for (int k = 0; k < 5; k++)
+                    pe[u][k] = g.in_edge(node[u], k); // slots beyond the in-degree: stale but readable
+            }
+#pragma unroll
+            for (int u = 0; u < kPre; u++)
+            {
+                uint32_t pr[5];
+#pragma unroll
+                for (int k = 0; k < 5; k++)
+                    pr[k] = (static_cast<uint32_t>(k) < pc[u]) ? static_cast<uint32_t>(g.pos[pe[u][k]] + 1) : 0u;
+                const int32_t r = rb + lane + 32 * u;
+                if (r <= node_count)
+                {
+                    desc.d0[r] = word[u] | (pc[u] << 8) | (pr[0] << 16);
+                    desc.d1[r] = pr[1] | (pr[2] << 16);
+                    desc.d2[r] = pr[3] | (pr[4] << 16);
+                    // predecessors the ring (rows r - 8 .. r - 1) will no longer hold; row 0 is always in slot 0
+#pragma unroll
+                    for (int k = 0; k < 5; k++)
+                        if (static_cast<uint32_t>(k) < pc[u] && static_cast<int32_t>(pr[k]) < r - kRingRows && pr[k] != 0u)
+                            far_mark[pr[k]] = 1;
+                    for (uint32_t k = 5; k < pc[u]; k++)
+                    {
+                        const int32_t p = g.pos[g.in_edge(node[u], static_cast<int32_t>(k))] + 1;
+                        if (p < r - kRingRows)
+                            far_mark[p] = 1;
+                    }
+                }
+            }
+        }
+    }
+    __syncwarp();
+    {
+        int32_t used = 1; // slot 0: row 0
+        for (int32_t r0 = 1; r0 <= node_count; r0 += 32)
+        {
+            const int32_t r     = r0 + lane;
+            const bool m        = r <= node_count && far_mark[r] != 0;
+            const unsigned mask = __ballot_sync(kFull, m);
+            if (m)
+            {
+                slot_of[r] = static_cast<uint16_t>(used + __popc(mask & lt));
+                desc.d0[r] |= 1u << 15;
+            }
+            used += __popc(mask);
+        }
+        if (used > spill_slots)
+            return kFastNotTaken;
+    }
+    // Row 0: T == 0 in columns 0 .. band + 3, sentinel beyond (cudapoa_nw_banded.cuh:138-143, :208-212); lead block
+    // {band start 0, -, -, left boundary 0}.  It lives in spill slot 0 only: a row whose predecessor is row 0 (a node
+    // without in-edges) takes the far path, which knows row 0's padding.  Ring slots carry their two pad blocks at the
+    // sentinel once and for all.
+    {
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        __stcg(reinterpret_cast<uint4*>(spill) + lane, z);
+        if (lane == 0)
+            __stcg(reinterpret_cast<uint4*>(spill) + 32, z);
+        if (lane < kRingRows)
+        {
+            sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 33, NEG4);
+            sts_v4(ring + lane * (kFastRowWords * 4) + 16u * 34, NEG4);
+        }
+    }
+    __syncwarp();
+
+    const uint32_t gapv   = pack2(gap, gap);
+    const uint32_t pdx2   = pack2(pd_x, pd_x);
+    const uint32_t prof_l = prof + 8u * static_cast<uint32_t>(lane);
+    uint8_t* code_lane4   = codes + 4 * lane; // nibble rows: one word per lane
+    uint8_t* code_lane8   = codes + 8 * lane; // byte rows: two words per lane
+
+    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last, its band start and left boundary
+    int32_t prev_bs     = -1;
+    int32_t prev_left_t = 0;
+    const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
+    int32_t best = best_floor, best_row = 0;
+    bool unranked = false;
+
+    // Descriptors travel in registers: chunk c* holds rows r0 .. r0 + 31 (one row per lane), chunk n* the next 32
+    // rows, loaded a chunk ahead; band starts likewise.  The row loop receives its descriptor by shuffle, issued one
+    // iteration early.
+    uint32_t c0 = 0, c1 = 0, c2 = 0, n0, n1, n2;
+    int32_t cbs = 0, nbs;
+    {
+        const int32_t rr = min(1 + lane, node_count);
+        n0  = desc.d0[rr];
+        n1  = desc.d1[rr];
+        n2  = desc.d2[rr];
+        nbs = band_start(rr, gradient, kFastBand, max_column);
+    }
+    uint32_t meta_next = __shfl_sync(kFull, n0, 0);
+    int32_t bs_next    = __shfl_sync(kFull, nbs, 0);
+
+    for (int32_t r = 1; r <= node_count; r++)
+    {
+        const int32_t k = (r - 1) & 31;
+        if (k == 0) // next chunk becomes current, fetch the one after
+        {
+            c0  = n0;
+            c1  = n1;
+            c2  = n2;
+            cbs = nbs;
+            const int32_t rr = min(r + 32 + lane, node_count);
+            n0  = desc.d0[rr];
+            n1  = desc.d1[rr];
+            n2  = desc.d2[rr];
+            nbs = band_start(rr, gradient, kFastBand, max_column);
+        }
+        const uint32_t meta   = meta_next;
+        const int32_t bs      = bs_next;
+        const int32_t pc      = (meta >> 8) & 0x3f;
+        const uint32_t pa     = meta & 0xff;              // profile row of the node's base; 4: not in the read
+        const int32_t ring_lo = max(r - kRingRows, 1);    // oldest row the ring still holds (never row 0)
+
+        // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
+        uint32_t Q0 = pdx2, Q1 = pdx2, Q2 = pdx2, Q3 = pdx2;
+        if (pa < static_cast<uint32_t>(kProfRows))
+        {
+            const uint32_t at = prof_l + pa * static_cast<uint32_t>(pstride) + static_cast<uint32_t>(bs);
+            const uint32_t lo = lds_u32(at); // bs is a multiple of 4: 4-byte aligned, not always 8
+            const uint32_t hi = lds_u32(at + 4);
+            Q0                = prmt(lo, hi, 0xC480u);
+            Q1                = prmt(lo, hi, 0xD591u);
+            Q2                = prmt(lo, hi, 0xE6A2u);
+            Q3                = prmt(lo, hi, 0xF7B3u);
+        }
+
+        int32_t min_d     = 1 << 20;   // smallest band shift over the predecessors
+        int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
+
+        // One predecessor row: its cells under this lane's cells (V_i) and the corner (D0 = (corner, V3.lo)); the
+        // diagonal operands are D_i = V_{i-1}.  All branches are warp-uniform (band shifts and row numbers are).
+        auto load_pred = [&](int32_t prow, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) {
+            int32_t d;
+            if (prow == r - 1 && bs == prev_bs)
+            {
+                // the row just written, same band start: its cells are still in this lane's registers; the corner is
+                // the last cell of the lane to the left (lane 0: that row's left boundary)
+                d  = 0;
+                V0 = prev_out.x;
+                V1 = prev_out.y;
+                V2 = prev_out.z;
+                V3 = prev_out.w;
+                uint32_t X = __shfl_up_sync(kFull, prev_out.w, 1);
+                if (lane == 0)
+                    X = static_cast<uint32_t>(prev_left_t) << 16;
+                D0        = __byte_perm(X, V3, 0x5432);
+                left_best = max(left_best, prev_left_t);
+            }
+            else if (prow >= ring_lo) // shared-memory ring
+            {
+                const uint32_t pa_ = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
+                const uint4 lead   = lds_v4(pa_);
+                d                  = bs - static_cast<int32_t>(lead.x); // >= 0, multiple of 4
+                const int32_t su   = lane + 1 + (d >> 3);               // block of the first vertical operand
+                const uint4 a      = lds_v4(pa_ + 16u * min(su, kPadBlock));
+                if (d & 4)
+                {
+                    // shift by an odd multiple of 4: operands straddle two blocks -> (hi of this block, lo of the
+                    // next); the corner is the low half of this block's last word
+                    const uint4 b = lds_v4(pa_ + 16u * min(su + 1, kPadBlock));
+                    V0            = __byte_perm(a.x, b.x, 0x5432);
+                    V1            = __byte_perm(a.y, b.y, 0x5432);
+                    V2            = __byte_perm(a.z, b.z, 0x5432);
+                    V3            = __byte_perm(a.w, b.w, 0x5432);
+                    D0            = __byte_perm(a.w, V3, 0x5410);
+                }
+                else
+                {
+                    // whole blocks: the corner is the high half of the previous block's last word (the lead block
+                    // for lane 0: the predecessor's left boundary)
+                    const uint32_t wv = lds_u32(pa_ + 16u * min(su - 1, kPadBlock) + 12u);
+                    V0                = a.x;
+                    V1                = a.y;
+                    V2                = a.z;
+                    V3                = a.w;
+                    D0                = __byte_perm(wv, V3, 0x5432);
+                }
+                left_best = max(left_best, hi16(lead.w));
+            }
+            else // far predecessor: its spilled copy (through L2); pad blocks are implied
+            {
+                const int32_t slot = (prow == 0) ? 0 : static_cast<int32_t>(slot_of[prow]);
+                const uint4* prow4 = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
+                const uint4 lead   = __ldcg(prow4);
+                d                  = bs - static_cast<int32_t>(lead.x);
+                const int32_t sl   = lane + 1 + (d >> 3);
+                const int32_t sc   = (8 * lane + d + 7) >> 3;
+                const uint32_t p33 = (prow == 0) ? pack2(0, kNegT) : NEG2; // row 0's first pad block
+                uint4 a = NEG4, b = NEG4;
+                uint32_t wv = NEG2;
+                if (sl <= 32)
+                    a = __ldcg(prow4 + sl);
+                else if (sl == 33)
+                    a = make_uint4(p33, p33, p33, p33);
+                if (sl + 1 <= 32)
+                    b = __ldcg(prow4 + sl + 1);
+                else if (sl + 1 == 33)
+                    b = make_uint4(p33, p33, p33, p33);
+                if (sc <= 32)
+                    wv = __ldcg(reinterpret_cast<const uint32_t*>(prow4 + sc) + 3);
+                else if (sc == 33)
+                    wv = p33;
+                const bool odd      = (d & 4) != 0;
+                const uint32_t selV = odd ? 0x5432u : 0x3210u;
+                V0                  = __byte_perm(a.x, b.x, selV);
+                V1                  = __byte_perm(a.y, b.y, selV);
+                V2                  = __byte_perm(a.z, b.z, selV);
+                V3                  = __byte_perm(a.w, b.w, selV);
+                D0                  = __byte_perm(odd ? a.w : wv, V3, odd ? 0x5410u : 0x5432u);
+                left_best           = max(left_best, hi16(lead.w));
+            }
+            min_d = min(min_d, d);
+            if (REBASED && d != 0)
+            {
+                // rebased rows: the predecessor's scores are relative to its own band start, beta * d below this
+                // row's.  Sentinel-class operands are lifted first so that the subtraction cannot wrap; real ones
+                // (>= kRealLo) are above the lift for every shift at which the bands still overlap.
+                const int32_t bd  = min(beta * d, 8000);
+                const uint32_t fl = pack2(kNegT + bd, kNegT + bd);
+                const uint32_t c2_ = pack2(-bd, -bd);
+                V0                = __vadd2(__vmaxs2(V0, fl), c2_);
+                V1                = __vadd2(__vmaxs2(V1, fl), c2_);
+                V2                = __vadd2(__vmaxs2(V2, fl), c2_);
+                V3                = __vadd2(__vmaxs2(V3, fl), c2_);
+                D0                = __vadd2(__vmaxs2(D0, fl), c2_);
+            }
+        };
+
+        // S_i: best diagonal / vertical candidate per cell; K_i: its move code (kind | predecessor slot << 2) under the
+        // assumption that the cell is not reached horizontally.
+        uint32_t S0, S1, S2, S3, K0, K1, K2, K3;
+        {
+            uint32_t V0, V1, V2, V3, D0;
+            load_pred(static_cast<int32_t>(meta >> 16), V0, V1, V2, V3, D0); // predecessor 0 (row 0 for a source node)
+            {
+                // descriptor of the next row, needed first thing next iteration
+                const int32_t kn = r & 31;
+                meta_next        = __shfl_sync(kFull, kn ? c0 : n0, kn);
+                bs_next          = __shfl_sync(kFull, kn ? cbs : nbs, kn);
+            }
+            const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
+            const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
+            const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
+            const uint32_t dq3 = __viaddmax_s16x2(V2, Q3, NEG2);
+            if (pc <= 1)
+            {
+                S0 = __viaddmax_s16x2(V0, gapv, dq0);
+                S1 = __viaddmax_s16x2(V1, gapv, dq1);
+                S2 = __viaddmax_s16x2(V2, gapv, dq2);
+                S3 = __viaddmax_s16x2(V3, gapv, dq3);
+                K0 = vminu2_1(S0 ^ dq0); // 0: the diagonal explains the cell, 1: only the vertical move does
+                K1 = vminu2_1(S1 ^ dq1);
+                K2 = vminu2_1(S2 ^ dq2);
+                K3 = vminu2_1(S3 ^ dq3);
+            }
+            else
+            {
+                // several predecessors: the best diagonal and the best vertical candidate with the slot of the FIRST
+                // predecessor that attains each (the reference tries predecessors in slot order)
+                uint32_t bD0 = dq0, bD1 = dq1, bD2 = dq2, bD3 = dq3;
+                uint32_t bV0 = __viaddmax_s16x2(V0, gapv, NEG2), bV1 = __viaddmax_s16x2(V1, gapv, NEG2),
+                         bV2 = __viaddmax_s16x2(V2, gapv, NEG2), bV3 = __viaddmax_s16x2(V3, gapv, NEG2);
+                uint32_t iD0 = 0, iD1 = 0, iD2 = 0, iD3 = 0, iV0 = 0, iV1 = 0, iV2 = 0, iV3 = 0;
+                const uint32_t p12 = __shfl_sync(kFull, c1, k);
+                const uint32_t p34 = (pc > 3) ? __shfl_sync(kFull, c2, k) : 0u;
+                for (int32_t p = 1; p < pc; p++)
+                {
+                    load_pred(pred_row<IdT>(g, meta, p12, p34, r, p), V0, V1, V2, V3, D0);
+                    const uint32_t pp = pack2(p, p);
+                    auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
+                        const uint32_t nb  = __vmaxs2(bestv, cand);
+                        const uint32_t chg = vminu2_1(nb ^ bestv) * 0xffffu; // 0xffff where cand is strictly better
+                        idx                = (idx & ~chg) | (pp & chg);
+                        bestv              = nb;
+                    };
+                    better(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
+                    better(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));
+                    better(bD2, iD2, __viaddmax_s16x2(V1, Q2, NEG2));
+                    better(bD3, iD3, __viaddmax_s16x2(V2, Q3, NEG2));
+                    better(bV0, iV0, __viaddmax_s16x2(V0, gapv, NEG2));
+                    better(bV1, iV1, __viaddmax_s16x2(V1, gapv, NEG2));
+                    better(bV2, iV2, __viaddmax_s16x2(V2, gapv, NEG2));
+                    better(bV3, iV3, __viaddmax_s16x2(V3, gapv, NEG2));
+                }
+                auto join = [&](uint32_t& S, uint32_t& K, uint32_t bD, uint32_t iD, uint32_t bV, uint32_t iV) {
+                    S                   = __vmaxs2(bD, bV);
+                    const uint32_t vert = vminu2_1(S ^ bD);     // 1 where no diagonal candidate reaches S
+                    const uint32_t vm   = vert * 0xffffu;
+                    K                   = vert + 4u * ((iD & ~vm) | (iV & vm));
+                };
+                join(S0, K0, bD0, iD0, bV0, iV0);
+                join(S1, K1, bD1, iD1, bV1, iV1);
+                join(S2, K2, bD2, iD2, bV2, iV2);
+                join(S3, K3, bD3, iD3, bV3, iV3);
+            }
+        }
+        // every predecessor wholly left of this row's band: sentinel arithmetic would decide the row
+        if (min_d > kFastBand)
+            return kFastNotTaken;
+
+        // left boundary of this row in the tilted domain (a source node's predecessor is row 0, whose boundary is 0)
+        int32_t left_t = kNegT;
+        if (bs == 0)
+            left_t = static_cast<int16_t>(left_best + gap);
+
+        // horizontal pass = prefix maximum, both halves at once
+        const uint32_t P1 = __vmaxs2(S1, S0);
+        const uint32_t P2 = __vmaxs2(S2, P1);
+        const uint32_t P3 = __vmaxs2(S3, P2);
+        const uint32_t tl = __byte_perm(P3, NEG2, 0x1054); // (NEG, P3.lo): cells 0..3 feed cells 4..7
+        uint32_t tot      = __vmaxs2(P3, tl);              // hi half = maximum over this lane's 8 cells
+        // exclusive prefix maximum over the lanes (Kogge-Stone on the values shifted by one lane)
+        {
+            uint32_t e = __shfl_up_sync(kFull, tot, 1);
+            if (lane == 0)
+                e = static_cast<uint32_t>(left_t) << 16;
+            uint32_t u;
+            u = __shfl_up_sync(kFull, e, 1);
+            e = __vmaxs2(e, u); // lanes below the shift receive their own value: harmless for a maximum
+            u = __shfl_up_sync(kFull, e, 2);
+            e = __vmaxs2(e, u);
+            u = __shfl_up_sync(kFull, e, 4);
+            e = __vmaxs2(e, u);
+            u = __shfl_up_sync(kFull, e, 8);
+            e = __vmaxs2(e, u);
+            u = __shfl_up_sync(kFull, e, 16);
+            tot = __vmaxs2(e, u);
+        }
+        const uint32_t cb = __byte_perm(tot, tot, 0x3232);
+        uint4 out;
+        out.x = __vimax3_s16x2(S0, cb, tl);
+        out.y = __vimax3_s16x2(P1, cb, tl);
+        out.z = __vimax3_s16x2(P2, cb, tl);
+        out.w = __vimax3_s16x2(P3, cb, tl);
+        if (REBASED)
+        {
+            // rebased rows carry no a-priori range: every stored cell must be sentinel class or inside
+            // [kRealLo, kRealHi].  Cells grow along the row, so the lane's first and last cell decide the common case.
+            const bool lane_ok = lo16(out.x) >= kRealLo && hi16(out.w) <= kRealHi;
+            if (!__all_sync(kFull, lane_ok))
+            {
+                auto bad = [](uint32_t reg) {
+                    const int32_t lo = lo16(reg), hi = hi16(reg);
+                    return (lo > kNegThreshold && lo < kRealLo) || lo > kRealHi || (hi > kNegThreshold && hi < kRealLo) ||
+                           hi > kRealHi;
+                };
+                if (__any_sync(kFull, bad(out.x) || bad(out.y) || bad(out.z) || bad(out.w)))
+                    return kFastNotTaken;
+            }
+        }
+        // move codes: a cell whose value exceeds its own candidate was reached horizontally
+        K0 += 2u * vminu2_1(out.x ^ S0);
+        K1 += 2u * vminu2_1(out.y ^ S1);
+        K2 += 2u * vminu2_1(out.z ^ S2);
+        K3 += 2u * vminu2_1(out.w ^ S3);
+        uint8_t* code_row = static_cast<uint8_t*>(nullptr) + static_cast<int64_t>(r) * kCodeRowBytes;
+        if (pc <= kWidePreds)
+        {
+            // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
+            const uint32_t w = K0 + 16u * K1 + 256u * K2 + 4096u * K3;
+            __stcg(reinterpret_cast<uint32_t*>(code_lane4 + (code_row - static_cast<uint8_t*>(nullptr))), w);
+        }
+        else
+        {
+            const uint32_t t01 = __byte_perm(K0, K1, 0x6240); // c0 c1 c4 c5
+            const uint32_t t23 = __byte_perm(K2, K3, 0x6240); // c2 c3 c6 c7
+            __stcg(reinterpret_cast<uint2*>(code_lane8 + (code_row - static_cast<uint8_t*>(nullptr))),
+                   make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
+        }
+
+        const uint32_t rrow = ring + static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
+        sts_v4(rrow + 16u + 16u * lane, out);
+        const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, static_cast<uint32_t>(left_t) << 16);
+        if (lane == 0)
+            sts_v4(rrow, lead);
+        if (meta & (1u << 15)) // a later row reads this one from beyond the ring
+        {
+            const int32_t kk   = (r - 1) & 31;
+            uint32_t my_slot   = (r <= node_count) ? static_cast<uint32_t>(slot_of[r]) : 0u; // uniform address
+            (void)kk;
+            uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(my_slot) * (kSpillRowBytes / 4));
+            __stcg(dst + 1 + lane, out);
+            if (lane == 0)
+                __stcg(dst, lead);
+        }
+        if (meta & (1u << 14))
+        {
+            // sink row: its score at column read_len (all candidates share the column, so tilted scores compare like
+            // the scores themselves); first strict maximum in row order (cudapoa_nw_banded.cuh:372-383)
+            const int32_t c = read_len - bs - 1; // 0-based cell of the band
+            int32_t t       = kNegT;
+            if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && read_len != 0)
+            {
+                const int32_t q  = c & 3;
+                const uint32_t w = (q == 0) ? out.x : (q == 1) ? out.y : (q == 2) ? out.z : out.w;
+                const int32_t v  = (c & 4) ? hi16(w) : lo16(w);
+                t                = __shfl_sync(kFull, v, c >> 3);
+            }
+            else if (read_len == 0 || c == -1)
+            {
+                t = static_cast<int16_t>(left_t);
+            }
+            if (t <= kNegThreshold)
+                t = kNegT;
+            int32_t s = t;
+            if (REBASED)
+            {
+                s = (t == kNegT) ? kNegAbs : t + beta * bs;
+                unranked |= (t == kNegT);
+            }
+            if (s > best)
+            {
+                best     = s;
+                best_row = r;
+            }
+        }
+        prev_out    = out;
+        prev_bs     = bs;
+        prev_left_t = static_cast<int16_t>(left_t);
+        __syncwarp();
+    }
+
+    if (unranked)
+        return kFastNotTaken; // a sink row whose band misses the last column cannot be ranked on rebased scores
+    if (best > best_floor)
+    {
+        // the start cell must be a real score (the walk compares nothing, but the exact path decides sentinel rows)
+        if (!REBASED && best <= kNegThreshold)
+            return kFastNotTaken;
+        start_row = best_row;
+    }
+    else
+    {
+        // no sink row: the reference starts from row 0, whose cell at column read_len is real up to column band + 3
+        if (read_len > kFastBand + 3)
+            return kFastNotTaken;
+        start_row = 0;
+    }
+    return 0;
+}
+
+} // namespace poa_b200
