@@ -628,7 +628,7 @@ bool B200Batch::launch_split(KernelParams& P)
     // shared memory per window: the fill needs the row ring and the padded read, the graph phases the traceback
     // tile and the read (the topological sort and the consensus reuse that scratch)
     const int32_t L          = std::max(batch_size_.max_sequence_size, 1);
-    const int32_t fill_smem  = (kRingBytes + ((L + kFastBand + 8 + 15) & ~15) + 255) & ~255;
+    const int32_t fill_smem  = (fill2_smem_bytes(L) + 255) & ~255;
     const int32_t graph_smem = (kTileBytes + ((L + 15) & ~15) + 255) & ~255;
     const int32_t graph_smem_large = std::max(graph_smem, kSmemPerWarp);
     if (4 * std::max(fill_smem, graph_smem_large) > kPhaseSmemLimit)

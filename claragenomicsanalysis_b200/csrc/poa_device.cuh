@@ -32,6 +32,7 @@ constexpr unsigned kFull = 0xffffffffu;
 // Emulator build (tests/emu, test infrastructure): shared addresses are bounds- and alignment-checked offsets into the
 // emulated block's shared memory.
 #define POA_DYNAMIC_SMEM(name) uint8_t* name = poa_emu::smem_base()
+#define POA_COUNT(name) poa_emu::count(name)
 template <typename T>
 inline T* emu_shared(uint32_t a, int line)
 {
@@ -75,6 +76,7 @@ inline void sts_v4(uint32_t a, uint4 v, int line = __builtin_LINE()) { *emu_shar
 inline uint32_t prmt(uint32_t x, uint32_t y, uint32_t s) { return poa_emu_prmt(x, y, s); }
 #else
 #define POA_DYNAMIC_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
+#define POA_COUNT(name)
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -55,7 +55,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
     const int32_t pd_x = mismatch - gap; // bases differ
-    if (sizeof(IdT) != 2 || pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128)
+    if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128)
         return kFastNotTaken;
     const int64_t code_bytes  = static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
     const int32_t spill_slots = static_cast<int32_t>(min(static_cast<long long>(65535),
@@ -224,13 +224,14 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     // Descriptors travel in registers: chunk c* holds rows r0 .. r0 + 31 (one row per lane), chunk n* the next 32
     // rows, loaded a chunk ahead; band starts likewise.  The row loop receives its descriptor by shuffle, issued one
     // iteration early.
-    uint32_t c0 = 0, c1 = 0, c2 = 0, n0, n1, n2;
+    uint32_t c0 = 0, c1 = 0, c2 = 0, cs = 0, n0, n1, n2, ns;
     int32_t cbs = 0, nbs;
     {
         const int32_t rr = min(1 + lane, node_count);
         n0  = desc.d0[rr];
         n1  = desc.d1[rr];
         n2  = desc.d2[rr];
+        ns  = slot_of[rr]; // meaningful for rows marked for spilling only
         nbs = band_start(rr, gradient, kFastBand, max_column);
     }
     uint32_t meta_next = __shfl_sync(kFull, n0, 0);
@@ -244,11 +245,13 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             c0  = n0;
             c1  = n1;
             c2  = n2;
+            cs  = ns;
             cbs = nbs;
             const int32_t rr = min(r + 32 + lane, node_count);
             n0  = desc.d0[rr];
             n1  = desc.d1[rr];
             n2  = desc.d2[rr];
+            ns  = slot_of[rr];
             nbs = band_start(rr, gradient, kFastBand, max_column);
         }
         const uint32_t meta   = meta_next;
@@ -281,6 +284,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             {
                 // the row just written, same band start: its cells are still in this lane's registers; the corner is
                 // the last cell of the lane to the left (lane 0: that row's left boundary)
+                POA_COUNT("fill2.pred_registers");
                 d  = 0;
                 V0 = prev_out.x;
                 V1 = prev_out.y;
@@ -294,6 +298,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             }
             else if (prow >= ring_lo) // shared-memory ring
             {
+                POA_COUNT("fill2.pred_ring");
                 const uint32_t pa_ = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
                 const uint4 lead   = lds_v4(pa_);
                 d                  = bs - static_cast<int32_t>(lead.x); // >= 0, multiple of 4
@@ -325,6 +330,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             }
             else // far predecessor: its spilled copy (through L2); pad blocks are implied
             {
+                POA_COUNT("fill2.pred_spilled");
                 const int32_t slot = (prow == 0) ? 0 : static_cast<int32_t>(slot_of[prow]);
                 const uint4* prow4 = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
                 const uint4 lead   = __ldcg(prow4);
@@ -499,18 +505,19 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         K1 += 2u * vminu2_1(out.y ^ S1);
         K2 += 2u * vminu2_1(out.z ^ S2);
         K3 += 2u * vminu2_1(out.w ^ S3);
-        uint8_t* code_row = static_cast<uint8_t*>(nullptr) + static_cast<int64_t>(r) * kCodeRowBytes;
+        const int64_t code_row = static_cast<int64_t>(r) * kCodeRowBytes;
+        POA_COUNT(pc <= 1 ? "fill2.rows_1pred" : pc <= kWidePreds ? "fill2.rows_2to4pred" : "fill2.rows_wide");
         if (pc <= kWidePreds)
         {
             // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
             const uint32_t w = K0 + 16u * K1 + 256u * K2 + 4096u * K3;
-            __stcg(reinterpret_cast<uint32_t*>(code_lane4 + (code_row - static_cast<uint8_t*>(nullptr))), w);
+            __stcg(reinterpret_cast<uint32_t*>(code_lane4 + code_row), w);
         }
         else
         {
             const uint32_t t01 = __byte_perm(K0, K1, 0x6240); // c0 c1 c4 c5
             const uint32_t t23 = __byte_perm(K2, K3, 0x6240); // c2 c3 c6 c7
-            __stcg(reinterpret_cast<uint2*>(code_lane8 + (code_row - static_cast<uint8_t*>(nullptr))),
+            __stcg(reinterpret_cast<uint2*>(code_lane8 + code_row),
                    make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
         }
 
@@ -521,9 +528,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             sts_v4(rrow, lead);
         if (meta & (1u << 15)) // a later row reads this one from beyond the ring
         {
-            const int32_t kk   = (r - 1) & 31;
-            uint32_t my_slot   = (r <= node_count) ? static_cast<uint32_t>(slot_of[r]) : 0u; // uniform address
-            (void)kk;
+            POA_COUNT("fill2.rows_spilled");
+            const uint32_t my_slot = __shfl_sync(kFull, cs, k);
             uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(my_slot) * (kSpillRowBytes / 4));
             __stcg(dst + 1 + lane, out);
             if (lane == 0)
@@ -577,8 +583,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     }
     else
     {
-        // no sink row: the reference starts from row 0, whose cell at column read_len is real up to column band + 3
-        if (read_len > kFastBand + 3)
+        // no sink row: the reference starts from row 0, whose cell at column read_len is inside its band up to column band
+        if (read_len > kFastBand)
             return kFastNotTaken;
         start_row = 0;
     }

@@ -16,6 +16,7 @@
 
 #include "poa_device.cuh"
 #include "poa_fast.cuh"
+#include "poa_trace2.cuh"
 
 namespace poa_b200
 {
@@ -24,7 +25,7 @@ constexpr int32_t kFillWarpsPerBlock  = 4;
 constexpr int32_t kGraphWarpsPerBlock = 4;
 constexpr int32_t kTileBytes          = kTileAndDescBytes; // traceback tile + its row descriptors
 #ifndef POA_FILL_MIN_BLOCKS
-#define POA_FILL_MIN_BLOCKS 7
+#define POA_FILL_MIN_BLOCKS 6
 #endif
 
 // First launch of a batch: per-window state and the backbone from read 0 (cudapoa_kernels.cuh:171-209).
@@ -96,14 +97,15 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
                 // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
                 // registers and instruction cache of this one belong to the loop the benchmark spends half its time in.
-                const int32_t beta = (P.smem_per_warp >= fast_fill_smem_bytes(len))
+                const int32_t beta = (P.smem_per_warp >= fill2_smem_bytes(len))
                                          ? fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match)
                                          : -1;
                 if (beta > 0)
                     aln_len = kAlnNeedsRebased;
                 else if (beta == 0 &&
-                         fast_fill_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.gap,
-                                                    P.mismatch, P.match, smem, lane, start_row, 0, nullptr) == 0)
+                         fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
+                                                P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
+                                                P.gap, P.mismatch, P.match, smem, lane, start_row, 0) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
@@ -150,11 +152,11 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
         const int32_t len   = P.read_len[wd.read_off + s];
         const uint8_t* seq  = P.bases + wd.base_off + st.seq_off;
         ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
-        int32_t aln_score   = 0;
         int32_t start_row   = 0;
         const int32_t beta  = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
-        if (beta > 0 && fast_fill_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<int16_t*>(scores), P.gap,
-                                                  P.mismatch, P.match, smem, lane, start_row, beta, &aln_score) == 0)
+        if (beta > 0 && fill2_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
+                                              P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
+                                              P.gap, P.mismatch, P.match, smem, lane, start_row, beta) == 0)
         {
             st.aln_len   = kAlnPendingTraceback;
             st.start_row = start_row;
@@ -237,8 +239,7 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
         // the scratch is legal, the sort and the consensus then run out of global memory)
         const WindowDesc wd = P.windows[w];
         const int32_t fits  = (s >= wd.n_reads - 1) ? P.class_cap_final : P.class_cap; // last read: consensus too
-        const bool other   = st.node_count + kClassMargin > fits ||
-                           (P.lean_class0 && (P.spoa_accurate || (st.aln_len == kAlnPendingTraceback && st.beta != 0)));
+        const bool other   = st.node_count + kClassMargin > fits || (P.lean_class0 && P.spoa_accurate);
         if (other != (P.phase_class == 1))
             continue;
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
@@ -252,14 +253,9 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
             int32_t aln_len    = st.aln_len;
             if (aln_len == kAlnPendingTraceback)
             {
-                int16_t* scores = reinterpret_cast<int16_t*>(static_cast<ScoreT*>(P.scores) +
-                                                             static_cast<int64_t>(w) * P.banded_score_stride);
-                if (LEAN)
-                    aln_len = fast_traceback_impl<IdT, false>(g, st.node_count, seq, len, scores, P.gap, P.mismatch,
-                                                              P.match, smem, smem + kTileBytes, st.start_row, lane, 0);
-                else
-                    aln_len = fast_traceback<IdT>(g, st.node_count, seq, len, scores, P.gap, P.mismatch, P.match, smem,
-                                                  smem + kTileBytes, st.start_row, lane, st.beta);
+                const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
+                                                                       static_cast<int64_t>(w) * P.banded_score_stride);
+                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, st.start_row, lane);
             }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {

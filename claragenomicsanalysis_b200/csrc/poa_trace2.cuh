@@ -1,0 +1,154 @@
+// Traceback over the move codes written by fill2_impl (poa_fill2.cuh).
+//
+// The reference re-derives every move from stored scores (cudapoa_nw_banded.cuh:386-474); here the fill has already
+// decided, per cell, which move that derivation takes (kind + predecessor slot), so a step of the walk is: load the
+// cell's code, load the row's descriptor, move.  Lane 0 walks; the warp stages the codes of 64 rows x 64 columns around
+// the walk into shared memory (2 KB, column-aligned so that a cell's nibble is addressed by (row, column) alone) with
+// the rows' descriptors (predecessor rows).  Rows with more than kWidePreds predecessors keep a byte per cell in global
+// memory and are read from there.
+//
+// Output as fast_traceback_impl's: g.aln_node[k] = node paired with read position k, or -1 for an inserted base.
+#pragma once
+
+#include "poa_fill2.cuh"
+
+namespace poa_b200
+{
+
+constexpr int32_t kT2Rows      = 64;
+constexpr int32_t kT2Cols      = 64;                     // columns per tile, a multiple of 8
+constexpr int32_t kT2RowBytes  = kT2Cols / 2;            // nibbles
+constexpr int32_t kT2TileBytes = kT2Rows * kT2RowBytes;  // 2 KB
+constexpr int32_t kT2Bytes     = kT2TileBytes + kT2Rows * 8; // + descriptors (d0, d1) per row
+
+// Returns the alignment length (> 0), or -1 if a code is not a move (cannot happen for codes the fill wrote; kept as the
+// reference's loop-count guard).  All 32 lanes.
+template <typename IdT>
+__device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t read_len, const uint8_t* area,
+                               uint32_t tile, int32_t start_row, int32_t lane)
+{
+    const uint8_t* codes = area;
+    RowDesc desc;
+    desc.d0 = g.rowinfo;
+    desc.d1 = desc.d0 + (g.M + 40);
+    desc.d2 = desc.d1 + (g.M + 40);
+    const int32_t max_column = read_len + 1;
+    const float gradient     = band_gradient(read_len, node_count);
+    const uint32_t tile_desc = tile + kT2TileBytes;
+
+    int32_t i = start_row, j = read_len;
+    int32_t steps = 0;
+    bool broken   = false;
+    while (i > 0 && j > 0 && !broken) // uniform: i, j are broadcast at the end of every round
+    {
+        // tile: rows tile_r0 .. tile_r0 + 63 (the walk's row is the last one), columns tile_c0 .. tile_c0 + 63 with
+        // tile_c0 = 1 (mod 8) and j among the last eight
+        POA_COUNT("trace2.tiles");
+        const int32_t tile_r0 = i - (kT2Rows - 1);
+        const int32_t tile_c0 = ((j - 1) & ~7) + 1 - (kT2Cols - 8);
+#pragma unroll
+        for (int32_t u = 0; u < kT2Rows / 32; u++)
+        {
+            const int32_t tr = lane + 32 * u;
+            const int32_t r  = tile_r0 + tr;
+            uint32_t w[kT2Cols / 8 + 1];
+            uint2 dsc = make_uint2(0u, 0u);
+            int32_t c0 = 0;
+            if (r >= 1)
+            {
+                dsc              = make_uint2(desc.d0[r], desc.d1[r]);
+                const int32_t b  = band_start(r, gradient, kFastBand, max_column);
+                c0               = tile_c0 - b - 1;       // band cell under the tile's first column, a multiple of 4
+                const int32_t w0 = c0 >> 3;               // first word of the row the tile needs (floor division)
+                const uint32_t* row = reinterpret_cast<const uint32_t*>(codes + static_cast<int64_t>(r) * kCodeRowBytes);
+#pragma unroll
+                for (int32_t q = 0; q <= kT2Cols / 8; q++)
+                {
+                    const int32_t wi = w0 + q;
+                    w[q]             = (static_cast<uint32_t>(wi) < 32u) ? __ldcg(row + wi) : 0xEEEEEEEEu; // outside the band
+                }
+            }
+            else
+            {
+#pragma unroll
+                for (int32_t q = 0; q <= kT2Cols / 8; q++)
+                    w[q] = 0xEEEEEEEEu;
+            }
+            // column-align: when the tile's first column falls in the middle of a word, shift by half a word
+            const uint32_t sel = (c0 & 4) ? 0x5432u : 0x3210u;
+            const uint32_t at  = tile + static_cast<uint32_t>(tr * kT2RowBytes);
+            sts_v4(at, make_uint4(__byte_perm(w[0], w[1], sel), __byte_perm(w[1], w[2], sel), __byte_perm(w[2], w[3], sel),
+                                  __byte_perm(w[3], w[4], sel)));
+            sts_v4(at + 16u, make_uint4(__byte_perm(w[4], w[5], sel), __byte_perm(w[5], w[6], sel),
+                                        __byte_perm(w[6], w[7], sel), __byte_perm(w[7], w[8], sel)));
+            sts_v2(tile_desc + 8u * static_cast<uint32_t>(tr), dsc);
+        }
+        __syncwarp();
+        if (lane == 0)
+        {
+            const int32_t row_floor = max(tile_r0, 1);
+            while (i >= row_floor && j >= tile_c0 && j > 0)
+            {
+                const int32_t tr    = i - tile_r0;
+                const uint2 dd      = lds_v2(tile_desc + 8u * static_cast<uint32_t>(tr));
+                const uint32_t meta = dd.x;
+                const int32_t pc    = (meta >> 8) & 0x3f;
+                uint32_t code;
+                if (pc <= kWidePreds)
+                {
+                    const int32_t x  = j - tile_c0; // 0 .. 63
+                    const uint32_t w = lds_u32(tile + static_cast<uint32_t>(tr * kT2RowBytes + ((x >> 3) << 2)));
+                    code             = (w >> ((x & 7) * 4)) & 0xfu;
+                }
+                else
+                {
+                    POA_COUNT("trace2.wide_steps");
+                    const int32_t b = band_start(i, gradient, kFastBand, max_column);
+                    code            = __ldcg(codes + static_cast<int64_t>(i) * kCodeRowBytes + (j - b - 1));
+                }
+                steps++;
+                if (code & 2u)
+                {
+                    g.aln_node[j - 1] = static_cast<IdT>(0); // horizontal: an inserted base
+                    j--;
+                    continue;
+                }
+                const int32_t p = static_cast<int32_t>(code >> 2);
+                if (p >= max(pc, 1))
+                {
+                    broken = true; // not a code the fill writes
+                    break;
+                }
+                int32_t pi;
+                if (p == 0)
+                    pi = static_cast<int32_t>(meta >> 16);
+                else
+                    pi = pred_row<IdT>(g, meta, dd.y, (p > 2) ? desc.d2[i] : 0u, i, p);
+                if ((code & 1u) == 0u)
+                {
+                    g.aln_node[j - 1] = static_cast<IdT>(i); // diagonal: the base pairs with this row's node
+                    j--;
+                }
+                i = pi;
+            }
+        }
+        i      = __shfl_sync(kFull, i, 0);
+        j      = __shfl_sync(kFull, j, 0);
+        broken = __shfl_sync(kFull, static_cast<int32_t>(broken), 0) != 0;
+        __syncwarp();
+    }
+    steps = __shfl_sync(kFull, steps, 0);
+    if (broken)
+        return -1;
+    // the walk reached row 0 (the remaining bases are inserted before the graph's first node) or column 0
+    // g.aln_node[] holds ROW indices (0: inserted base); they become node ids here
+    __syncwarp();
+    for (int32_t k = lane; k < read_len; k += 32)
+    {
+        const int32_t row = (k < j) ? 0 : static_cast<int32_t>(g.aln_node[k]);
+        g.aln_node[k]     = static_cast<IdT>(row > 0 ? static_cast<int32_t>(g.sorted[row - 1]) : -1);
+    }
+    return max(steps + j, 1);
+}
+
+} // namespace poa_b200

@@ -216,6 +216,7 @@ enum Op
 uint32_t collective(unsigned mask, Op op, uint32_t value, int arg, int width, int line);
 
 float rcp_approx(float d); // MUFU.RCP as measured on a B200 (tests/golden/b200_mufu_rcp_u16.npy)
+void count(const char* name, long long n = 1); // coverage counters: which device-code paths a test exercised
 
 } // namespace poa_emu
 

@@ -2,6 +2,7 @@
 // collectives, the kernel launcher and the MUFU.RCP table.
 #include "poa_emu.hpp"
 
+#include <map>
 #include <string>
 #include <vector>
 
@@ -303,4 +304,30 @@ float rcp_approx(float d)
     return 1.0f / d;
 }
 
+static std::map<std::string, long long>& counters()
+{
+    static std::map<std::string, long long> c;
+    return c;
+}
+void count(const char* name, long long n)
+{
+    if (lane_id() <= 0) // once per warp
+        counters()[name] += n;
+}
+
 } // namespace poa_emu
+
+// "name=value;..." of the coverage counters since the last call
+extern "C" int poa_emu_counters(char* buf, int cap)
+{
+    std::string out;
+    for (const auto& kv : poa_emu::counters())
+        out += kv.first + "=" + std::to_string(kv.second) + ";";
+    poa_emu::counters().clear();
+    if (buf != nullptr && cap > 0)
+    {
+        std::strncpy(buf, out.c_str(), static_cast<size_t>(cap) - 1);
+        buf[cap - 1] = 0;
+    }
+    return static_cast<int>(out.size());
+}
