@@ -812,18 +812,26 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
     }
 }
 
-// The same order computed in the warp's shared-memory scratch: all lanes stage in-degrees and the first three
-// out-edges of every node (coalesced), lane 0 runs the FIFO at shared-memory latency and writes sorted[] and
-// node_id_to_pos[] as nodes leave the queue.  Returns false when the graph does not fit the scratch or the queue
-// ring is overrun (sorted[] / node_id_to_pos[] may then be partly written); the caller then runs topsort_kahn, which
-// rewrites both.  All 32 lanes call this.
-constexpr int32_t kKahnBytesPerNode = 8;   // record {edge0, edge1, edge2, out-degree, remaining in-degree}
-constexpr int32_t kKahnQueueEntries = 128; // the FIFO is a ring: a POA graph's frontier is a handful of nodes
+// The same order computed in the warp's shared-memory scratch.  All 32 lanes call this.
+//   * the warp stages one 4-byte record per node (coalesced reads of the slot-major graph arrays):
+//       out-edge 0 | out-edge 1 << 12 | min(out-degree, 3) << 24 | remaining in-degree << 26
+//     and a 2-byte side record (out-edge 2 | min(out-degree - 3, 15) << 12), read only for nodes with three or more
+//     out-edges; node ids must fit 12 bits;
+//   * the FIFO is a full-length array that ends up holding the order itself (as the reference's sorted_poa doubles as
+//     its queue, cudapoa_topsort.cuh:56-85), so the serial lane never stores to global memory; when it is done the
+//     warp writes sorted[] and node_id_to_pos[] out in parallel;
+//   * lane 0 runs the FIFO.  A POA graph is mostly chains: the node popped next is usually the one pushed last, whose
+//     record the push has just had in registers -- it is kept there, so a chain step is one shared-memory load
+//     (the child's record), one store (its decremented in-degree) and one 2-byte store (the queue).
+// Returns false (nothing written) when the graph does not fit the scratch; the caller then runs topsort_kahn.
+constexpr int32_t kKahnBytesPerNode = 8; // 4 (record) + 2 (side record) + 2 (queue entry == sorted[])
+constexpr int32_t kKahnMaxNodes     = 4095;
 
 // Nodes a graph may have for the sort to run out of `smem_bytes` of scratch.
 __host__ __device__ inline int32_t kahn_smem_nodes(int32_t smem_bytes)
 {
-    return ((smem_bytes - 2 * kKahnQueueEntries) / kKahnBytesPerNode) & ~7;
+    const int32_t n = (smem_bytes / kKahnBytesPerNode) & ~7;
+    return n < kKahnMaxNodes ? n : (kKahnMaxNodes & ~7);
 }
 
 template <typename IdT>
@@ -835,9 +843,9 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
     const int32_t cap = kahn_smem_nodes(smem_bytes);
     if (node_count > cap)
         return false;
-    const uint32_t rec   = smem;           // uint2[cap]: x = edge0 | edge1 << 16, y = edge2 | out-degree << 16 | in-degree << 24
-    const uint32_t queue = rec + 8 * cap;  // u16[kKahnQueueEntries], a ring indexed by pop / push counts
-    constexpr uint32_t kQMask = kKahnQueueEntries - 1;
+    const uint32_t rec   = smem;                 // u32[cap]
+    const uint32_t queue = rec + 4u * cap;       // u16[cap]: FIFO, in the end the order
+    const uint32_t side  = queue + 2u * cap;     // u16[cap]
     const unsigned lt    = (1u << lane) - 1u;
     int32_t tail         = 0;
 #pragma unroll 2
@@ -850,71 +858,85 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
             const uint32_t ic = g.in_cnt[n];
             const uint32_t oc = g.out_cnt[n];
             // slots beyond the out-degree hold stale but readable values: load unconditionally, never used
-            const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0));
-            const uint32_t e1 = static_cast<uint16_t>(g.out_edge(n, 1));
-            const uint32_t e2 = static_cast<uint16_t>(g.out_edge(n, 2));
-            sts_v2(rec + 8 * n, make_uint2(e0 | (e1 << 16), e2 | (oc << 16) | (ic << 24)));
+            const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0)) & 0xfffu;
+            const uint32_t e1 = static_cast<uint16_t>(g.out_edge(n, 1)) & 0xfffu;
+            const uint32_t e2 = static_cast<uint16_t>(g.out_edge(n, 2)) & 0xfffu;
+            sts_u32(rec + 4u * n, e0 | (e1 << 12) | (min(oc, 3u) << 24) | (ic << 26));
+            sts_u16(side + 2u * n, e2 | (min(max(oc, 3u) - 3u, 15u) << 12));
             source = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
-        if (tail + __popc(mask) > kKahnQueueEntries) // more sources than the ring holds (uniform; nothing written yet)
-            return false;
         if (source)
-            sts_u16(queue + 2 * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
+            sts_u16(queue + 2u * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
         tail += __popc(mask);
     }
     __syncwarp();
-    int32_t ok = 1;
     if (lane == 0)
     {
-        // sorted[] and node_id_to_pos[] are written as nodes leave the queue (nothing waits for these stores)
-        uint32_t head   = 0;                                   // nodes popped so far == rank of the next node
-        uint32_t pushed = static_cast<uint32_t>(tail);         // nodes queued so far
-        IdT* sorted_out = g.sorted;
+        constexpr uint32_t kOne = 1u << 26; // one in-edge
+        uint32_t head   = 0;                // nodes popped so far == rank of the node in hand
+        uint32_t pushed = static_cast<uint32_t>(tail);
+        uint32_t node   = lds_u16(queue);   // a graph always has a source
+        uint32_t v      = lds_u32(rec + 4u * node);
+        uint32_t last_node = 0, last_rec = 0, last_at = 0xffffffffu; // the node pushed last, its record and queue index
         // visit(child): one in-edge of child is satisfied; queue it when it was the last one
-#define POA_KAHN_VISIT(child_expr)                                  \
-    {                                                               \
-        const uint32_t child_ = (child_expr);                       \
-        const uint32_t da_    = rec + 8 * child_ + 7;               \
-        const uint32_t c_     = lds_u8(da_) - 1;                    \
-        sts_u8(da_, c_);                                            \
-        if (c_ == 0)                                                \
-        {                                                           \
-            sts_u16(queue + 2 * (pushed & kQMask), child_);         \
-            pushed++;                                               \
-        }                                                           \
+#define POA_KAHN_VISIT(child_expr)                                   \
+    {                                                                \
+        const uint32_t child_ = (child_expr);                        \
+        const uint32_t at_    = rec + 4u * child_;                   \
+        const uint32_t left_  = lds_u32(at_) - kOne;                 \
+        sts_u32(at_, left_);                                         \
+        if (left_ < kOne)                                            \
+        {                                                            \
+            sts_u16(queue + 2u * pushed, child_);                    \
+            last_node = child_;                                      \
+            last_rec  = left_;                                       \
+            last_at   = pushed;                                      \
+            pushed++;                                                \
+        }                                                            \
     }
-        while (true)
+        for (;;)
         {
-            const uint32_t node = lds_u16(queue + 2 * (head & kQMask)); // a graph always has a source
-            const uint2 v       = lds_v2(rec + 8 * node);
-            *sorted_out++       = static_cast<IdT>(node);
-            g.pos[node]         = static_cast<IdT>(head);
-            const uint32_t oc   = (v.y >> 16) & 0xffu;
+            const uint32_t oc = (v >> 24) & 3u;
             if (oc > 0)
-                POA_KAHN_VISIT(v.x & 0xffffu)
+                POA_KAHN_VISIT(v & 0xfffu)
             if (oc > 1)
-                POA_KAHN_VISIT(v.x >> 16)
+                POA_KAHN_VISIT((v >> 12) & 0xfffu)
             if (oc > 2)
             {
-                POA_KAHN_VISIT(v.y & 0xffffu)
-                for (uint32_t e = 3; e < oc; e++)
-                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, e)))
+                const uint32_t s = lds_u16(side + 2u * node);
+                POA_KAHN_VISIT(s & 0xfffu)
+                uint32_t more = s >> 12;
+                if (more == 15u)
+                    more = static_cast<uint32_t>(g.out_cnt[node]) - 3u;
+                for (uint32_t e = 0; e < more; e++)
+                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(3u + e))))
             }
             head++;
             if (head == pushed)
                 break;
-            if (pushed - head > kKahnQueueEntries) // the ring was overrun: give up, the caller sorts again
+            if (last_at == head)
             {
-                ok = 0;
-                break;
+                node = last_node;
+                v    = last_rec;
+            }
+            else
+            {
+                node = lds_u16(queue + 2u * head);
+                v    = lds_u32(rec + 4u * node);
             }
         }
 #undef POA_KAHN_VISIT
     }
-    ok = __shfl_sync(kFull, ok, 0);
     __syncwarp();
-    return ok != 0;
+    for (int32_t k = lane; k < node_count; k += 32)
+    {
+        const uint32_t n = lds_u16(queue + 2u * k);
+        g.sorted[k]      = static_cast<IdT>(n);
+        g.pos[n]         = static_cast<IdT>(k);
+    }
+    __syncwarp();
+    return true;
 }
 
 // SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.
