@@ -629,7 +629,9 @@ bool B200Batch::launch_split(KernelParams& P)
     // tile and the read (the topological sort and the consensus reuse that scratch)
     const int32_t L          = std::max(batch_size_.max_sequence_size, 1);
     const int32_t fill_smem  = (fill2_smem_bytes(L) + 255) & ~255;
-    const int32_t graph_smem = (kTileBytes + ((L + 15) & ~15) + 255) & ~255;
+    // graph launches: the traceback tile + the rows it records; the topological sort (8 bytes per node) and the
+    // consensus reuse the scratch
+    const int32_t graph_smem = std::max((trace2_smem_bytes(L) + 255) & ~255, 9 * 1024);
     const int32_t graph_smem_large = std::max(graph_smem, kSmemPerWarp);
     if (4 * std::max(fill_smem, graph_smem_large) > kPhaseSmemLimit)
         return false;

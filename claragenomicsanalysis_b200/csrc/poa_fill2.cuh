@@ -13,6 +13,9 @@
 //   * the substitution profile comes from shared memory: one int8 row per distinct base of the read (at most four,
 //     else the exact path takes the read), holding match - gap / mismatch - gap per read position; a lane fetches its
 //     eight values with two 4-byte loads and widens them with four sign-replicating byte permutes.
+//   * a row's descriptor is one 16-byte record {predecessor rows 0..3, profile offset, in-degree, flags, band start,
+//     spill slot} built by a warp-parallel pre-pass; the row loop gets it with one broadcast shared-memory load out of
+//     a 32-row buffer that the lanes refill together every 32 rows.
 //   * sink selection happens as the sink rows are produced.
 // Window's score area: [code rows: (M + 1) x 256 B][spill slots: 528 B each].
 #pragma once
@@ -26,6 +29,10 @@ constexpr int32_t kCodeRowBytes  = 256; // nibble codes use the first 128 B, byt
 constexpr int32_t kSpillRowBytes = 33 * 16; // lead block + 32 cell blocks
 constexpr int32_t kWidePreds     = 4;  // rows with more predecessors than this store one byte per cell
 constexpr int32_t kProfRows      = 4;  // distinct read bases the profile holds
+constexpr uint32_t kRecChain     = 1u << 24; // record.z: predecessor 0 is the previous row and the band did not move
+constexpr uint32_t kRecSink      = 1u << 25; //           the row's node has no out-edge
+constexpr uint32_t kRecSpill     = 1u << 26; //           a later row reads this row from beyond the ring
+constexpr int32_t kDescBufBytes  = 32 * 16;  // descriptor records of 32 rows
 constexpr int32_t kMoveDiag      = 0;
 constexpr int32_t kMoveVert      = 1;
 constexpr int32_t kMoveHoriz     = 2;  // bit 1 set (3 also means horizontal)
@@ -34,15 +41,27 @@ __host__ __device__ inline int32_t fill2_profile_stride(int32_t read_len)
 {
     return (read_len + kFastBand + 8 + 15) & ~15;
 }
-// Shared memory the fill needs for a read of this length: the ring plus the profile.
+// Shared memory the fill needs for a read of this length: the ring, the descriptor buffer and the profile.
 __host__ __device__ inline int32_t fill2_smem_bytes(int32_t read_len)
 {
-    return kRingBytes + kProfRows * fill2_profile_stride(read_len);
+    return kRingBytes + kDescBufBytes + kProfRows * fill2_profile_stride(read_len);
 }
 
 __device__ __forceinline__ uint32_t vminu2_1(uint32_t x) // per half: 0 if zero, else 1
 {
     return __vminu2(x, 0x00010001u);
+}
+
+// Row of predecessor p of row `row` from its record; slots beyond the fourth are looked up in the graph.
+template <typename IdT>
+__device__ __forceinline__ int32_t record_pred_row(const Graph<IdT>& g, uint32_t x, uint32_t y, int32_t row, int32_t p)
+{
+    if (p < 4)
+    {
+        const uint32_t w = (p < 2) ? x : y;
+        return static_cast<int32_t>((p & 1) ? (w >> 16) : (w & 0xffffu));
+    }
+    return g.pos[g.in_edge(g.sorted[row - 1], p)] + 1;
 }
 
 // Returns 0 and the row the traceback starts from in start_row, or kFastNotTaken (nothing the caller needs was
@@ -55,33 +74,34 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
     const int32_t pd_x = mismatch - gap; // bases differ
-    if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128)
+    const int32_t pstride = fill2_profile_stride(read_len);
+    if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > 65535)
         return kFastNotTaken;
     const int64_t code_bytes  = static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
     const int32_t spill_slots = static_cast<int32_t>(min(static_cast<long long>(65535),
                                                          static_cast<long long>((area_bytes - code_bytes) / kSpillRowBytes)));
     if (spill_slots < 2)
         return kFastNotTaken;
-    uint8_t* codes      = area;
-    uint32_t* spill     = reinterpret_cast<uint32_t*>(area + code_bytes);
-    uint16_t* slot_of   = g.kahn;  // spill slot per row (scratch of the topological sort, idle during the fill)
-    uint8_t* far_mark   = g.marks; // per row: a later row reads it from beyond the ring
+    uint8_t* codes    = area;
+    uint32_t* spill   = reinterpret_cast<uint32_t*>(area + code_bytes);
+    uint4* records    = reinterpret_cast<uint4*>(g.rowinfo);
+    uint8_t* far_mark = g.marks; // per row: a later row reads it from beyond the ring
 
-    const uint32_t ring    = smem;
-    const uint32_t prof    = ring + kRingBytes;
-    const int32_t pstride  = fill2_profile_stride(read_len);
-    const unsigned lt      = (1u << lane) - 1u;
-    const uint32_t NEG2    = pack2(kNegT, kNegT);
-    const uint4 NEG4       = make_uint4(NEG2, NEG2, NEG2, NEG2);
+    const uint32_t ring = smem;
+    const uint32_t dbuf = ring + kRingBytes;
+    const uint32_t prof = dbuf + kDescBufBytes;
+    const unsigned lt   = (1u << lane) - 1u;
+    const uint32_t NEG2 = pack2(kNegT, kNegT);
+    const uint4 NEG4    = make_uint4(NEG2, NEG2, NEG2, NEG2);
 
     // ---- the read's alphabet (at most kProfRows distinct bytes) and the profile ------------------------------------
     uint32_t alpha = 0; // byte a = base of profile row a
     int32_t nalpha = 0;
     for (int32_t k0 = 0; k0 < read_len; k0 += 32)
     {
-        const int32_t k   = k0 + lane;
-        const bool have   = k < read_len;
-        const uint32_t b  = have ? read[k] : 0u;
+        const int32_t k  = k0 + lane;
+        const bool have  = k < read_len;
+        const uint32_t b = have ? read[k] : 0u;
         for (;;)
         {
             const uint32_t valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
@@ -96,37 +116,32 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             nalpha++;
         }
     }
+    const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
+    // rows beyond the alphabet hold "mismatch" everywhere: the first of them serves graph bases the read does not have
+    for (int32_t k = lane; k < pstride; k += 32)
     {
-        const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
-        for (int32_t k = lane; k < pstride; k += 32)
-        {
-            const uint32_t b  = (k < read_len) ? read[k] : 0u;
-            const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
+        const uint32_t b  = (k < read_len) ? read[k] : 0u;
+        const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
 #pragma unroll
-            for (int a = 0; a < kProfRows; a++)
-                sts_u8(prof + static_cast<uint32_t>(a * pstride + k), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
-        }
+        for (int a = 0; a < kProfRows; a++)
+            sts_u8(prof + static_cast<uint32_t>(a * pstride + k), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
     }
 
-    RowDesc desc;
-    desc.d0 = g.rowinfo;
-    desc.d1 = desc.d0 + (g.M + 40);
-    desc.d2 = desc.d1 + (g.M + 40);
     const int32_t max_column = read_len + 1;
     const float gradient     = band_gradient(read_len, node_count);
 
-    // ---- pre-pass: descriptors, far marks, spill slots -----------------------------------------------------------------
+    // ---- pre-pass: records, far marks, spill slots ---------------------------------------------------------------------
     for (int32_t r = lane; r <= node_count; r += 32)
         far_mark[r] = 0;
     __syncwarp();
+    bool foreign = false; // a graph base the read does not have, and no spare profile row for it
     {
-        const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
-        constexpr int32_t kPre     = 4;
+        constexpr int32_t kPre = 4;
         for (int32_t rb = 1; rb <= node_count; rb += 32 * kPre)
         {
             int32_t node[kPre];
-            uint32_t pc[kPre], word[kPre];
-            int32_t pe[kPre][5];
+            uint32_t pc[kPre], zw[kPre];
+            int32_t pe[kPre][4];
 #pragma unroll
             for (int u = 0; u < kPre; u++)
             {
@@ -139,31 +154,40 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 pc[u]               = g.in_cnt[node[u]];
                 const uint32_t base = g.nodes[node[u]];
                 const uint32_t eq   = __vcmpeq4(alpha, base * 0x01010101u) & alpha_valid;
-                const uint32_t a    = eq ? static_cast<uint32_t>((__ffs(static_cast<int32_t>(eq)) - 1) >> 3) : 4u;
-                word[u]             = a | ((g.out_cnt[node[u]] == 0) ? (1u << 14) : 0u);
+                uint32_t a          = eq ? static_cast<uint32_t>((__ffs(static_cast<int32_t>(eq)) - 1) >> 3)
+                                         : static_cast<uint32_t>(nalpha);
+                if (a >= static_cast<uint32_t>(kProfRows))
+                {
+                    foreign = true;
+                    a       = 0;
+                }
+                zw[u] = a * static_cast<uint32_t>(pstride) + (pc[u] << 16) | ((g.out_cnt[node[u]] == 0) ? kRecSink : 0u);
 #pragma unroll
-                for (int k = 0; k < 5; k++)
+                for (int k = 0; k < 4; k++)
                     pe[u][k] = g.in_edge(node[u], k); // slots beyond the in-degree: stale but readable
             }
 #pragma unroll
             for (int u = 0; u < kPre; u++)
             {
-                uint32_t pr[5];
+                uint32_t pr[4];
 #pragma unroll
-                for (int k = 0; k < 5; k++)
+                for (int k = 0; k < 4; k++)
                     pr[k] = (static_cast<uint32_t>(k) < pc[u]) ? static_cast<uint32_t>(g.pos[pe[u][k]] + 1) : 0u;
                 const int32_t r = rb + lane + 32 * u;
                 if (r <= node_count)
                 {
-                    desc.d0[r] = word[u] | (pc[u] << 8) | (pr[0] << 16);
-                    desc.d1[r] = pr[1] | (pr[2] << 16);
-                    desc.d2[r] = pr[3] | (pr[4] << 16);
+                    const int32_t bs  = band_start(r, gradient, kFastBand, max_column);
+                    const int32_t bsp = band_start(r - 1, gradient, kFastBand, max_column);
+                    uint32_t z        = zw[u] + static_cast<uint32_t>(bs);
+                    if (r > 1 && static_cast<int32_t>(pr[0]) == r - 1 && bs == bsp)
+                        z |= kRecChain;
+                    records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs));
                     // predecessors the ring (rows r - 8 .. r - 1) will no longer hold; row 0 is always in slot 0
 #pragma unroll
-                    for (int k = 0; k < 5; k++)
+                    for (int k = 0; k < 4; k++)
                         if (static_cast<uint32_t>(k) < pc[u] && static_cast<int32_t>(pr[k]) < r - kRingRows && pr[k] != 0u)
                             far_mark[pr[k]] = 1;
-                    for (uint32_t k = 5; k < pc[u]; k++)
+                    for (uint32_t k = 4; k < pc[u]; k++)
                     {
                         const int32_t p = g.pos[g.in_edge(node[u], static_cast<int32_t>(k))] + 1;
                         if (p < r - kRingRows)
@@ -173,7 +197,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             }
         }
     }
-    __syncwarp();
+    if (__any_sync(kFull, foreign))
+        return kFastNotTaken;
     {
         int32_t used = 1; // slot 0: row 0
         for (int32_t r0 = 1; r0 <= node_count; r0 += 32)
@@ -183,8 +208,9 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             const unsigned mask = __ballot_sync(kFull, m);
             if (m)
             {
-                slot_of[r] = static_cast<uint16_t>(used + __popc(mask & lt));
-                desc.d0[r] |= 1u << 15;
+                const uint32_t slot = static_cast<uint32_t>(used + __popc(mask & lt));
+                records[r].z |= kRecSpill;
+                records[r].w |= slot << 16;
             }
             used += __popc(mask);
         }
@@ -209,63 +235,38 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     __syncwarp();
 
     const uint32_t gapv   = pack2(gap, gap);
-    const uint32_t pdx2   = pack2(pd_x, pd_x);
     const uint32_t prof_l = prof + 8u * static_cast<uint32_t>(lane);
+    const uint32_t ring_l = ring + 16u + 16u * static_cast<uint32_t>(lane); // this lane's cell block in ring row 0
     uint8_t* code_lane4   = codes + 4 * lane; // nibble rows: one word per lane
     uint8_t* code_lane8   = codes + 8 * lane; // byte rows: two words per lane
 
-    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last, its band start and left boundary
-    int32_t prev_bs     = -1;
+    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last and its left boundary
     int32_t prev_left_t = 0;
     const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
     int32_t best = best_floor, best_row = 0;
     bool unranked = false;
 
-    // Descriptors travel in registers: chunk c* holds rows r0 .. r0 + 31 (one row per lane), chunk n* the next 32
-    // rows, loaded a chunk ahead; band starts likewise.  The row loop receives its descriptor by shuffle, issued one
-    // iteration early.
-    uint32_t c0 = 0, c1 = 0, c2 = 0, cs = 0, n0, n1, n2, ns;
-    int32_t cbs = 0, nbs;
-    {
-        const int32_t rr = min(1 + lane, node_count);
-        n0  = desc.d0[rr];
-        n1  = desc.d1[rr];
-        n2  = desc.d2[rr];
-        ns  = slot_of[rr]; // meaningful for rows marked for spilling only
-        nbs = band_start(rr, gradient, kFastBand, max_column);
-    }
-    uint32_t meta_next = __shfl_sync(kFull, n0, 0);
-    int32_t bs_next    = __shfl_sync(kFull, nbs, 0);
+    // records of the next 32 rows, one per lane, loaded a chunk ahead
+    uint4 nrec = records[min(1 + lane, node_count)];
 
     for (int32_t r = 1; r <= node_count; r++)
     {
         const int32_t k = (r - 1) & 31;
-        if (k == 0) // next chunk becomes current, fetch the one after
+        if (k == 0) // the lanes hand over the records of rows r .. r + 31 and fetch the next 32
         {
-            c0  = n0;
-            c1  = n1;
-            c2  = n2;
-            cs  = ns;
-            cbs = nbs;
-            const int32_t rr = min(r + 32 + lane, node_count);
-            n0  = desc.d0[rr];
-            n1  = desc.d1[rr];
-            n2  = desc.d2[rr];
-            ns  = slot_of[rr];
-            nbs = band_start(rr, gradient, kFastBand, max_column);
+            sts_v4(dbuf + 16u * static_cast<uint32_t>(lane), nrec);
+            __syncwarp();
+            nrec = records[min(r + 32 + lane, node_count)];
         }
-        const uint32_t meta   = meta_next;
-        const int32_t bs      = bs_next;
-        const int32_t pc      = (meta >> 8) & 0x3f;
-        const uint32_t pa     = meta & 0xff;              // profile row of the node's base; 4: not in the read
-        const int32_t ring_lo = max(r - kRingRows, 1);    // oldest row the ring still holds (never row 0)
+        const uint4 rec  = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
+        const int32_t bs = static_cast<int32_t>(rec.w & 0xffffu);
+        const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
 
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
-        uint32_t Q0 = pdx2, Q1 = pdx2, Q2 = pdx2, Q3 = pdx2;
-        if (pa < static_cast<uint32_t>(kProfRows))
+        uint32_t Q0, Q1, Q2, Q3;
         {
-            const uint32_t at = prof_l + pa * static_cast<uint32_t>(pstride) + static_cast<uint32_t>(bs);
-            const uint32_t lo = lds_u32(at); // bs is a multiple of 4: 4-byte aligned, not always 8
+            const uint32_t at = prof_l + (rec.z & 0xffffu); // profile row + band start: 4-byte aligned, not always 8
+            const uint32_t lo = lds_u32(at);
             const uint32_t hi = lds_u32(at + 4);
             Q0                = prmt(lo, hi, 0xC480u);
             Q1                = prmt(lo, hi, 0xD591u);
@@ -273,30 +274,14 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             Q3                = prmt(lo, hi, 0xF7B3u);
         }
 
-        int32_t min_d     = 1 << 20;   // smallest band shift over the predecessors
+        int32_t min_d     = 0;         // smallest band shift over the predecessors
         int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
 
-        // One predecessor row: its cells under this lane's cells (V_i) and the corner (D0 = (corner, V3.lo)); the
-        // diagonal operands are D_i = V_{i-1}.  All branches are warp-uniform (band shifts and row numbers are).
-        auto load_pred = [&](int32_t prow, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) {
+        // One predecessor row from the ring or from its spilled copy: its cells under this lane's cells (V_i) and the
+        // corner (D0 = (corner, V3.lo)); the diagonal operands are D_i = V_{i-1}.  All branches are warp-uniform.
+        auto load_pred = [&](int32_t prow, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) -> int32_t {
             int32_t d;
-            if (prow == r - 1 && bs == prev_bs)
-            {
-                // the row just written, same band start: its cells are still in this lane's registers; the corner is
-                // the last cell of the lane to the left (lane 0: that row's left boundary)
-                POA_COUNT("fill2.pred_registers");
-                d  = 0;
-                V0 = prev_out.x;
-                V1 = prev_out.y;
-                V2 = prev_out.z;
-                V3 = prev_out.w;
-                uint32_t X = __shfl_up_sync(kFull, prev_out.w, 1);
-                if (lane == 0)
-                    X = static_cast<uint32_t>(prev_left_t) << 16;
-                D0        = __byte_perm(X, V3, 0x5432);
-                left_best = max(left_best, prev_left_t);
-            }
-            else if (prow >= ring_lo) // shared-memory ring
+            if (prow >= r - kRingRows && prow > 0) // shared-memory ring: rows r - 8 .. r - 1
             {
                 POA_COUNT("fill2.pred_ring");
                 const uint32_t pa_ = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
@@ -331,13 +316,13 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             else // far predecessor: its spilled copy (through L2); pad blocks are implied
             {
                 POA_COUNT("fill2.pred_spilled");
-                const int32_t slot = (prow == 0) ? 0 : static_cast<int32_t>(slot_of[prow]);
-                const uint4* prow4 = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
-                const uint4 lead   = __ldcg(prow4);
-                d                  = bs - static_cast<int32_t>(lead.x);
-                const int32_t sl   = lane + 1 + (d >> 3);
-                const int32_t sc   = (8 * lane + d + 7) >> 3;
-                const uint32_t p33 = (prow == 0) ? pack2(0, kNegT) : NEG2; // row 0's first pad block
+                const uint32_t slot = (prow == 0) ? 0u : (records[prow].w >> 16);
+                const uint4* prow4  = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
+                const uint4 lead    = __ldcg(prow4);
+                d                   = bs - static_cast<int32_t>(lead.x);
+                const int32_t sl    = lane + 1 + (d >> 3);
+                const int32_t sc    = (8 * lane + d + 7) >> 3;
+                const uint32_t p33  = (prow == 0) ? pack2(0, kNegT) : NEG2; // row 0's first pad block
                 uint4 a = NEG4, b = NEG4;
                 uint32_t wv = NEG2;
                 if (sl <= 32)
@@ -361,21 +346,21 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 D0                  = __byte_perm(odd ? a.w : wv, V3, odd ? 0x5410u : 0x5432u);
                 left_best           = max(left_best, hi16(lead.w));
             }
-            min_d = min(min_d, d);
             if (REBASED && d != 0)
             {
                 // rebased rows: the predecessor's scores are relative to its own band start, beta * d below this
                 // row's.  Sentinel-class operands are lifted first so that the subtraction cannot wrap; real ones
                 // (>= kRealLo) are above the lift for every shift at which the bands still overlap.
-                const int32_t bd  = min(beta * d, 8000);
-                const uint32_t fl = pack2(kNegT + bd, kNegT + bd);
+                const int32_t bd   = min(beta * d, 8000);
+                const uint32_t fl  = pack2(kNegT + bd, kNegT + bd);
                 const uint32_t c2_ = pack2(-bd, -bd);
-                V0                = __vadd2(__vmaxs2(V0, fl), c2_);
-                V1                = __vadd2(__vmaxs2(V1, fl), c2_);
-                V2                = __vadd2(__vmaxs2(V2, fl), c2_);
-                V3                = __vadd2(__vmaxs2(V3, fl), c2_);
-                D0                = __vadd2(__vmaxs2(D0, fl), c2_);
+                V0                 = __vadd2(__vmaxs2(V0, fl), c2_);
+                V1                 = __vadd2(__vmaxs2(V1, fl), c2_);
+                V2                 = __vadd2(__vmaxs2(V2, fl), c2_);
+                V3                 = __vadd2(__vmaxs2(V3, fl), c2_);
+                D0                 = __vadd2(__vmaxs2(D0, fl), c2_);
             }
+            return d;
         };
 
         // S_i: best diagonal / vertical candidate per cell; K_i: its move code (kind | predecessor slot << 2) under the
@@ -383,12 +368,24 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         uint32_t S0, S1, S2, S3, K0, K1, K2, K3;
         {
             uint32_t V0, V1, V2, V3, D0;
-            load_pred(static_cast<int32_t>(meta >> 16), V0, V1, V2, V3, D0); // predecessor 0 (row 0 for a source node)
+            if (rec.z & kRecChain)
             {
-                // descriptor of the next row, needed first thing next iteration
-                const int32_t kn = r & 31;
-                meta_next        = __shfl_sync(kFull, kn ? c0 : n0, kn);
-                bs_next          = __shfl_sync(kFull, kn ? cbs : nbs, kn);
+                // the row just written, same band start: its cells are still in this lane's registers; the corner is
+                // the last cell of the lane to the left (lane 0: that row's left boundary)
+                POA_COUNT("fill2.pred_registers");
+                V0 = prev_out.x;
+                V1 = prev_out.y;
+                V2 = prev_out.z;
+                V3 = prev_out.w;
+                uint32_t X = __shfl_up_sync(kFull, prev_out.w, 1);
+                if (lane == 0)
+                    X = static_cast<uint32_t>(prev_left_t) << 16;
+                D0        = __byte_perm(X, V3, 0x5432);
+                left_best = prev_left_t;
+            }
+            else
+            {
+                min_d = load_pred(static_cast<int32_t>(rec.x & 0xffffu), V0, V1, V2, V3, D0); // row 0 for a source node
             }
             const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
             const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
@@ -412,18 +409,37 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 uint32_t bD0 = dq0, bD1 = dq1, bD2 = dq2, bD3 = dq3;
                 uint32_t bV0 = __viaddmax_s16x2(V0, gapv, NEG2), bV1 = __viaddmax_s16x2(V1, gapv, NEG2),
                          bV2 = __viaddmax_s16x2(V2, gapv, NEG2), bV3 = __viaddmax_s16x2(V3, gapv, NEG2);
-                uint32_t iD0 = 0, iD1 = 0, iD2 = 0, iD3 = 0, iV0 = 0, iV1 = 0, iV2 = 0, iV3 = 0;
-                const uint32_t p12 = __shfl_sync(kFull, c1, k);
-                const uint32_t p34 = (pc > 3) ? __shfl_sync(kFull, c2, k) : 0u;
-                for (int32_t p = 1; p < pc; p++)
+                uint32_t iD0, iD1, iD2, iD3, iV0, iV1, iV2, iV3;
                 {
-                    load_pred(pred_row<IdT>(g, meta, p12, p34, r, p), V0, V1, V2, V3, D0);
-                    const uint32_t pp = pack2(p, p);
+                    // predecessor 1: the slot index is just "strictly better than predecessor 0"
+                    const int32_t d = load_pred(static_cast<int32_t>(rec.x >> 16), V0, V1, V2, V3, D0);
+                    min_d           = min(min_d, d);
+                    auto second = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
+                        const uint32_t nb = __vmaxs2(bestv, cand);
+                        idx               = vminu2_1(nb ^ bestv);
+                        bestv             = nb;
+                    };
+                    second(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
+                    second(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));
+                    second(bD2, iD2, __viaddmax_s16x2(V1, Q2, NEG2));
+                    second(bD3, iD3, __viaddmax_s16x2(V2, Q3, NEG2));
+                    second(bV0, iV0, __viaddmax_s16x2(V0, gapv, NEG2));
+                    second(bV1, iV1, __viaddmax_s16x2(V1, gapv, NEG2));
+                    second(bV2, iV2, __viaddmax_s16x2(V2, gapv, NEG2));
+                    second(bV3, iV3, __viaddmax_s16x2(V3, gapv, NEG2));
+                }
+                for (int32_t p = 2; p < pc; p++)
+                {
+                    const int32_t d = load_pred(record_pred_row<IdT>(g, rec.x, rec.y, r, p), V0, V1, V2, V3, D0);
+                    min_d           = min(min_d, d);
+                    const uint32_t plo = static_cast<uint32_t>(p), phi = static_cast<uint32_t>(p) << 16;
                     auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
-                        const uint32_t nb  = __vmaxs2(bestv, cand);
-                        const uint32_t chg = vminu2_1(nb ^ bestv) * 0xffffu; // 0xffff where cand is strictly better
-                        idx                = (idx & ~chg) | (pp & chg);
-                        bestv              = nb;
+                        bool keep_hi, keep_lo; // the best so far is at least as good: it stays (first slot wins ties)
+                        bestv = __vibmax_s16x2(bestv, cand, &keep_hi, &keep_lo);
+                        if (!keep_lo)
+                            idx = (idx & 0xffff0000u) | plo;
+                        if (!keep_hi)
+                            idx = (idx & 0x0000ffffu) | phi;
                     };
                     better(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
                     better(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));
@@ -436,7 +452,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 }
                 auto join = [&](uint32_t& S, uint32_t& K, uint32_t bD, uint32_t iD, uint32_t bV, uint32_t iV) {
                     S                   = __vmaxs2(bD, bV);
-                    const uint32_t vert = vminu2_1(S ^ bD);     // 1 where no diagonal candidate reaches S
+                    const uint32_t vert = vminu2_1(S ^ bD); // 1 where no diagonal candidate reaches S
                     const uint32_t vm   = vert * 0xffffu;
                     K                   = vert + 4u * ((iD & ~vm) | (iV & vm));
                 };
@@ -451,9 +467,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             return kFastNotTaken;
 
         // left boundary of this row in the tilted domain (a source node's predecessor is row 0, whose boundary is 0)
-        int32_t left_t = kNegT;
-        if (bs == 0)
-            left_t = static_cast<int16_t>(left_best + gap);
+        const int32_t left_t = (bs == 0) ? static_cast<int32_t>(static_cast<int16_t>(left_best + gap)) : kNegT;
 
         // horizontal pass = prefix maximum, both halves at once
         const uint32_t P1 = __vmaxs2(S1, S0);
@@ -505,8 +519,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         K1 += 2u * vminu2_1(out.y ^ S1);
         K2 += 2u * vminu2_1(out.z ^ S2);
         K3 += 2u * vminu2_1(out.w ^ S3);
-        const int64_t code_row = static_cast<int64_t>(r) * kCodeRowBytes;
         POA_COUNT(pc <= 1 ? "fill2.rows_1pred" : pc <= kWidePreds ? "fill2.rows_2to4pred" : "fill2.rows_wide");
+        const int64_t code_row = static_cast<int64_t>(r) * kCodeRowBytes;
         if (pc <= kWidePreds)
         {
             // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
@@ -521,54 +535,55 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                    make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
         }
 
-        const uint32_t rrow = ring + static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
-        sts_v4(rrow + 16u + 16u * lane, out);
+        const uint32_t rrow = static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
+        sts_v4(ring_l + rrow, out);
         const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, static_cast<uint32_t>(left_t) << 16);
         if (lane == 0)
-            sts_v4(rrow, lead);
-        if (meta & (1u << 15)) // a later row reads this one from beyond the ring
+            sts_v4(ring + rrow, lead);
+        if (rec.z & (kRecSpill | kRecSink))
         {
-            POA_COUNT("fill2.rows_spilled");
-            const uint32_t my_slot = __shfl_sync(kFull, cs, k);
-            uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(my_slot) * (kSpillRowBytes / 4));
-            __stcg(dst + 1 + lane, out);
-            if (lane == 0)
-                __stcg(dst, lead);
-        }
-        if (meta & (1u << 14))
-        {
-            // sink row: its score at column read_len (all candidates share the column, so tilted scores compare like
-            // the scores themselves); first strict maximum in row order (cudapoa_nw_banded.cuh:372-383)
-            const int32_t c = read_len - bs - 1; // 0-based cell of the band
-            int32_t t       = kNegT;
-            if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && read_len != 0)
+            if (rec.z & kRecSpill) // a later row reads this one from beyond the ring
             {
-                const int32_t q  = c & 3;
-                const uint32_t w = (q == 0) ? out.x : (q == 1) ? out.y : (q == 2) ? out.z : out.w;
-                const int32_t v  = (c & 4) ? hi16(w) : lo16(w);
-                t                = __shfl_sync(kFull, v, c >> 3);
+                POA_COUNT("fill2.rows_spilled");
+                uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(rec.w >> 16) * (kSpillRowBytes / 4));
+                __stcg(dst + 1 + lane, out);
+                if (lane == 0)
+                    __stcg(dst, lead);
             }
-            else if (read_len == 0 || c == -1)
+            if (rec.z & kRecSink)
             {
-                t = static_cast<int16_t>(left_t);
-            }
-            if (t <= kNegThreshold)
-                t = kNegT;
-            int32_t s = t;
-            if (REBASED)
-            {
-                s = (t == kNegT) ? kNegAbs : t + beta * bs;
-                unranked |= (t == kNegT);
-            }
-            if (s > best)
-            {
-                best     = s;
-                best_row = r;
+                // sink row: its score at column read_len (all candidates share the column, so tilted scores compare
+                // like the scores themselves); first strict maximum in row order (cudapoa_nw_banded.cuh:372-383)
+                const int32_t c = read_len - bs - 1; // 0-based cell of the band
+                int32_t t       = kNegT;
+                if (static_cast<uint32_t>(c) < static_cast<uint32_t>(kFastBand) && read_len != 0)
+                {
+                    const int32_t q  = c & 3;
+                    const uint32_t w = (q == 0) ? out.x : (q == 1) ? out.y : (q == 2) ? out.z : out.w;
+                    const int32_t v  = (c & 4) ? hi16(w) : lo16(w);
+                    t                = __shfl_sync(kFull, v, c >> 3);
+                }
+                else if (read_len == 0 || c == -1)
+                {
+                    t = static_cast<int16_t>(left_t);
+                }
+                if (t <= kNegThreshold)
+                    t = kNegT;
+                int32_t s = t;
+                if (REBASED)
+                {
+                    s = (t == kNegT) ? kNegAbs : t + beta * bs;
+                    unranked |= (t == kNegT);
+                }
+                if (s > best)
+                {
+                    best     = s;
+                    best_row = r;
+                }
             }
         }
         prev_out    = out;
-        prev_bs     = bs;
-        prev_left_t = static_cast<int16_t>(left_t);
+        prev_left_t = left_t;
         __syncwarp();
     }
 

@@ -41,7 +41,8 @@ struct ArenaLayout
     int64_t in_w;                                // uint16[50][M]
     int64_t aln_node;                            // IdT[max_seq + 32]  the alignment: node per read position
     int64_t row_bs;                              // int32[M + 1]   band start per score row
-    int64_t rowinfo;                             // uint32[3][M + 40] per-row descriptors of the fast fill
+    int64_t rowinfo;                             // uint4[M + 40] per-row records of the packed fill (poa_fill2.cuh);
+                                                 // the first formulation reads it as uint32[3][M + 40]
     int64_t cscore;                              // int32[M]       consensus scores / racon marks scratch
     int64_t cpred;                               // IdT[M]         consensus predecessors / racon stack
     int64_t marks, check;                        // uint8[M]
@@ -149,7 +150,7 @@ inline ArenaLayout make_arena_layout(int32_t M, int32_t aln_cap, int32_t max_rea
     L.in_w          = take(2 * m * kMaxNodeEdges);
     L.aln_node      = take(static_cast<int64_t>(id_bytes) * (max_seq + 32));
     L.row_bs        = take(4 * (m + 1));
-    L.rowinfo       = take(12 * (m + 40));
+    L.rowinfo       = take(16 * (m + 40));
     L.cscore        = take(4 * m);
     L.cpred         = take(id_bytes * (m + 8));
     L.marks         = take(m);

@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
             {
                 const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
                                                                        static_cast<int64_t>(w) * P.banded_score_stride);
-                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, st.start_row, lane);
+                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, P.smem_per_warp, st.start_row, lane);
             }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {

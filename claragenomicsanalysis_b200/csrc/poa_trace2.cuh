@@ -4,7 +4,7 @@
 // decided, per cell, which move that derivation takes (kind + predecessor slot), so a step of the walk is: load the
 // cell's code, load the row's descriptor, move.  Lane 0 walks; the warp stages the codes of 64 rows x 64 columns around
 // the walk into shared memory (2 KB, column-aligned so that a cell's nibble is addressed by (row, column) alone) with
-// the rows' descriptors (predecessor rows).  Rows with more than kWidePreds predecessors keep a byte per cell in global
+// the rows' records (predecessor rows, in-degree, band start).  Rows with more than kWidePreds predecessors keep a byte per cell in global
 // memory and are read from there.
 //
 // Output as fast_traceback_impl's: g.aln_node[k] = node paired with read position k, or -1 for an inserted base.
@@ -19,22 +19,33 @@ constexpr int32_t kT2Rows      = 64;
 constexpr int32_t kT2Cols      = 64;                     // columns per tile, a multiple of 8
 constexpr int32_t kT2RowBytes  = kT2Cols / 2;            // nibbles
 constexpr int32_t kT2TileBytes = kT2Rows * kT2RowBytes;  // 2 KB
-constexpr int32_t kT2Bytes     = kT2TileBytes + kT2Rows * 8; // + descriptors (d0, d1) per row
+constexpr int32_t kT2Bytes     = kT2TileBytes + kT2Rows * 16; // + the rows' records
+
+// Shared memory the traceback wants: the tile, and -- when it fits -- 2 bytes per read position for the rows the walk
+// records (the serial lane then never stores to global memory).
+__host__ __device__ inline int32_t trace2_smem_bytes(int32_t read_len)
+{
+    return kT2Bytes + ((2 * read_len + 15) & ~15);
+}
 
 // Returns the alignment length (> 0), or -1 if a code is not a move (cannot happen for codes the fill wrote; kept as the
-// reference's loop-count guard).  All 32 lanes.
+// reference's loop-count guard).  All 32 lanes.  `smem_bytes` of scratch at `tile`.
 template <typename IdT>
 __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t read_len, const uint8_t* area,
-                               uint32_t tile, int32_t start_row, int32_t lane)
+                               uint32_t tile, int32_t smem_bytes, int32_t start_row, int32_t lane)
 {
     const uint8_t* codes = area;
-    RowDesc desc;
-    desc.d0 = g.rowinfo;
-    desc.d1 = desc.d0 + (g.M + 40);
-    desc.d2 = desc.d1 + (g.M + 40);
-    const int32_t max_column = read_len + 1;
-    const float gradient     = band_gradient(read_len, node_count);
+    const uint4* records = reinterpret_cast<const uint4*>(g.rowinfo);
     const uint32_t tile_desc = tile + kT2TileBytes;
+    const uint32_t rows_s    = tile + kT2Bytes;                        // u16[read_len]: row paired with each base
+    const bool in_smem       = smem_bytes >= trace2_smem_bytes(read_len);
+    // record(k, row): read position k pairs with `row` (0: inserted base)
+    auto record = [&](int32_t k, int32_t row) {
+        if (in_smem)
+            sts_u16(rows_s + 2u * static_cast<uint32_t>(k), static_cast<uint32_t>(row));
+        else
+            g.aln_node[k] = static_cast<IdT>(row);
+    };
 
     int32_t i = start_row, j = read_len;
     int32_t steps = 0;
@@ -52,12 +63,12 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
             const int32_t tr = lane + 32 * u;
             const int32_t r  = tile_r0 + tr;
             uint32_t w[kT2Cols / 8 + 1];
-            uint2 dsc = make_uint2(0u, 0u);
+            uint4 dsc = make_uint4(0u, 0u, 0u, 0u);
             int32_t c0 = 0;
             if (r >= 1)
             {
-                dsc              = make_uint2(desc.d0[r], desc.d1[r]);
-                const int32_t b  = band_start(r, gradient, kFastBand, max_column);
+                dsc              = records[r];
+                const int32_t b  = static_cast<int32_t>(dsc.w & 0xffffu);
                 c0               = tile_c0 - b - 1;       // band cell under the tile's first column, a multiple of 4
                 const int32_t w0 = c0 >> 3;               // first word of the row the tile needs (floor division)
                 const uint32_t* row = reinterpret_cast<const uint32_t*>(codes + static_cast<int64_t>(r) * kCodeRowBytes);
@@ -81,52 +92,52 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
                                   __byte_perm(w[3], w[4], sel)));
             sts_v4(at + 16u, make_uint4(__byte_perm(w[4], w[5], sel), __byte_perm(w[5], w[6], sel),
                                         __byte_perm(w[6], w[7], sel), __byte_perm(w[7], w[8], sel)));
-            sts_v2(tile_desc + 8u * static_cast<uint32_t>(tr), dsc);
+            sts_v4(tile_desc + 16u * static_cast<uint32_t>(tr), dsc);
         }
         __syncwarp();
         if (lane == 0)
         {
             const int32_t row_floor = max(tile_r0, 1);
+            // shared addresses of record(row) and code word(row, column) as base + 16 * row / base + 32 * row + ..
+            // (32-bit arithmetic; it may wrap)
+            const uint32_t desc_base = tile_desc - 16u * static_cast<uint32_t>(tile_r0);
+            const uint32_t code_base = tile - static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(tile_r0);
             while (i >= row_floor && j >= tile_c0 && j > 0)
             {
-                const int32_t tr    = i - tile_r0;
-                const uint2 dd      = lds_v2(tile_desc + 8u * static_cast<uint32_t>(tr));
-                const uint32_t meta = dd.x;
-                const int32_t pc    = (meta >> 8) & 0x3f;
-                uint32_t code;
-                if (pc <= kWidePreds)
-                {
-                    const int32_t x  = j - tile_c0; // 0 .. 63
-                    const uint32_t w = lds_u32(tile + static_cast<uint32_t>(tr * kT2RowBytes + ((x >> 3) << 2)));
-                    code             = (w >> ((x & 7) * 4)) & 0xfu;
-                }
-                else
+                // descriptor and code word are fetched together: one shared-memory latency per step
+                const int32_t x     = j - tile_c0; // 0 .. 63
+                const uint4 dd      = lds_v4(desc_base + 16u * static_cast<uint32_t>(i));
+                const uint32_t cw   = lds_u32(code_base + static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(i) +
+                                            static_cast<uint32_t>((x >> 3) << 2));
+                const int32_t pc    = static_cast<int32_t>((dd.z >> 16) & 0x3fu);
+                uint32_t code       = (cw >> ((x & 7) * 4)) & 0xfu;
+                if (pc > kWidePreds)
                 {
                     POA_COUNT("trace2.wide_steps");
-                    const int32_t b = band_start(i, gradient, kFastBand, max_column);
+                    const int32_t b = static_cast<int32_t>(dd.w & 0xffffu);
                     code            = __ldcg(codes + static_cast<int64_t>(i) * kCodeRowBytes + (j - b - 1));
                 }
                 steps++;
                 if (code & 2u)
                 {
-                    g.aln_node[j - 1] = static_cast<IdT>(0); // horizontal: an inserted base
+                    record(j - 1, 0); // horizontal: an inserted base
                     j--;
                     continue;
                 }
                 const int32_t p = static_cast<int32_t>(code >> 2);
-                if (p >= max(pc, 1))
+                int32_t pi      = static_cast<int32_t>(dd.x & 0xffffu);
+                if (p != 0)
                 {
-                    broken = true; // not a code the fill writes
-                    break;
+                    if (p >= pc)
+                    {
+                        broken = true; // not a code the fill writes
+                        break;
+                    }
+                    pi = record_pred_row<IdT>(g, dd.x, dd.y, i, p);
                 }
-                int32_t pi;
-                if (p == 0)
-                    pi = static_cast<int32_t>(meta >> 16);
-                else
-                    pi = pred_row<IdT>(g, meta, dd.y, (p > 2) ? desc.d2[i] : 0u, i, p);
                 if ((code & 1u) == 0u)
                 {
-                    g.aln_node[j - 1] = static_cast<IdT>(i); // diagonal: the base pairs with this row's node
+                    record(j - 1, i); // diagonal: the base pairs with this row's node
                     j--;
                 }
                 i = pi;
@@ -140,13 +151,16 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
     steps = __shfl_sync(kFull, steps, 0);
     if (broken)
         return -1;
-    // the walk reached row 0 (the remaining bases are inserted before the graph's first node) or column 0
-    // g.aln_node[] holds ROW indices (0: inserted base); they become node ids here
+    // the walk reached row 0 (the remaining bases are inserted before the graph's first node) or column 0.
+    // Recorded ROW indices (0: inserted base) become node ids here.
     __syncwarp();
     for (int32_t k = lane; k < read_len; k += 32)
     {
-        const int32_t row = (k < j) ? 0 : static_cast<int32_t>(g.aln_node[k]);
-        g.aln_node[k]     = static_cast<IdT>(row > 0 ? static_cast<int32_t>(g.sorted[row - 1]) : -1);
+        int32_t row = 0;
+        if (k >= j)
+            row = in_smem ? static_cast<int32_t>(lds_u16(rows_s + 2u * static_cast<uint32_t>(k)))
+                          : static_cast<int32_t>(g.aln_node[k]);
+        g.aln_node[k] = static_cast<IdT>(row > 0 ? static_cast<int32_t>(g.sorted[row - 1]) : -1);
     }
     return max(steps + j, 1);
 }

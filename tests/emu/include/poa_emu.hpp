@@ -348,6 +348,12 @@ static inline unsigned __vminu2(unsigned a, unsigned b)
 static inline unsigned __vimax_s16x2(unsigned a, unsigned b) { return __vmaxs2(a, b); }
 static inline unsigned __vimin_s16x2(unsigned a, unsigned b) { return __vmins2(a, b); }
 static inline unsigned __vimin_u16x2(unsigned a, unsigned b) { return __vminu2(a, b); }
+static inline unsigned __vibmax_s16x2(unsigned a, unsigned b, bool* pred_hi, bool* pred_lo)
+{
+    *pred_hi = poa_emu_hi(a) >= poa_emu_hi(b);
+    *pred_lo = poa_emu_lo(a) >= poa_emu_lo(b);
+    return __vmaxs2(a, b);
+}
 static inline unsigned __vimax3_s16x2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
 static inline unsigned __viaddmax_s16x2(unsigned a, unsigned b, unsigned c)
 {
