@@ -581,6 +581,19 @@ int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fi
     });
     return rc == 0 ? n : -1;
 }
+
+int64_t cudapoa_b200_debug_read_window(cudapoa_b200_batch* batch, int32_t window, int32_t region, void* out, int64_t cap)
+{
+    int64_t n  = -1;
+    int32_t rc = guarded([&]() {
+        auto* src = dynamic_cast<poa::EngineStatsSource*>(batch->impl.get());
+        if (src == nullptr)
+            return -1;
+        n = src->debug_read_window(window, region, out, cap);
+        return 0;
+    });
+    return rc == 0 ? n : -1;
+}
 #endif
 
 } // extern "C"

@@ -182,6 +182,20 @@ public:
     int32_t relaunch_phases(double* fill_ms, double* graph_ms) override;
     double relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches) override;
     void set_overlapped(bool overlapped) override { overlapped_ = overlapped; }
+    int64_t debug_read_window(int32_t window, int32_t region, void* out, int64_t cap) override
+    {
+        scoped_device_switch dev(device_id_);
+        if (window < 0 || window >= poa_count_)
+            return -1;
+        GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
+        const int64_t score_bytes = static_cast<int64_t>(plan_.band_cells + kBandRowPad) * plan_.G * (plan_.score32 ? 4 : 2);
+        const int64_t size        = (region == 0) ? plan_.layout.stride : score_bytes;
+        const uint8_t* src        = (region == 0) ? arena_d_ + static_cast<int64_t>(window) * plan_.layout.stride
+                                                  : scores_d_ + static_cast<int64_t>(window) * score_bytes;
+        if (out != nullptr && cap > 0)
+            GW_CU_CHECK_ERR(cudaMemcpy(out, src, static_cast<size_t>(std::min(size, cap)), cudaMemcpyDeviceToHost));
+        return size;
+    }
 
 private:
     void allocate(size_t max_mem);
@@ -692,6 +706,10 @@ void B200Batch::launch()
     const char* env = std::getenv("CUDAPOA_B200_SPOA_ACCURATE");
     P.spoa_accurate = (env != nullptr && env[0] == '1') ? 1 : 0;
 #endif
+    {
+        const char* dbg = std::getenv("CUDAPOA_B200_DEBUG_FLAGS");
+        P.debug_flags   = dbg ? std::atoi(dbg) : 0;
+    }
     if (launch_split(P))
     {
         GW_CU_CHECK_ERR(cudaPeekAtLastError());

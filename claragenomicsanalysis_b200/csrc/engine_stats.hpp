@@ -32,6 +32,9 @@ public:
     // less than about two waves of windows is served faster by the single launch; overlapping batches by the
     // phase-split schedule whatever their size.
     virtual void set_overlapped(bool overlapped) = 0;
+    // Development aid: copy a window's device state to the host.  region 0 = its arena slice (graph, records, scratch),
+    // 1 = its score area (move codes, spilled rows).  Returns the region's size in bytes; copies min(size, cap).
+    virtual int64_t debug_read_window(int32_t window, int32_t region, void* out, int64_t cap) = 0;
 };
 
 } // namespace cudapoa

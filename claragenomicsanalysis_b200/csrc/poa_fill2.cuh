@@ -69,7 +69,8 @@ __device__ __forceinline__ int32_t record_pred_row(const Graph<IdT>& g, uint32_t
 template <typename IdT, bool REBASED>
 __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                               uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
-                              int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t beta_arg)
+                              int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t beta_arg,
+                              int32_t debug_flags = 0)
 {
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
@@ -258,7 +259,11 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             __syncwarp();
             nrec = records[min(r + 32 + lane, node_count)];
         }
-        const uint4 rec  = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
+        uint4 rec = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
+        if (debug_flags & 8)
+            rec = records[r];
+        if (debug_flags & 4)
+            rec.z &= ~kRecChain;
         const int32_t bs = static_cast<int32_t>(rec.w & 0xffffu);
         const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
 
@@ -432,14 +437,12 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 {
                     const int32_t d = load_pred(record_pred_row<IdT>(g, rec.x, rec.y, r, p), V0, V1, V2, V3, D0);
                     min_d           = min(min_d, d);
-                    const uint32_t plo = static_cast<uint32_t>(p), phi = static_cast<uint32_t>(p) << 16;
+                    const uint32_t pp = pack2(p, p);
                     auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
-                        bool keep_hi, keep_lo; // the best so far is at least as good: it stays (first slot wins ties)
-                        bestv = __vibmax_s16x2(bestv, cand, &keep_hi, &keep_lo);
-                        if (!keep_lo)
-                            idx = (idx & 0xffff0000u) | plo;
-                        if (!keep_hi)
-                            idx = (idx & 0x0000ffffu) | phi;
+                        const uint32_t nb  = __vmaxs2(bestv, cand);
+                        const uint32_t chg = vminu2_1(nb ^ bestv) * 0xffffu; // 0xffff where cand is strictly better
+                        idx                = (idx & ~chg) | (pp & chg);      // (first slot wins ties)
+                        bestv              = nb;
                     };
                     better(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
                     better(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));

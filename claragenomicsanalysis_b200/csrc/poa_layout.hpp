@@ -113,6 +113,7 @@ struct KernelParams
     int32_t class_cap;     // ... the smaller scratch (node_count + kClassMargin <= class_cap), 1 the others
     int32_t class_cap_final; // the same bound for a window's last read, whose launch also runs the consensus
     int32_t lean_class0;   // launch 0 is the lean instance: rebased rows and the SPOA_ACCURATE order go to launch 1
+    int32_t debug_flags;   // development switches (CUDAPOA_B200_DEBUG_FLAGS), 0 in production
 };
 
 inline int64_t align_up64(int64_t v, int64_t a)

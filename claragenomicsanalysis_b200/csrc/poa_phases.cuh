@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 else if (beta == 0 &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                                P.gap, P.mismatch, P.match, smem, lane, start_row, 0) == 0)
+                                                P.gap, P.mismatch, P.match, smem, lane, start_row, 0, P.debug_flags) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
         const int32_t beta  = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
         if (beta > 0 && fill2_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                               P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                              P.gap, P.mismatch, P.match, smem, lane, start_row, beta) == 0)
+                                              P.gap, P.mismatch, P.match, smem, lane, start_row, beta, P.debug_flags) == 0)
         {
             st.aln_len   = kAlnPendingTraceback;
             st.start_row = start_row;
@@ -255,7 +255,8 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
             {
                 const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
                                                                        static_cast<int64_t>(w) * P.banded_score_stride);
-                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, P.smem_per_warp, st.start_row, lane);
+                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, (P.debug_flags & 2) ? kT2Bytes : P.smem_per_warp,
+                                           st.start_row, lane);
             }
             if (aln_len == -1) // cudapoa_kernels.cuh:281-289
             {
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
                             rc = kStGenericError;
                         rc = __shfl_sync(kFull, rc, 0);
                     }
-                    else if (!topsort_kahn_smem<IdT>(g, st.node_count, smem, P.smem_per_warp, lane))
+                    else if ((P.debug_flags & 1) || !topsort_kahn_smem<IdT>(g, st.node_count, smem, P.smem_per_warp, lane))
                     {
                         if (lane == 0)
                             topsort_kahn<IdT>(g, st.node_count);

@@ -175,3 +175,30 @@ def config_windows(name, n_windows, start_index=0, with_weights=False):
                                 length_probs=[0.2, 0.5, 0.2, 0.1], n_reads_range=(10, 60),
                                 with_weights=with_weights)
     raise ValueError("unknown config " + name)
+
+
+def _config_chunk(args):
+    name, n, start, with_weights = args
+    ws = config_windows(name, n, start_index=start, with_weights=with_weights)
+    return ws.bases, ws.read_lengths, ws.window_n_reads, ws.weights
+
+
+def config_windows_parallel(name, n_windows, start_index=0, with_weights=False, processes=None):
+    """config_windows over a process pool (window i depends on seed0 + i only, so the result is identical).  Call it
+    before CUDA is initialised in the process: the pool forks."""
+    import multiprocessing as mp
+    import os
+
+    if processes is None:
+        try:
+            processes = len(os.sched_getaffinity(0))
+        except AttributeError:
+            processes = os.cpu_count() or 1
+    processes = max(1, min(processes, 32, n_windows // 64))
+    if processes <= 1:
+        return config_windows(name, n_windows, start_index=start_index, with_weights=with_weights)
+    step = (n_windows + 4 * processes - 1) // (4 * processes)
+    jobs = [(name, min(step, n_windows - at), start_index + at, with_weights) for at in range(0, n_windows, step)]
+    with mp.get_context("fork").Pool(processes) as pool:
+        parts = pool.map(_config_chunk, jobs)
+    return WindowSet.concat([WindowSet(*p) for p in parts])

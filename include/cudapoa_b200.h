@@ -252,6 +252,11 @@ int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fi
 double cudapoa_b200_bench_relaunch_timed(cudapoa_b200_batch* batch, int32_t iterations, double* fill_ms,
                                          double* graph_ms, int32_t* launches);
 
+/* Native library only (development aid): copy a window's device state to the host after generate_poa.  region 0 = the
+ * window's arena slice (graph arrays, row records, scratch), 1 = its score area (move codes, spilled score rows).
+ * Returns the region's size in bytes (copies min(size, cap)), negative on error. */
+int64_t cudapoa_b200_debug_read_window(cudapoa_b200_batch* batch, int32_t window, int32_t region, void* out, int64_t cap);
+
 /* ---- Window pipeline (native library only; no reference counterpart) ------------------------------------------
  * The stream scheduler / sharding layer above the Batch interface (the reference drives several Batch objects from
  * std::async tasks in cudapoa/benchmarks/multi_batch.hpp:157-170; it has no multi-GPU code).  Each worker thread owns
