@@ -309,6 +309,18 @@ def bind_bench_hooks(dll):
     dll.cudapoa_b200_bench_relaunch_timed.restype = ctypes.c_double
     dll.cudapoa_b200_bench_relaunch_timed.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_double),
                                                       ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int32)]
+    dll.cudapoa_b200_bench_phase_ms.restype = ctypes.c_int32
+    dll.cudapoa_b200_bench_phase_ms.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.c_int32]
+
+
+PHASES = ("fill", "traceback", "fusion", "topological_sort", "consensus")
+
+
+def phase_ms(dll, batch, steps):
+    """Per-phase milliseconds per step of the last relaunch_timed call (CUDA events between the launches)."""
+    out = (ctypes.c_double * len(PHASES))()
+    n = dll.cudapoa_b200_bench_phase_ms(batch._handle, out, len(PHASES))
+    return {PHASES[i]: out[i] / steps for i in range(max(n, 0))}
 
 
 def relaunch_timed(dll, batch, steps):
@@ -349,6 +361,7 @@ def measure_other_config(name, spec, ws, lib, dll, device, ranks, max_mem, dpx_p
         ranks.barrier()
         torch.cuda.synchronize()
         total_ms, fill_ms, graph_ms, launches = relaunch_timed(dll, batch, steps)
+        phases = phase_ms(dll, batch, steps)
         ms_step = ranks.max(total_ms / steps)
         batch.fetch(spec["output"])
         stable = batch.result_digest() == digest0
@@ -366,7 +379,7 @@ def measure_other_config(name, spec, ws, lib, dll, device, ranks, max_mem, dpx_p
                 "windows_per_step_per_gpu": n, "steps": steps, "value": windows / (ms_step * 1e-3), "unit": UNIT,
                 "ms_per_step": ms_step, "e2e": windows / e2e_s, "e2e_path": "one Batch: add_poa_group -> generate_poa -> get_*",
                 "gcups": gcups, "fill_ms_per_step": fill_ms / steps, "graph_ms_per_step": graph_ms / steps,
-                "launches_per_step": launches // max(steps, 1),
+                "phase_ms_per_step": phases, "launches_per_step": launches // max(steps, 1),
                 "roofline_frac": (fill_gcups / dpx_peak_gcups) if dpx_peak_gcups > 0 and fill_ms > 0 else None,
                 "whole_step_frac": (gcups / world / dpx_peak_gcups) if dpx_peak_gcups > 0 else None,
                 "windows_ok": ok, "results_stable": stable, "exact_path_alignments": stats["exact_path"],
@@ -446,6 +459,7 @@ def run_native(args, rank, world, local_rank):
     barrier()
     sampler.mark()
     ms_total, fill_total, graph_total, n_launches = relaunch_timed(dll, batch, args.steps)
+    phases = phase_ms(dll, batch, args.steps)
     barrier()
     clocks = sampler.stop()
     if ms_total <= 0:
@@ -508,8 +522,9 @@ def run_native(args, rank, world, local_rank):
     achieved_gbs = fill_alg_bytes / (fill_launch_ms * 1e-3) / 1e9
     traffic = ncu_traffic()
     fill_traffic = traffic.get("poa_fill_kernel", {}).get("dram_bytes_per_window_step")
-    graph_traffic = traffic.get("poa_graph_kernel", {}).get("dram_bytes_per_window_step")
-    phase_ms = fill_ms + graph_ms
+    graph_traffic = sum(traffic.get(k, {}).get("dram_bytes_per_window_step") or 0.0
+                        for k in ("poa_trace_kernel", "poa_fuse_kernel", "poa_sort_kernel", "poa_final_kernel")) or None
+    step_phase_ms = fill_ms + graph_ms
     r16 = ctypes.c_double(0)
     r16ms = ctypes.c_double(0)
     dll.cudapoa_b200_debug_dpx_peak(device, 0, ctypes.byref(r16), ctypes.byref(r16ms))
@@ -538,13 +553,16 @@ def run_native(args, rank, world, local_rank):
         "kernels": {
             "launches_per_step": int(launches_per_step),
             "poa_fill_kernel": {"launches": n_fill, "ms_per_step": fill_ms,
-                                "share_of_step": fill_ms / phase_ms if phase_ms > 0 else None, "gcups": fill_gcups,
+                                "share_of_step": fill_ms / step_phase_ms if step_phase_ms > 0 else None, "gcups": fill_gcups,
                                 "dram_gb_per_s": (fill_traffic * n_win / (fill_ms * 1e-3) / 1e9) if fill_traffic else None,
                                 "note": "includes the stand-by launches after it (poa_fill_rebased_kernel, "
                                         "poa_exact_kernel: nothing to do on this workload) and poa_init_kernel"},
-            "poa_graph_kernel": {"launches": max(int(launches_per_step) - 3 * n_fill - 1, 0), "ms_per_step": graph_ms,
-                                 "share_of_step": graph_ms / phase_ms if phase_ms > 0 else None,
-                                 "dram_gb_per_s": (graph_traffic * n_win / (graph_ms * 1e-3) / 1e9) if graph_traffic else None},
+            "graph_kernels": {"launches": max(int(launches_per_step) - 3 * n_fill - 1, 0), "ms_per_step": graph_ms,
+                              "share_of_step": graph_ms / step_phase_ms if step_phase_ms > 0 else None,
+                              "dram_gb_per_s": (graph_traffic * n_win / (graph_ms * 1e-3) / 1e9) if graph_traffic else None,
+                              "poa_trace_kernel_ms": phases.get("traceback"), "poa_fuse_kernel_ms": phases.get("fusion"),
+                              "poa_sort_kernel_ms": phases.get("topological_sort"),
+                              "poa_final_kernel_ms": phases.get("consensus")},
             "note": "CUDA events between the launches of the timed region, this rank's GPU",
         },
         "roofline": {"bound": "dpx-int16", "kernel": "poa_fill_kernel", "achieved": fill_gcups, "peak": dpx_peak_gcups,

@@ -569,6 +569,19 @@ double cudapoa_b200_bench_relaunch_timed(cudapoa_b200_batch* batch, int32_t iter
     return rc == 0 ? ms : -1.0;
 }
 
+int32_t cudapoa_b200_bench_phase_ms(cudapoa_b200_batch* batch, double* out, int32_t cap)
+{
+    int32_t n  = -1;
+    int32_t rc = guarded([&]() {
+        auto* src = dynamic_cast<poa::EngineStatsSource*>(batch->impl.get());
+        if (src == nullptr || out == nullptr || cap <= 0)
+            return -1;
+        n = src->last_phase_ms(out, cap);
+        return 0;
+    });
+    return rc == 0 ? n : -1;
+}
+
 int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fill_ms, double* graph_ms)
 {
     int32_t n  = -1;

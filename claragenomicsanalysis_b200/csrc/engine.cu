@@ -181,6 +181,13 @@ public:
     double relaunch(int32_t iterations) override;
     int32_t relaunch_phases(double* fill_ms, double* graph_ms) override;
     double relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches) override;
+    int32_t last_phase_ms(double* out, int32_t cap) const override
+    {
+        const int32_t n = std::min<int32_t>(cap, kPhaseKinds);
+        for (int32_t i = 0; i < n; i++)
+            out[i] = phase_ms_[i];
+        return n;
+    }
     void set_overlapped(bool overlapped) override { overlapped_ = overlapped; }
     int64_t debug_read_window(int32_t window, int32_t region, void* out, int64_t cap) override
     {
@@ -270,6 +277,8 @@ private:
     bool launched_          = false;
     int64_t kernel_launches_ = 0; // kernels enqueued by the last generate_poa / relaunch
     PhaseTimeline* timeline_ = nullptr; // set while relaunch_phases() is timing the launches
+    static constexpr int kPhaseKinds = 5;
+    double phase_ms_[kPhaseKinds]    = {0, 0, 0, 0, 0}; // last relaunch_timed(): fill, traceback, fusion, sort, consensus
     bool overlapped_         = false;   // other batches are in flight on this device (set_overlapped)
     bool timed_             = false;
     int32_t timed_iters_    = 1;
@@ -535,7 +544,8 @@ static int32_t consensus_scratch_nodes(int32_t smem)
 }
 
 // Optional CUDA events between the launches of a batch (relaunch_timed): kinds[i] tells what ran between events[i - 1]
-// and events[i] (0 fill launch, 1 graph launch, -1 anything else: counter reset, the gap between two steps).
+// and events[i] (0 fill launches, 1 traceback, 2 fusion, 3 topological sort, 4 consensus / MSA, -1 anything else: counter
+// reset, the gap between two steps).
 struct PhaseTimeline
 {
     std::vector<cudaEvent_t> events;
@@ -559,18 +569,24 @@ struct PhaseTimeline
     }
 };
 
+// Scratch sizes of the launches of one step (bytes per warp == per window).
+struct PhaseScratch
+{
+    int32_t fill, trace, sort_small, sort_large, final_;
+};
+constexpr int32_t kCountersPerStep = 8;
+
 template <typename ScoreT, typename IdT, bool MSA>
-static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_smem, int32_t graph_smem,
-                                  int32_t graph_smem_large, int32_t* counters, int32_t sm_count, cudaStream_t stream,
-                                  PhaseTimeline* timeline)
+static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScratch& scratch,
+                                  const std::vector<uint8_t>& ends_at, int32_t* counters, int32_t sm_count,
+                                  cudaStream_t stream, PhaseTimeline* timeline)
 {
     int32_t launches = 0;
     if (timeline)
         timeline->mark(stream, -1);
-    const bool two   = graph_smem_large > graph_smem;
-    P.class_cap       = two ? kahn_smem_nodes(graph_smem) : INT32_MAX - kClassMargin;
-    P.lean_class0     = two ? 1 : 0;
-    P.class_cap_final = two ? std::min(kahn_smem_nodes(graph_smem), consensus_scratch_nodes(graph_smem)) : P.class_cap;
+    const bool two = scratch.sort_large > scratch.sort_small;
+    P.class_cap    = two ? kahn_smem_nodes(scratch.sort_small) : INT32_MAX;
+    P.lean_class0  = two ? 1 : 0;
     {
         const int32_t blocks = std::max(1, std::min((P.n_windows + kFillWarpsPerBlock - 1) / kFillWarpsPerBlock, sm_count * 16));
         auto init_kernel = poa_init_kernel<IdT, MSA>;
@@ -579,38 +595,55 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, int32_t fill_s
     }
     for (int32_t s = 1; s <= steps; s++)
     {
+        int32_t* c      = counters + kCountersPerStep * (s - 1);
         P.step          = s;
-        P.next_window   = counters + 5 * (s - 1);
-        P.smem_per_warp = fill_smem;
+        P.next_window   = c + 0;
+        P.smem_per_warp = scratch.fill;
         launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        P.next_window   = counters + 5 * (s - 1) + 4;
+        P.next_window = c + 1;
         launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        launches++;
-        P.next_window   = counters + 5 * (s - 1) + 3;
+        P.next_window   = c + 2;
         P.smem_per_warp = 0;
         launch_phase(poa_exact_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        launches++;
+        launches += 3;
         if (timeline)
             timeline->mark(stream, 0);
-        P.next_window   = counters + 5 * (s - 1) + 1;
-        P.smem_per_warp = graph_smem;
-        P.phase_class   = 0;
-        if (two)
-            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, true>, P, kGraphWarpsPerBlock, sm_count, stream);
-        else
-            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, false>, P, kGraphWarpsPerBlock, sm_count, stream);
+        P.next_window   = c + 3;
+        P.smem_per_warp = scratch.trace;
+        launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream);
         if (timeline)
             timeline->mark(stream, 1);
-        launches += 2;
+        P.next_window   = c + 4;
+        P.smem_per_warp = 0;
+        launch_phase(poa_fuse_kernel<IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+        if (timeline)
+            timeline->mark(stream, 2);
+        P.next_window   = c + 5;
+        P.smem_per_warp = scratch.sort_small;
+        P.phase_class   = 0;
+        if (two)
+            launch_phase(poa_sort_kernel<IdT, true>, P, kGraphWarpsPerBlock, sm_count, stream);
+        else
+            launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream);
+        launches += 3;
         if (two)
         {
-            P.next_window   = counters + 5 * (s - 1) + 2;
-            P.smem_per_warp = graph_smem_large;
+            P.next_window   = c + 6;
+            P.smem_per_warp = scratch.sort_large;
             P.phase_class   = 1;
-            launch_phase(poa_graph_kernel<ScoreT, IdT, MSA, false>, P, kGraphWarpsPerBlock, sm_count, stream);
-            if (timeline)
-                timeline->mark(stream, 1);
+            launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream);
             launches++;
+        }
+        if (timeline)
+            timeline->mark(stream, 3);
+        if (s == steps || ends_at[static_cast<size_t>(s)])
+        {
+            P.next_window   = c + 7;
+            P.smem_per_warp = scratch.final_;
+            launch_phase(poa_final_kernel<IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+            launches++;
+            if (timeline)
+                timeline->mark(stream, 4);
         }
     }
     return launches;
@@ -637,17 +670,25 @@ bool B200Batch::launch_split(KernelParams& P)
     for (int32_t i = 0; i < poa_count_; i++)
         max_reads = std::max(max_reads, windows_h_[i].n_reads);
     const int32_t steps = std::max(max_reads - 1, 1);
-    if (5 * steps > kPhaseCounters)
+    if (kCountersPerStep * steps > kPhaseCounters)
         return false;
-    // shared memory per window: the fill needs the row ring and the padded read, the graph phases the traceback
-    // tile and the read (the topological sort and the consensus reuse that scratch)
-    const int32_t L          = std::max(batch_size_.max_sequence_size, 1);
-    const int32_t fill_smem  = (fill2_smem_bytes(L) + 255) & ~255;
-    // graph launches: the traceback tile + the rows it records; the topological sort (8 bytes per node) and the
-    // consensus reuse the scratch
-    const int32_t graph_smem = std::max((trace2_smem_bytes(L) + 255) & ~255, 9 * 1024);
-    const int32_t graph_smem_large = std::max(graph_smem, kSmemPerWarp);
-    if (4 * std::max(fill_smem, graph_smem_large) > kPhaseSmemLimit)
+    // steps after which some window is complete (its last read; a window of one read ends at step 1)
+    std::vector<uint8_t> ends_at(static_cast<size_t>(steps) + 1, 0);
+    for (int32_t i = 0; i < poa_count_; i++)
+        ends_at[static_cast<size_t>(std::min(std::max(windows_h_[i].n_reads - 1, 1), steps))] = 1;
+    // shared memory per window and launch: the fill needs the row ring, the record buffer and the profile; the
+    // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 024 nodes,
+    // large class: the single launch's scratch); the consensus its staging area and 6 bytes per node
+    const int32_t L = std::max(batch_size_.max_sequence_size, 1);
+    PhaseScratch scratch{};
+    scratch.fill       = (fill2_smem_bytes(L) + 255) & ~255;
+    scratch.trace      = (trace2_smem_bytes(L) + 255) & ~255;
+    scratch.sort_large = kSmemPerWarp;
+    scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, 1024) + 2 * kKahnQueueEntries + 255) & ~255);
+    if (kahn_smem_nodes(scratch.sort_small) >= plan_.M)
+        scratch.sort_large = scratch.sort_small; // one class serves every graph of this batch
+    scratch.final_ = kSmemPerWarp;
+    if (4 * std::max(std::max(scratch.fill, scratch.trace), scratch.sort_large) > kPhaseSmemLimit)
         return false;
     P.phase = phase_d_;
     int32_t launches = 0;
@@ -655,16 +696,16 @@ bool B200Batch::launch_split(KernelParams& P)
     if (!plan_.score32)
     {
         if (msa_)
-            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     else
     {
         if (msa_)
-            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, fill_smem, graph_smem, graph_smem_large, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     kernel_launches_ += launches;
     return true;
@@ -822,8 +863,9 @@ double B200Batch::relaunch_timed(int32_t iterations, double* fill_ms, double* gr
     float total = 0.f;
     GW_CU_CHECK_ERR(cudaEventElapsedTime(&total, ev_start_, ev_stop_));
     double fill = 0.0, graph = 0.0;
+    std::fill(phase_ms_, phase_ms_ + kPhaseKinds, 0.0);
     if (timeline.used < 2) // single launch: everything is one kernel
-        fill = total;
+        fill = phase_ms_[0] = total;
     for (size_t i = 1; i < timeline.used; i++)
     {
         if (timeline.kinds[i] < 0)
@@ -831,6 +873,7 @@ double B200Batch::relaunch_timed(int32_t iterations, double* fill_ms, double* gr
         float ms = 0.f;
         GW_CU_CHECK_ERR(cudaEventElapsedTime(&ms, timeline.events[i - 1], timeline.events[i]));
         (timeline.kinds[i] == 0 ? fill : graph) += ms;
+        phase_ms_[std::min<int>(timeline.kinds[i], kPhaseKinds - 1)] += ms;
     }
     if (fill_ms)
         *fill_ms = fill;

@@ -28,6 +28,8 @@ public:
     // relaunch() and relaunch_phases() in one: `iterations` passes with events between the launches; returns the
     // CUDA-event time of all of them, the sums per kernel in *fill_ms / *graph_ms, the launch count in *launches.
     virtual double relaunch_timed(int32_t iterations, double* fill_ms, double* graph_ms, int32_t* launches) = 0;
+    // Per-phase totals of the last relaunch_timed(): fill, traceback, fusion, topological sort, consensus / MSA (ms).
+    virtual int32_t last_phase_ms(double* out, int32_t cap) const = 0;
     // Scheduling hint: this batch shares its device with other batches in flight (several streams).  A lone batch of
     // less than about two waves of windows is served faster by the single launch; overlapping batches by the
     // phase-split schedule whatever their size.

@@ -815,22 +815,24 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 // The same order computed in the warp's shared-memory scratch.  All 32 lanes call this.
 //   * the warp stages one 4-byte record per node (coalesced reads of the slot-major graph arrays):
 //       out-edge 0 | out-edge 1 << 12 | min(out-degree, 3) << 24 | remaining in-degree << 26
-//     and a 2-byte side record (out-edge 2 | min(out-degree - 3, 15) << 12), read only for nodes with three or more
-//     out-edges; node ids must fit 12 bits;
-//   * the FIFO is a full-length array that ends up holding the order itself (as the reference's sorted_poa doubles as
-//     its queue, cudapoa_topsort.cuh:56-85), so the serial lane never stores to global memory; when it is done the
-//     warp writes sorted[] and node_id_to_pos[] out in parallel;
-//   * lane 0 runs the FIFO.  A POA graph is mostly chains: the node popped next is usually the one pushed last, whose
-//     record the push has just had in registers -- it is kept there, so a chain step is one shared-memory load
-//     (the child's record), one store (its decremented in-degree) and one 2-byte store (the queue).
-// Returns false (nothing written) when the graph does not fit the scratch; the caller then runs topsort_kahn.
-constexpr int32_t kKahnBytesPerNode = 8; // 4 (record) + 2 (side record) + 2 (queue entry == sorted[])
+//     (node ids must fit 12 bits); the third and later out-edges of the few nodes that have them stay in global
+//     memory and are fetched as soon as such a node is popped, under the visits of its first two children;
+//   * lane 0 runs the FIFO.  The queue is a 256-entry ring (a POA graph's frontier is a handful of nodes), sorted[] and
+//     node_id_to_pos[] are written as nodes leave it: the walk is a chain of dependent shared-memory accesses, so
+//     the stores ride along for free, and 4 bytes per node is what lets ~48 windows per SM sort at the same time.
+//     A POA graph is mostly chains: the node popped next is usually the one pushed last, whose record the push has
+//     just had in registers -- it is kept there, so a chain step is one shared-memory load (the child's record)
+//     and one store (its decremented in-degree).
+// Returns false when the graph does not fit the scratch or the ring is overrun (sorted[] / node_id_to_pos[] may then
+// be partly written); the caller then runs topsort_kahn, which rewrites both.
+constexpr int32_t kKahnBytesPerNode = 4;
+constexpr int32_t kKahnQueueEntries = 256;
 constexpr int32_t kKahnMaxNodes     = 4095;
 
 // Nodes a graph may have for the sort to run out of `smem_bytes` of scratch.
 __host__ __device__ inline int32_t kahn_smem_nodes(int32_t smem_bytes)
 {
-    const int32_t n = (smem_bytes / kKahnBytesPerNode) & ~7;
+    const int32_t n = ((smem_bytes - 2 * kKahnQueueEntries) / kKahnBytesPerNode) & ~7;
     return n < kKahnMaxNodes ? n : (kKahnMaxNodes & ~7);
 }
 
@@ -843,9 +845,9 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
     const int32_t cap = kahn_smem_nodes(smem_bytes);
     if (node_count > cap)
         return false;
-    const uint32_t rec   = smem;                 // u32[cap]
-    const uint32_t queue = rec + 4u * cap;       // u16[cap]: FIFO, in the end the order
-    const uint32_t side  = queue + 2u * cap;     // u16[cap]
+    const uint32_t rec   = smem;           // u32[cap]
+    const uint32_t queue = rec + 4u * cap; // u16[kKahnQueueEntries], a ring indexed by pop / push counts
+    constexpr uint32_t kQMask = kKahnQueueEntries - 1;
     const unsigned lt    = (1u << lane) - 1u;
     int32_t tail         = 0;
 #pragma unroll 2
@@ -860,17 +862,18 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
             // slots beyond the out-degree hold stale but readable values: load unconditionally, never used
             const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0)) & 0xfffu;
             const uint32_t e1 = static_cast<uint16_t>(g.out_edge(n, 1)) & 0xfffu;
-            const uint32_t e2 = static_cast<uint16_t>(g.out_edge(n, 2)) & 0xfffu;
             sts_u32(rec + 4u * n, e0 | (e1 << 12) | (min(oc, 3u) << 24) | (ic << 26));
-            sts_u16(side + 2u * n, e2 | (min(max(oc, 3u) - 3u, 15u) << 12));
             source = (ic == 0);
         }
         const unsigned mask = __ballot_sync(kFull, source);
+        if (tail + __popc(mask) > kKahnQueueEntries) // more sources than the ring holds (uniform; nothing written yet)
+            return false;
         if (source)
             sts_u16(queue + 2u * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
         tail += __popc(mask);
     }
     __syncwarp();
+    int32_t ok = 1;
     if (lane == 0)
     {
         constexpr uint32_t kOne = 1u << 26; // one in-edge
@@ -878,7 +881,8 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         uint32_t pushed = static_cast<uint32_t>(tail);
         uint32_t node   = lds_u16(queue);   // a graph always has a source
         uint32_t v      = lds_u32(rec + 4u * node);
-        uint32_t last_node = 0, last_rec = 0, last_at = 0xffffffffu; // the node pushed last, its record and queue index
+        uint32_t last_node = 0, last_rec = 0, last_at = 0xffffffffu; // the node pushed last, its record and push index
+        IdT* sorted_out = g.sorted;
         // visit(child): one in-edge of child is satisfied; queue it when it was the last one
 #define POA_KAHN_VISIT(child_expr)                                   \
     {                                                                \
@@ -888,7 +892,7 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         sts_u32(at_, left_);                                         \
         if (left_ < kOne)                                            \
         {                                                            \
-            sts_u16(queue + 2u * pushed, child_);                    \
+            sts_u16(queue + 2u * (pushed & kQMask), child_);         \
             last_node = child_;                                      \
             last_rec  = left_;                                       \
             last_at   = pushed;                                      \
@@ -897,24 +901,33 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
     }
         for (;;)
         {
+            *sorted_out++ = static_cast<IdT>(node);
+            g.pos[node]   = static_cast<IdT>(head);
             const uint32_t oc = (v >> 24) & 3u;
+            uint32_t more = 0, e2 = 0;
+            if (oc > 2) // rare: the out-degree and the third child come from global memory, under the first two visits
+            {
+                more = static_cast<uint32_t>(g.out_cnt[node]) - 2u;
+                e2   = static_cast<uint16_t>(g.out_edge(node, 2));
+            }
             if (oc > 0)
                 POA_KAHN_VISIT(v & 0xfffu)
             if (oc > 1)
                 POA_KAHN_VISIT((v >> 12) & 0xfffu)
             if (oc > 2)
             {
-                const uint32_t s = lds_u16(side + 2u * node);
-                POA_KAHN_VISIT(s & 0xfffu)
-                uint32_t more = s >> 12;
-                if (more == 15u)
-                    more = static_cast<uint32_t>(g.out_cnt[node]) - 3u;
-                for (uint32_t e = 0; e < more; e++)
-                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(3u + e))))
+                POA_KAHN_VISIT(e2)
+                for (uint32_t e = 1; e < more; e++)
+                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(2u + e))))
             }
             head++;
             if (head == pushed)
                 break;
+            if (pushed - head > kKahnQueueEntries) // the ring was overrun: give up, the caller sorts again
+            {
+                ok = 0;
+                break;
+            }
             if (last_at == head)
             {
                 node = last_node;
@@ -922,21 +935,15 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
             }
             else
             {
-                node = lds_u16(queue + 2u * head);
+                node = lds_u16(queue + 2u * (head & kQMask));
                 v    = lds_u32(rec + 4u * node);
             }
         }
 #undef POA_KAHN_VISIT
     }
+    ok = __shfl_sync(kFull, ok, 0);
     __syncwarp();
-    for (int32_t k = lane; k < node_count; k += 32)
-    {
-        const uint32_t n = lds_u16(queue + 2u * k);
-        g.sorted[k]      = static_cast<IdT>(n);
-        g.pos[n]         = static_cast<IdT>(k);
-    }
-    __syncwarp();
-    return true;
+    return ok != 0;
 }
 
 // SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.

@@ -210,18 +210,31 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
     }
 }
 
-// LEAN: the instance of the small-scratch launch.  It leaves the windows with rebased score rows and the
-// SPOA_ACCURATE order to the other launch (class 1) and does not carry their code.
-template <typename ScoreT, typename IdT, bool MSA, bool LEAN>
-__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(const KernelParams P)
+// ---- graph work of a step, one launch per phase ------------------------------------------------------------------------
+// The phases after the fill are walks by one lane per window (traceback, topological sort) or gathers over the graph
+// (fusion): bound by dependent latency times the windows an SM keeps in flight, not by issue slots.  Each phase gets
+// a kernel of its own so that each runs at ITS occupancy -- registers and scratch of the traceback do not cap the
+// sort, and the other way round.
+
+#ifndef POA_TRACE_MIN_BLOCKS
+#define POA_TRACE_MIN_BLOCKS 10
+#endif
+#ifndef POA_FUSE_MIN_BLOCKS
+#define POA_FUSE_MIN_BLOCKS 8
+#endif
+#ifndef POA_SORT_MIN_BLOCKS
+#define POA_SORT_MIN_BLOCKS 10
+#endif
+
+// Traceback over the move codes of the read the fill launch has just aligned (poa_trace2.cuh).
+template <typename ScoreT, typename IdT>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_TRACE_MIN_BLOCKS) poa_trace_kernel(const KernelParams P)
 {
     POA_DYNAMIC_SMEM(smem_block);
     int32_t lane  = threadIdx.x & 31;
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
     asm volatile("" : "+r"(smem));
-    const int32_t s = P.step;
-
     for (;;)
     {
         int32_t w = 0;
@@ -230,121 +243,205 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 6) poa_graph_kernel(
         w = __shfl_sync(kFull, w, 0);
         if (w >= P.n_windows)
             break;
-
         PhaseState* ps = P.phase + w;
-        PhaseState st  = *ps;
-        if (st.finalized || st.graph_step == s)
+        const PhaseState st = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        if (st.aln_len != kAlnPendingTraceback || st.status != kStSuccess || st.finalized)
             continue;
-        // two launches per step, differing in scratch size: each window goes to the one its graph fits (outgrowing
-        // the scratch is legal, the sort and the consensus then run out of global memory)
         const WindowDesc wd = P.windows[w];
-        const int32_t fits  = (s >= wd.n_reads - 1) ? P.class_cap_final : P.class_cap; // last read: consensus too
-        const bool other   = st.node_count + kClassMargin > fits || (P.lean_class0 && P.spoa_accurate);
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t len   = P.read_len[wd.read_off + P.step];
+        const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
+                                                               static_cast<int64_t>(w) * P.banded_score_stride);
+        const int32_t aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, P.smem_per_warp, st.start_row, lane);
+        if (lane == 0)
+            ps->aln_len = aln_len;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// Fusion of the alignment into the graph (add_alignment).
+template <typename IdT, bool MSA>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_FUSE_MIN_BLOCKS) poa_fuse_kernel(const KernelParams P)
+{
+    int32_t lane = threadIdx.x & 31;
+    asm volatile("" : "+r"(lane));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        const PhaseState st = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        if (st.status != kStSuccess || st.finalized)
+            continue;
+        const WindowDesc wd = P.windows[w];
+        if (s >= wd.n_reads)
+            continue;
+        int32_t node_count = st.node_count;
+        int32_t status     = kStSuccess;
+        if (st.aln_len == -1) // cudapoa_kernels.cuh:281-289
+        {
+            status = kStLoopCountExceeded;
+        }
+        else
+        {
+            const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+            const int64_t off  = st.seq_off;
+            const uint8_t* seq = P.bases + wd.base_off + off;
+            const int8_t* wts  = P.weights ? P.weights + wd.base_off + off : nullptr;
+            const int32_t len  = P.read_len[wd.read_off + s];
+            status = add_alignment<IdT, MSA>(g, node_count, seq, len, wts,
+                                             MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
+                                             P.max_nodes, lane); // cudapoa_kernels.cuh:314-319 on failure
+        }
+        if (lane == 0)
+        {
+            ps->node_count = node_count;
+            ps->status     = status;
+        }
+    }
+}
+
+// Topological sort of the graph the fusion left (two launches per step that differ in scratch: a window goes to the one
+// its graph fits; outgrowing both is legal, the sort then runs out of global memory).  LEAN: the instance of the
+// small-scratch launch; it leaves the SPOA_ACCURATE order to the other one and does not carry its code.
+template <typename IdT, bool LEAN>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_SORT_MIN_BLOCKS) poa_sort_kernel(const KernelParams P)
+{
+    POA_DYNAMIC_SMEM(smem_block);
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        const PhaseState st = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        if (st.status != kStSuccess || st.finalized || st.graph_step == s)
+            continue;
+        const WindowDesc wd = P.windows[w];
+        if (s >= wd.n_reads)
+            continue;
+        const int32_t node_count = st.node_count;
+        const bool other         = node_count > P.class_cap || (P.lean_class0 && P.spoa_accurate);
         if (other != (P.phase_class == 1))
             continue;
-        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
-        const int32_t* rlen = P.read_len + wd.read_off;
-
-        if (st.status == kStSuccess && s < wd.n_reads)
+        const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        int32_t rc         = kStSuccess;
+        if (!LEAN && P.spoa_accurate)
         {
-            const uint8_t* seq = P.bases + wd.base_off + st.seq_off;
-            const int8_t* wts  = P.weights ? P.weights + wd.base_off + st.seq_off : nullptr;
-            const int32_t len  = rlen[s];
-            int32_t aln_len    = st.aln_len;
-            if (aln_len == kAlnPendingTraceback)
+            if (lane == 0 && !topsort_spoa_order<IdT>(g, node_count))
+                rc = kStGenericError;
+            rc = __shfl_sync(kFull, rc, 0);
+        }
+        else if ((P.debug_flags & 1) || !topsort_kahn_smem<IdT>(g, node_count, smem, P.smem_per_warp, lane))
+        {
+            if (lane == 0)
+                topsort_kahn<IdT>(g, node_count);
+        }
+        if (lane == 0)
+        {
+            ps->graph_step = s;
+            if (rc != kStSuccess)
+                ps->status = rc;
+        }
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// Outputs of the windows that are complete after step P.step (their last read, or a failure): consensus + coverage or
+// MSA rows, status, counters.  Launched after the steps at which some window of the batch ends, and after the last one.
+template <typename IdT, bool MSA>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, 4) poa_final_kernel(const KernelParams P)
+{
+    POA_DYNAMIC_SMEM(smem_block);
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        const PhaseState st = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        if (st.finalized)
+            continue;
+        const WindowDesc wd = P.windows[w];
+        if (st.status == kStSuccess && s < wd.n_reads - 1)
+            continue; // more reads to come
+        int32_t status = st.status;
+        if (status == kStSuccess)
+        {
+            const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+            const int32_t* rlen = P.read_len + wd.read_off;
+            if (!MSA)
             {
-                const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
-                                                                       static_cast<int64_t>(w) * P.banded_score_stride);
-                aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, (P.debug_flags & 2) ? kT2Bytes : P.smem_per_warp,
-                                           st.start_row, lane);
-            }
-            if (aln_len == -1) // cudapoa_kernels.cuh:281-289
-            {
-                st.status = kStLoopCountExceeded;
+                uint8_t* cons_out = P.consensus + static_cast<int64_t>(w) * P.max_consensus;
+                uint16_t* cov_out = P.coverage + static_cast<int64_t>(w) * P.max_consensus;
+                int32_t rc = generate_consensus_smem<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus, smem,
+                                                          P.smem_per_warp, lane);
+                if (rc < 0) // does not fit the scratch: serial version out of global memory
+                {
+                    if (lane == 0)
+                        rc = generate_consensus<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus);
+                    rc = __shfl_sync(kFull, rc, 0);
+                }
+                status = rc;
             }
             else
             {
-                __syncwarp(); // lane 0's traceback output becomes visible to the warp
-                int32_t rc = add_alignment<IdT, MSA>(g, st.node_count, seq, len, wts,
-                                                     MSA ? g.path + static_cast<int64_t>(s) * P.layout.max_seq : nullptr,
-                                                     P.max_nodes, lane);
-                __syncwarp();
-                if (rc == kStSuccess)
+                int32_t msa_len = 0;
+                if (lane == 0)
                 {
-                    if (!LEAN && P.spoa_accurate)
+                    if (!topsort_spoa_order<IdT>(g, st.node_count))
+                        status = kStGenericError;
+                    else
                     {
-                        if (lane == 0 && !topsort_spoa_order<IdT>(g, st.node_count))
-                            rc = kStGenericError;
-                        rc = __shfl_sync(kFull, rc, 0);
-                    }
-                    else if ((P.debug_flags & 1) || !topsort_kahn_smem<IdT>(g, st.node_count, smem, P.smem_per_warp, lane))
-                    {
-                        if (lane == 0)
-                            topsort_kahn<IdT>(g, st.node_count);
+                        msa_len = msa_columns<IdT>(g, st.node_count);
+                        if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
+                            status = kStSeqSizeExceeded;
                     }
                 }
+                status  = __shfl_sync(kFull, status, 0);
+                msa_len = __shfl_sync(kFull, msa_len, 0);
                 __syncwarp();
-                if (rc != kStSuccess) // cudapoa_kernels.cuh:314-319
-                    st.status = rc;
+                if (status == kStSuccess)
+                    msa_rows<IdT>(g, P.bases + wd.base_off, rlen, wd.n_reads,
+                                  P.msa + static_cast<int64_t>(w) * P.max_reads * P.max_consensus, msa_len,
+                                  P.max_consensus, P.layout.max_seq, lane);
             }
         }
-
-        if (st.status != kStSuccess || s >= wd.n_reads - 1) // the window is complete: outputs
-        {
-            int32_t status = st.status;
-            if (status == kStSuccess)
-            {
-                if (!MSA)
-                {
-                    uint8_t* cons_out = P.consensus + static_cast<int64_t>(w) * P.max_consensus;
-                    uint16_t* cov_out = P.coverage + static_cast<int64_t>(w) * P.max_consensus;
-                    int32_t rc = generate_consensus_smem<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus, smem,
-                                                              P.smem_per_warp, lane);
-                    if (rc < 0) // does not fit the scratch: serial version out of global memory
-                    {
-                        if (lane == 0)
-                            rc = generate_consensus<IdT>(g, st.node_count, cons_out, cov_out, P.max_consensus);
-                        rc = __shfl_sync(kFull, rc, 0);
-                    }
-                    status = rc;
-                }
-                else
-                {
-                    int32_t msa_len = 0;
-                    if (lane == 0)
-                    {
-                        if (!topsort_spoa_order<IdT>(g, st.node_count))
-                            status = kStGenericError;
-                        else
-                        {
-                            msa_len = msa_columns<IdT>(g, st.node_count);
-                            if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
-                                status = kStSeqSizeExceeded;
-                        }
-                    }
-                    status  = __shfl_sync(kFull, status, 0);
-                    msa_len = __shfl_sync(kFull, msa_len, 0);
-                    __syncwarp();
-                    if (status == kStSuccess)
-                        msa_rows<IdT>(g, P.bases + wd.base_off, rlen, wd.n_reads,
-                                      P.msa + static_cast<int64_t>(w) * P.max_reads * P.max_consensus, msa_len,
-                                      P.max_consensus, P.layout.max_seq, lane);
-                }
-            }
-            if (lane == 0)
-            {
-                P.status[w]     = static_cast<uint8_t>(status);
-                P.node_count[w] = st.node_count;
-                P.stat_rows[w]  = st.rows;
-                P.stat_exact[w] = st.exact;
-                P.stat_cells[w] = st.cells;
-            }
-            st.status    = status;
-            st.finalized = 1;
-        }
-        st.graph_step = s;
         if (lane == 0)
-            *ps = st;
+        {
+            P.status[w]     = static_cast<uint8_t>(status);
+            P.node_count[w] = st.node_count;
+            P.stat_rows[w]  = st.rows;
+            P.stat_exact[w] = st.exact;
+            P.stat_cells[w] = st.cells;
+            ps->status      = status;
+            ps->finalized   = 1;
+        }
         __syncwarp(); // the scratch is reused by the next window
     }
 }

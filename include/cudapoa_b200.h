@@ -252,6 +252,11 @@ int32_t cudapoa_b200_bench_relaunch_phases(cudapoa_b200_batch* batch, double* fi
 double cudapoa_b200_bench_relaunch_timed(cudapoa_b200_batch* batch, int32_t iterations, double* fill_ms,
                                          double* graph_ms, int32_t* launches);
 
+/* Native library only: per-phase totals of the last bench_relaunch_timed call, in milliseconds: out[0] score fill,
+ * out[1] traceback, out[2] fusion into the graph, out[3] topological sort, out[4] consensus / MSA.  Returns how many
+ * were written (at most `cap`), negative on error.  No reference counterpart (measurement only). */
+int32_t cudapoa_b200_bench_phase_ms(cudapoa_b200_batch* batch, double* out, int32_t cap);
+
 /* Native library only (development aid): copy a window's device state to the host after generate_poa.  region 0 = the
  * window's arena slice (graph arrays, row records, scratch), 1 = its score area (move codes, spilled score rows).
  * Returns the region's size in bytes (copies min(size, cap)), negative on error. */
