@@ -2,6 +2,7 @@
 //
 // Observable behaviour follows the reference host code (cudapoa/src/cudapoa_batch.cuh, allocate_block.hpp,
 // batch.cu, cudapoa_limits.hpp, utils.cu, cudapoa.cpp); memory layout, staging and kernels are this engine's own.
+#include "nvtx_ranges.hpp"
 #include "engine_stats.hpp"
 #include "poa_layout.hpp"
 #include "poa_window.cuh"
@@ -770,6 +771,7 @@ void B200Batch::launch()
 // generate_poa, cudapoa_batch.cuh:152-193: copies and launch are enqueued, nothing is waited for.
 void B200Batch::generate_poa()
 {
+    NvtxRange range("cudapoa_b200::generate_poa (h2d + launches)");
     scoped_device_switch dev(device_id_);
     if (poa_count_ == 0)
         return;
@@ -797,6 +799,7 @@ void B200Batch::generate_poa()
 
 void B200Batch::sync_and_collect()
 {
+    NvtxRange range("cudapoa_b200::sync_and_collect (d2h + wait)");
     const size_t n = static_cast<size_t>(poa_count_);
     GW_CU_CHECK_ERR(cudaMemcpyAsync(status_h_, status_d_, n, cudaMemcpyDeviceToHost, stream_));
     GW_CU_CHECK_ERR(cudaMemcpyAsync(node_count_h_, node_count_d_, n * 4, cudaMemcpyDeviceToHost, stream_));
@@ -903,6 +906,7 @@ StatusType B200Batch::get_consensus(std::vector<std::string>& consensus, std::ve
 {
     if (!(OutputType::consensus & output_mask_))
         return StatusType::output_type_unavailable;
+    NvtxRange range("cudapoa_b200::get_consensus");
     scoped_device_switch dev(device_id_);
     const int64_t C = batch_size_.max_consensus_size;
     if (poa_count_ > 0 && launched_)
@@ -942,6 +946,7 @@ StatusType B200Batch::get_msa(std::vector<std::vector<std::string>>& msa, std::v
 {
     if (!(OutputType::msa & output_mask_))
         return StatusType::output_type_unavailable;
+    NvtxRange range("cudapoa_b200::get_msa");
     scoped_device_switch dev(device_id_);
     const int64_t C = batch_size_.max_consensus_size;
     const int64_t S = std::max(max_sequences_per_poa_, 1);
@@ -969,6 +974,7 @@ StatusType B200Batch::get_msa(std::vector<std::vector<std::string>>& msa, std::v
 // get_graphs, cudapoa_batch.cuh:309-387: node label = base, one edge source -> sink per in-edge slot.
 void B200Batch::get_graphs(std::vector<DirectedGraph>& graphs, std::vector<StatusType>& output_status)
 {
+    NvtxRange range("cudapoa_b200::get_graphs");
     scoped_device_switch dev(device_id_);
     graphs.resize(poa_count_);
     if (poa_count_ == 0)

@@ -2,10 +2,12 @@
 //
 // The reference has no such layer; its benchmarks drive several Batch objects from std::async tasks, one stream
 // each (cudapoa/benchmarks/multi_batch.hpp:157-170).  This component does the same thing as a library service:
-// every worker thread owns one stream and one Batch on one device, pulls fixed-size chunks of windows from a shared
-// counter, stages them (add_poa_group), launches (generate_poa) and collects (get_consensus / get_msa) into result
-// slots indexed by the global window id -- so the output order is deterministic whatever the interleaving, staging
-// of one chunk overlaps the kernel of another, and several devices share one queue (tail balancing for free).
+// a pool of worker threads that lives as long as the pipeline; every worker owns one stream and one Batch on one
+// device, pulls chunks of windows from a shared schedule (most expensive windows first, small chunks at the start and
+// towards the end: plan_chunks), stages them (add_poa_group), launches (generate_poa) and collects (get_consensus /
+// get_msa) into result slots indexed by the global window id -- so the output order is deterministic whatever the
+// interleaving, staging and collecting of one chunk overlap the kernels of the others (the pool of batches is the
+// multi-buffering), and several devices share one queue (tail balancing for free).
 // Only the public C++ interface is used.
 
 #include "cudapoa_b200.h"
@@ -14,12 +16,14 @@
 #include <claraparabricks/genomeworks/cudapoa/cudapoa.hpp>
 
 #include "engine_stats.hpp"
+#include "nvtx_ranges.hpp"
 
 #include <cuda_runtime_api.h>
 
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <exception>
 #include <memory>
 #include <mutex>
@@ -37,6 +41,21 @@ struct cudapoa_b200_pipeline
         cudaStream_t stream = nullptr;
         std::unique_ptr<poa::Batch> batch;
         int32_t capacity = 0;
+        std::thread thread; // lives as long as the pipeline; sleeps between runs
+    };
+    // One run's inputs and schedule, shared by the workers.
+    struct Job
+    {
+        const uint8_t* bases          = nullptr;
+        const int8_t* weights         = nullptr;
+        const int32_t* read_lengths   = nullptr;
+        const int32_t* window_n_reads = nullptr;
+        std::vector<int64_t> read_off, base_off; // first read / first base of every window
+        std::vector<int32_t> order;              // window ids, most expensive first
+        std::vector<int32_t> chunk_end;          // chunk c covers order[chunk_end[c - 1] .. chunk_end[c])
+        std::atomic<int32_t> next_chunk{0};
+        bool want_msa = false;
+        std::string first_error;
     };
     std::vector<Worker> workers;
     int8_t output_mask = 1;
@@ -48,6 +67,13 @@ struct cudapoa_b200_pipeline
     cudapoa_b200_stats stats{};
     double wall_ms = 0;
     std::string error;
+    // worker pool
+    std::mutex mu;
+    std::condition_variable wake, done;
+    Job* job           = nullptr;
+    uint64_t generation = 0; // bumped by run(): a worker takes part in every generation once
+    int32_t busy        = 0; // workers still inside the current job
+    bool quit           = false;
 };
 
 namespace
@@ -63,6 +89,160 @@ inline void fnv(uint64_t& h, const void* data, size_t n)
         h *= 1099511628211ull;
     }
 }
+
+void add_stats(cudapoa_b200_stats& to, const cudapoa_b200_stats& s)
+{
+    to.windows += s.windows;
+    to.reads_aligned += s.reads_aligned;
+    to.dp_cells += s.dp_cells;
+    to.graph_rows += s.graph_rows;
+    to.exact_path += s.exact_path;
+    to.widened += s.widened;
+    to.kernel_launches += s.kernel_launches;
+    to.h2d_bytes += s.h2d_bytes;
+    to.d2h_bytes += s.d2h_bytes;
+    to.kernel_ms += s.kernel_ms;
+    to.graph_kernel_ms += s.graph_kernel_ms;
+}
+
+// One worker's share of a job: pull chunks until none is left.  Stage (add_poa_group), launch (generate_poa), collect
+// (get_consensus / get_msa) -- while this worker stages or collects, the other workers' kernels keep the device busy:
+// the pool of batches is the multi-buffering.
+void work(cudapoa_b200_pipeline* p, cudapoa_b200_pipeline::Worker& wk, cudapoa_b200_pipeline::Job& job)
+{
+    cudapoa_b200_stats local{};
+    try
+    {
+        cudaSetDevice(wk.device);
+        poa::Group group;
+        std::vector<poa::StatusType> seq_status, out_status;
+        std::vector<std::string> cons;
+        std::vector<std::vector<uint16_t>> cov;
+        std::vector<std::vector<std::string>> msa;
+        const int32_t n_chunks = static_cast<int32_t>(job.chunk_end.size());
+        for (;;)
+        {
+            const int32_t c = job.next_chunk.fetch_add(1);
+            if (c >= n_chunks)
+                break;
+            int32_t a       = c == 0 ? 0 : job.chunk_end[c - 1];
+            const int32_t b = job.chunk_end[c];
+            while (a < b)
+            {
+                int32_t added = 0;
+                {
+                    NvtxRange range("pipeline: stage");
+                    wk.batch->reset();
+                    for (int32_t k = a; k < b; k++)
+                    {
+                        const int32_t w = job.order[k];
+                        group.clear();
+                        int64_t off = job.base_off[w];
+                        for (int32_t r = 0; r < job.window_n_reads[w]; r++)
+                        {
+                            poa::Entry e{};
+                            e.seq     = reinterpret_cast<const char*>(job.bases + off);
+                            e.weights = job.weights != nullptr ? job.weights + off : nullptr;
+                            e.length  = job.read_lengths[job.read_off[w] + r];
+                            off += e.length;
+                            group.push_back(e);
+                        }
+                        if (wk.batch->add_poa_group(seq_status, group) != poa::StatusType::success)
+                            break; // batch full: launch what it holds, continue with the rest
+                        added++;
+                    }
+                }
+                if (added == 0)
+                    throw std::runtime_error("pipeline: window " + std::to_string(job.order[a]) + " does not fit a batch");
+                {
+                    NvtxRange range("pipeline: launch");
+                    wk.batch->generate_poa();
+                }
+                NvtxRange range("pipeline: collect");
+                out_status.clear();
+                if (job.want_msa)
+                {
+                    msa.clear();
+                    wk.batch->get_msa(msa, out_status);
+                    for (int32_t k = 0; k < added; k++)
+                        p->msa[job.order[a + k]] = std::move(msa[k]);
+                }
+                else
+                {
+                    cons.clear();
+                    cov.clear();
+                    wk.batch->get_consensus(cons, cov, out_status);
+                    for (int32_t k = 0; k < added; k++)
+                    {
+                        p->consensus[job.order[a + k]] = std::move(cons[k]);
+                        p->coverage[job.order[a + k]]  = std::move(cov[k]);
+                    }
+                }
+                for (int32_t k = 0; k < added; k++)
+                    p->status[job.order[a + k]] = static_cast<int32_t>(out_status[k]);
+                if (auto* src = dynamic_cast<poa::EngineStatsSource*>(wk.batch.get()))
+                {
+                    cudapoa_b200_stats s{};
+                    src->fill_stats(&s);
+                    add_stats(local, s);
+                }
+                a += added;
+            }
+        }
+    }
+    catch (const std::exception& e)
+    {
+        std::lock_guard<std::mutex> lock(p->mu);
+        if (job.first_error.empty())
+            job.first_error = e.what();
+        job.next_chunk.store(static_cast<int32_t>(job.chunk_end.size())); // stop the other workers
+    }
+    std::lock_guard<std::mutex> lock(p->mu);
+    add_stats(p->stats, local);
+}
+
+void worker_main(cudapoa_b200_pipeline* p, size_t wi)
+{
+    uint64_t seen = 0;
+    for (;;)
+    {
+        cudapoa_b200_pipeline::Job* job = nullptr;
+        {
+            std::unique_lock<std::mutex> lock(p->mu);
+            p->wake.wait(lock, [&] { return p->quit || p->generation != seen; });
+            if (p->quit)
+                return;
+            seen = p->generation;
+            job  = p->job;
+        }
+        work(p, p->workers[wi], *job);
+        {
+            std::lock_guard<std::mutex> lock(p->mu);
+            if (--p->busy == 0)
+                p->done.notify_all();
+        }
+    }
+}
+
+// Chunk schedule of a run over `n` windows with `workers` workers and a nominal chunk of `chunk` windows: the first
+// round of chunks is a quarter of that (the device gets work while the bulk is still being staged), then full chunks,
+// shrinking towards the end (guided self-scheduling: at most 1 / (2 workers) of what is left) so that the last
+// workers finish close together.
+std::vector<int32_t> plan_chunks(int32_t n, int32_t workers, int32_t chunk)
+{
+    std::vector<int32_t> ends;
+    const int32_t small = std::max(1, chunk / 4);
+    int32_t at          = 0;
+    while (at < n)
+    {
+        const int32_t left = n - at;
+        int32_t size       = static_cast<int32_t>(ends.size()) < workers ? small : chunk;
+        size               = std::min(size, std::max(small, left / (2 * workers)));
+        at += std::min(size, left);
+        ends.push_back(at);
+    }
+    return ends;
+}
 } // namespace
 
 extern "C" {
@@ -72,17 +252,20 @@ const char* cudapoa_b200_pipeline_last_error(void)
     return g_pipeline_error.c_str();
 }
 
+void cudapoa_b200_pipeline_destroy(cudapoa_b200_pipeline* p);
+
 cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int32_t n_devices,
                                                     int32_t workers_per_device, size_t mem_per_worker,
                                                     int8_t output_mask, const cudapoa_b200_batch_size* bs,
                                                     int16_t gap_score, int16_t mismatch_score, int16_t match_score,
                                                     int32_t cuda_banded_alignment)
 {
+    cudapoa_b200_pipeline* p = nullptr;
     try
     {
         if (n_devices <= 0 || workers_per_device <= 0)
             throw std::invalid_argument("pipeline needs at least one device and one worker");
-        std::unique_ptr<cudapoa_b200_pipeline> p(new cudapoa_b200_pipeline());
+        p              = new cudapoa_b200_pipeline();
         p->output_mask = output_mask;
         poa::BatchSize size(bs->max_sequence_size, bs->max_sequences_per_poa, bs->alignment_band_width);
         size.max_sequence_size                 = bs->max_sequence_size;
@@ -94,11 +277,14 @@ cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int3
         size.max_matrix_sequence_dimension     = bs->max_matrix_sequence_dimension;
         size.alignment_band_width              = bs->alignment_band_width;
         size.max_sequences_per_poa             = bs->max_sequences_per_poa;
-        for (int32_t d = 0; d < n_devices; d++)
+        p->workers.resize(static_cast<size_t>(n_devices) * static_cast<size_t>(workers_per_device));
+        size_t wi = 0;
+        // worker k of every device first, then worker k + 1: chunk c goes to device c mod n_devices at the start
+        for (int32_t k = 0; k < workers_per_device; k++)
         {
-            for (int32_t k = 0; k < workers_per_device; k++)
+            for (int32_t d = 0; d < n_devices; d++)
             {
-                cudapoa_b200_pipeline::Worker w;
+                cudapoa_b200_pipeline::Worker& w = p->workers[wi++];
                 w.device = devices[d];
                 if (cudaSetDevice(w.device) != cudaSuccess ||
                     cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -110,14 +296,16 @@ cudapoa_b200_pipeline* cudapoa_b200_pipeline_create(const int32_t* devices, int3
                 w.capacity = src != nullptr ? src->max_poas() : 0;
                 if (src != nullptr)
                     src->set_overlapped(workers_per_device > 1); // several batches share the device
-                p->workers.push_back(std::move(w));
             }
         }
-        return p.release();
+        for (size_t i = 0; i < p->workers.size(); i++)
+            p->workers[i].thread = std::thread(worker_main, p, i);
+        return p;
     }
     catch (const std::exception& e)
     {
         g_pipeline_error = e.what();
+        cudapoa_b200_pipeline_destroy(p);
         return nullptr;
     }
 }
@@ -126,6 +314,14 @@ void cudapoa_b200_pipeline_destroy(cudapoa_b200_pipeline* p)
 {
     if (p == nullptr)
         return;
+    {
+        std::lock_guard<std::mutex> lock(p->mu);
+        p->quit = true;
+    }
+    p->wake.notify_all();
+    for (auto& w : p->workers)
+        if (w.thread.joinable())
+            w.thread.join();
     for (auto& w : p->workers)
     {
         w.batch.reset();
@@ -139,7 +335,9 @@ void cudapoa_b200_pipeline_destroy(cudapoa_b200_pipeline* p)
 }
 
 // Process n_windows windows given as flat host buffers (layout of cudapoa_b200_add_poa_groups_flat).  Blocking.
-// chunk_windows: windows per batch round (0: a quarter of the smallest batch capacity, at least 256).
+// chunk_windows: nominal windows per batch round (0: a quarter of the smallest batch capacity, at least 256); see
+// plan_chunks.  Windows are dealt most expensive first (cost: bases of the window, i.e. reads x length at a fixed
+// band), results are indexed by window whatever the order.
 // Returns 0, or a negative value with cudapoa_b200_pipeline_last_error() set.
 int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases, const int8_t* weights,
                                   const int32_t* read_lengths, const int32_t* window_n_reads, int32_t n_windows,
@@ -147,28 +345,43 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
 {
     try
     {
-        const bool want_msa = (p->output_mask & poa::OutputType::msa) != 0;
+        NvtxRange range("cudapoa_b200_pipeline_run");
+        cudapoa_b200_pipeline::Job job;
+        job.bases          = bases;
+        job.weights        = weights;
+        job.read_lengths   = read_lengths;
+        job.window_n_reads = window_n_reads;
+        job.want_msa       = (p->output_mask & poa::OutputType::msa) != 0;
         p->status.assign(static_cast<size_t>(n_windows), static_cast<int32_t>(poa::StatusType::generic_error));
-        p->consensus.assign(want_msa ? 0 : static_cast<size_t>(n_windows), std::string());
-        p->coverage.assign(want_msa ? 0 : static_cast<size_t>(n_windows), std::vector<uint16_t>());
-        p->msa.assign(want_msa ? static_cast<size_t>(n_windows) : 0, std::vector<std::string>());
+        p->consensus.assign(job.want_msa ? 0 : static_cast<size_t>(n_windows), std::string());
+        p->coverage.assign(job.want_msa ? 0 : static_cast<size_t>(n_windows), std::vector<uint16_t>());
+        p->msa.assign(job.want_msa ? static_cast<size_t>(n_windows) : 0, std::vector<std::string>());
         p->stats = cudapoa_b200_stats{};
+        if (n_windows <= 0)
+            return 0;
 
-        // prefix offsets: first read and first base of every window
-        std::vector<int64_t> read_off(static_cast<size_t>(n_windows) + 1, 0), base_off(static_cast<size_t>(n_windows) + 1, 0);
+        job.read_off.assign(static_cast<size_t>(n_windows) + 1, 0);
+        job.base_off.assign(static_cast<size_t>(n_windows) + 1, 0);
         {
             int64_t r = 0, b = 0;
             for (int32_t w = 0; w < n_windows; w++)
             {
-                read_off[w] = r;
-                base_off[w] = b;
+                job.read_off[w] = r;
+                job.base_off[w] = b;
                 for (int32_t k = 0; k < window_n_reads[w]; k++)
                     b += read_lengths[r + k];
                 r += window_n_reads[w];
             }
-            read_off[n_windows] = r;
-            base_off[n_windows] = b;
+            job.read_off[n_windows] = r;
+            job.base_off[n_windows] = b;
         }
+        // most expensive first, in 4 K-base classes (a stable sort: windows of one class keep the input order)
+        job.order.resize(static_cast<size_t>(n_windows));
+        for (int32_t w = 0; w < n_windows; w++)
+            job.order[w] = w;
+        std::stable_sort(job.order.begin(), job.order.end(), [&](int32_t x, int32_t y) {
+            return ((job.base_off[x + 1] - job.base_off[x]) >> 12) > ((job.base_off[y + 1] - job.base_off[y]) >> 12);
+        });
         int32_t min_cap = INT32_MAX;
         for (const auto& w : p->workers)
             min_cap = std::min(min_cap, w.capacity);
@@ -176,122 +389,21 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
             throw std::runtime_error("pipeline: a batch has no capacity");
         int32_t chunk = chunk_windows > 0 ? chunk_windows : std::max(256, min_cap / 4);
         chunk         = std::min(chunk, min_cap);
+        job.chunk_end = plan_chunks(n_windows, static_cast<int32_t>(p->workers.size()), chunk);
 
-        std::atomic<int32_t> next(0);
-        std::mutex mu;
-        std::string first_error;
         const auto t0 = std::chrono::steady_clock::now();
-        std::vector<std::thread> threads;
-        for (size_t wi = 0; wi < p->workers.size(); wi++)
         {
-            threads.emplace_back([&, wi]() {
-                auto& wk = p->workers[wi];
-                cudapoa_b200_stats local{};
-                try
-                {
-                    cudaSetDevice(wk.device);
-                    poa::Group group;
-                    std::vector<poa::StatusType> seq_status, out_status;
-                    std::vector<std::string> cons;
-                    std::vector<std::vector<uint16_t>> cov;
-                    std::vector<std::vector<std::string>> msa;
-                    for (;;)
-                    {
-                        int32_t a = next.fetch_add(chunk);
-                        if (a >= n_windows)
-                            break;
-                        const int32_t b = std::min(n_windows, a + chunk);
-                        while (a < b)
-                        {
-                            wk.batch->reset();
-                            int32_t added = 0;
-                            for (int32_t w = a; w < b; w++)
-                            {
-                                group.clear();
-                                int64_t off = base_off[w];
-                                for (int32_t k = 0; k < window_n_reads[w]; k++)
-                                {
-                                    poa::Entry e{};
-                                    e.seq     = reinterpret_cast<const char*>(bases + off);
-                                    e.weights = weights != nullptr ? weights + off : nullptr;
-                                    e.length  = read_lengths[read_off[w] + k];
-                                    off += e.length;
-                                    group.push_back(e);
-                                }
-                                if (wk.batch->add_poa_group(seq_status, group) != poa::StatusType::success)
-                                    break; // batch full: launch what it holds, continue with the rest
-                                added++;
-                            }
-                            if (added == 0)
-                                throw std::runtime_error("pipeline: window " + std::to_string(a) + " does not fit a batch");
-                            wk.batch->generate_poa();
-                            out_status.clear();
-                            if (want_msa)
-                            {
-                                msa.clear();
-                                wk.batch->get_msa(msa, out_status);
-                                for (int32_t k = 0; k < added; k++)
-                                    p->msa[a + k] = std::move(msa[k]);
-                            }
-                            else
-                            {
-                                cons.clear();
-                                cov.clear();
-                                wk.batch->get_consensus(cons, cov, out_status);
-                                for (int32_t k = 0; k < added; k++)
-                                {
-                                    p->consensus[a + k] = std::move(cons[k]);
-                                    p->coverage[a + k]  = std::move(cov[k]);
-                                }
-                            }
-                            for (int32_t k = 0; k < added; k++)
-                                p->status[a + k] = static_cast<int32_t>(out_status[k]);
-                            if (auto* src = dynamic_cast<poa::EngineStatsSource*>(wk.batch.get()))
-                            {
-                                cudapoa_b200_stats s{};
-                                src->fill_stats(&s);
-                                local.windows += s.windows;
-                                local.reads_aligned += s.reads_aligned;
-                                local.dp_cells += s.dp_cells;
-                                local.graph_rows += s.graph_rows;
-                                local.exact_path += s.exact_path;
-                                local.widened += s.widened;
-                                local.kernel_launches += s.kernel_launches;
-                                local.h2d_bytes += s.h2d_bytes;
-                                local.d2h_bytes += s.d2h_bytes;
-                                local.kernel_ms += s.kernel_ms;
-                                local.graph_kernel_ms += s.graph_kernel_ms;
-                            }
-                            a += added;
-                        }
-                    }
-                }
-                catch (const std::exception& e)
-                {
-                    std::lock_guard<std::mutex> lock(mu);
-                    if (first_error.empty())
-                        first_error = e.what();
-                    next.store(n_windows); // stop the other workers
-                }
-                std::lock_guard<std::mutex> lock(mu);
-                p->stats.windows += local.windows;
-                p->stats.reads_aligned += local.reads_aligned;
-                p->stats.dp_cells += local.dp_cells;
-                p->stats.graph_rows += local.graph_rows;
-                p->stats.exact_path += local.exact_path;
-                p->stats.widened += local.widened;
-                p->stats.kernel_launches += local.kernel_launches;
-                p->stats.h2d_bytes += local.h2d_bytes;
-                p->stats.d2h_bytes += local.d2h_bytes;
-                p->stats.kernel_ms += local.kernel_ms;
-                p->stats.graph_kernel_ms += local.graph_kernel_ms;
-            });
+            std::unique_lock<std::mutex> lock(p->mu);
+            p->job  = &job;
+            p->busy = static_cast<int32_t>(p->workers.size());
+            p->generation++;
+            p->wake.notify_all();
+            p->done.wait(lock, [&] { return p->busy == 0; });
+            p->job = nullptr;
         }
-        for (auto& t : threads)
-            t.join();
         p->wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-        if (!first_error.empty())
-            throw std::runtime_error(first_error);
+        if (!job.first_error.empty())
+            throw std::runtime_error(job.first_error);
         return 0;
     }
     catch (const std::exception& e)

@@ -779,36 +779,62 @@ __device__ bool alignment_touches_band(const Graph<IdT>& g, int32_t node_count, 
     return __any_sync(kFull, touch);
 }
 
-// Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88).  Lane 0 only, global memory.
+// Kahn order with the reference's FIFO discipline (cudapoa_topsort.cuh:38-88: sources in id order, children in out-edge
+// order), out of global memory: the path of graphs that outgrow the shared-memory sort below and of 32-bit node ids.
+// Edge-parallel: sorted[] doubles as the queue; the warp pops one node at a time, lane e satisfies one in-edge of the
+// node's e-th child (the children of a node are distinct, so the decrements do not collide) and the children that
+// became ready are appended in lane order by a ballot.  The sources are compacted the same way, 32 ids at a time.
 template <typename IdT>
-__device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
+__device__ void topsort_kahn_warp(const Graph<IdT>& g, int32_t node_count, int32_t lane)
 {
-    int32_t tail = 0;
-    for (int32_t n = 0; n < node_count; n++)
+    const unsigned below = (1u << lane) - 1u;
+    int32_t tail         = 0;
+    for (int32_t n0 = 0; n0 < node_count; n0 += 32)
     {
-        const uint16_t c = g.in_cnt[n];
-        g.kahn[n]        = c;
-        if (c == 0)
+        const int32_t n = n0 + lane;
+        bool source     = false;
+        if (n < node_count)
         {
-            g.pos[n]         = static_cast<IdT>(tail);
-            g.sorted[tail++] = static_cast<IdT>(n);
+            const uint16_t pending = g.in_cnt[n];
+            g.kahn[n]              = pending;
+            source                 = pending == 0;
         }
+        const unsigned mask = __ballot_sync(kFull, source);
+        if (source)
+        {
+            const int32_t at = tail + __popc(mask & below);
+            g.sorted[at]     = static_cast<IdT>(n);
+            g.pos[n]         = static_cast<IdT>(at);
+        }
+        tail += __popc(mask);
     }
+    __syncwarp();
     for (int32_t head = 0; head < tail; head++)
     {
-        const int32_t node = g.sorted[head];
-        const int32_t oc   = g.out_cnt[node];
-        for (int32_t e = 0; e < oc; e++)
+        const int32_t node   = g.sorted[head]; // one address for the warp: a broadcast
+        const int32_t fanout = g.out_cnt[node];
+        for (int32_t e0 = 0; e0 < fanout; e0 += 32)
         {
-            const int32_t child = g.out_edge(node, e);
-            const uint16_t c    = g.kahn[child] - 1;
-            g.kahn[child]       = c;
-            if (c == 0)
+            const int32_t e = e0 + lane;
+            bool ready      = false;
+            int32_t child   = 0;
+            if (e < fanout)
             {
-                g.pos[child]     = static_cast<IdT>(tail);
-                g.sorted[tail++] = static_cast<IdT>(child);
+                child                  = g.out_edge(node, e);
+                const uint16_t pending = static_cast<uint16_t>(g.kahn[child] - 1);
+                g.kahn[child]          = pending;
+                ready                  = pending == 0;
             }
+            const unsigned mask = __ballot_sync(kFull, ready);
+            if (ready)
+            {
+                const int32_t at = tail + __popc(mask & below);
+                g.sorted[at]     = static_cast<IdT>(child);
+                g.pos[child]     = static_cast<IdT>(at);
+            }
+            tail += __popc(mask);
         }
+        __syncwarp(); // the appended ids are read by every lane
     }
 }
 
@@ -824,7 +850,7 @@ __device__ void topsort_kahn(const Graph<IdT>& g, int32_t node_count)
 //     just had in registers -- it is kept there, so a chain step is one shared-memory load (the child's record)
 //     and one store (its decremented in-degree).
 // Returns false when the graph does not fit the scratch or the ring is overrun (sorted[] / node_id_to_pos[] may then
-// be partly written); the caller then runs topsort_kahn, which rewrites both.
+// be partly written); the caller then runs topsort_kahn_warp, which rewrites both.
 constexpr int32_t kKahnBytesPerNode = 4;
 constexpr int32_t kKahnQueueEntries = 256;
 constexpr int32_t kKahnMaxNodes     = 4095;
@@ -946,280 +972,248 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
     return ok != 0;
 }
 
-// SPOA-order DFS that keeps aligned nodes contiguous (cudapoa_topsort.cuh:94-189).  Lane 0 only.
-// Returns false if the explicit stack would overflow its 4*M capacity.
+// Topological order that keeps aligned nodes next to each other (the SPOA_ACCURATE build of the reference and every
+// MSA: cudapoa_topsort.cuh:94-189).  The reference's order is that of a depth-first walk towards predecessors in which
+// a node first visits its aligned nodes (last to first), then its predecessors (last to first), and a group of
+// aligned nodes is emitted -- leader, then the leader's aligned list -- when the member the walk met first (the leader)
+// completes.  Here the walk keeps one frame per open node, (node, candidates still to visit), instead of a stack of
+// pending ids; the warp looks at 32 candidates of the open node at a time (lane k: the k-th from the end), and the
+// group is written out by the lanes together.  check[n] stays 1 exactly for the leaders, which is what msa_columns
+// counts.  All 32 lanes.
 template <typename IdT>
-__device__ bool topsort_spoa_order(const Graph<IdT>& g, int32_t node_count)
+__device__ void topsort_spoa_order(const Graph<IdT>& g, int32_t node_count, int32_t lane)
 {
-    for (int32_t i = 0; i < node_count; i++)
+    constexpr uint8_t kOpen = 1, kDone = 2;
+    for (int32_t n = lane; n < node_count; n += 32)
     {
-        g.marks[i] = 0;
-        g.check[i] = 1;
+        g.marks[n] = 0;
+        g.check[n] = 1;
     }
-    const int32_t cap = 4 * g.M - 2 * (kMaxNodeEdges + kMaxNodeAlignments);
-    int32_t top       = -1;
-    int32_t out       = 0;
-    for (int32_t i = 0; i < node_count; i++)
+    __syncwarp();
+    IdT* frames = g.stack; // frames[2 d] = node, frames[2 d + 1] = candidates left; depth <= node_count <= M
+    int32_t out = 0;
+    for (int32_t root = 0; root < node_count; root++)
     {
-        if (g.marks[i] != 0)
+        const bool visited = g.marks[root] != 0; // uniform
+        __syncwarp();                            // .. and read by every lane before lane 0 marks the root
+        if (visited)
             continue;
-        g.stack[++top] = static_cast<IdT>(i);
-        while (top != -1)
+        int32_t depth = 0;
+        int32_t node  = root;
+        int32_t left  = -1; // -1: not looked at yet
+        for (;;)
         {
-            const int32_t node = g.stack[top];
-            bool valid         = true;
-            if (g.marks[node] != 2)
+            const int32_t n_in  = g.in_cnt[node];
+            const int32_t n_aln = g.check[node] ? static_cast<int32_t>(g.aln_cnt[node]) : 0;
+            if (left < 0)
             {
-                if (top >= cap)
-                    return false;
-                const int32_t ic = g.in_cnt[node];
-                for (int32_t e = 0; e < ic; e++)
+                // first look: this node leads its group unless an aligned node got here first; the aligned nodes
+                // that are still open follow it (check = 0: they neither emit nor look at their own aligned lists)
+                for (int32_t a = lane; a < n_aln; a += 32)
                 {
-                    const int32_t b = g.in_edge(node, e);
-                    if (g.marks[b] != 2)
-                    {
-                        g.stack[++top] = static_cast<IdT>(b);
-                        valid          = false;
-                    }
+                    const int32_t peer = g.aln(node, a);
+                    if (g.marks[peer] != kDone)
+                        g.check[peer] = 0;
                 }
-                if (g.check[node])
-                {
-                    const int32_t na = g.aln_cnt[node];
-                    for (int32_t a = 0; a < na; a++)
-                    {
-                        const int32_t aid = g.aln(node, a);
-                        if (g.marks[aid] != 2)
-                        {
-                            g.stack[++top] = static_cast<IdT>(aid);
-                            g.check[aid]   = 0;
-                            valid          = false;
-                        }
-                    }
-                }
-                if (valid)
-                {
-                    g.marks[node] = 2;
-                    if (g.check[node])
-                    {
-                        g.sorted[out] = static_cast<IdT>(node);
-                        g.pos[node]   = static_cast<IdT>(out);
-                        out++;
-                        const int32_t na = g.aln_cnt[node];
-                        for (int32_t a = 0; a < na; a++)
-                        {
-                            const int32_t aid = g.aln(node, a);
-                            g.sorted[out]     = static_cast<IdT>(aid);
-                            g.pos[aid]        = static_cast<IdT>(out);
-                            out++;
-                        }
-                    }
-                }
-                else
-                {
-                    g.marks[node] = 1;
-                }
+                if (lane == 0)
+                    g.marks[node] = kOpen;
+                left = n_in + n_aln;
             }
-            if (valid)
-                top--;
-        }
-    }
-    return true;
-}
-
-// Re-score the tail of the graph after invalidating the competitors of the current best node
-// (cudapoa_generate_consensus.cuh:28-112).
-template <typename IdT>
-__device__ int32_t branch_completion(const Graph<IdT>& g, int32_t max_pos, int32_t node_count)
-{
-    int32_t node = g.sorted[max_pos];
-    const int32_t oc = g.out_cnt[node];
-    for (int32_t oe = 0; oe < oc; oe++)
-    {
-        const int32_t child = g.out_edge(node, oe);
-        const int32_t ic    = g.in_cnt[child];
-        for (int32_t ie = 0; ie < ic; ie++)
-        {
-            const int32_t id = g.in_edge(child, ie);
-            if (id != node)
-                g.cscore[id] = -1;
-        }
-    }
-    int32_t max_score = 0, max_id = 0;
-    for (int32_t p = max_pos + 1; p < node_count; p++)
-    {
-        node          = g.sorted[p];
-        int32_t pred  = -1;
-        int32_t score = -1;
-        const int32_t ic = g.in_cnt[node];
-        for (int32_t e = 0; e < ic; e++)
-        {
-            const int32_t begin = g.in_edge(node, e);
-            const int32_t bsc   = g.cscore[begin];
-            if (bsc == -1)
+            // next candidate that is not done, from the end: aligned nodes occupy [n_in, n_in + n_aln)
+            int32_t next = -1;
+            while (left > 0)
+            {
+                const int32_t c = left - 1 - lane;
+                int32_t cand    = -1;
+                if (c >= 0)
+                {
+                    cand = c >= n_in ? static_cast<int32_t>(g.aln(node, c - n_in)) : static_cast<int32_t>(g.in_edge(node, c));
+                    if (g.marks[cand] == kDone)
+                        cand = -1;
+                }
+                const unsigned mask = __ballot_sync(kFull, cand >= 0);
+                if (mask != 0)
+                {
+                    const int32_t first = __ffs(mask) - 1;
+                    next                = __shfl_sync(kFull, cand, first);
+                    left                = left - 1 - first;
+                    break;
+                }
+                left = max(left - 32, 0);
+            }
+            if (next >= 0)
+            {
+                if (lane == 0)
+                {
+                    frames[2 * depth]     = static_cast<IdT>(node);
+                    frames[2 * depth + 1] = static_cast<IdT>(left);
+                }
+                depth++;
+                node = next;
+                left = -1;
+                __syncwarp();
                 continue;
-            const int32_t w = g.weight(node, e);
-            if (score < w || (score == w && g.cscore[pred] <= bsc))
-            {
-                score = w;
-                pred  = begin;
             }
+            // every candidate is done: the node is, too; a leader emits its group
+            if (g.check[node])
+            {
+                const int32_t members = 1 + g.aln_cnt[node];
+                for (int32_t m = lane; m < members; m += 32)
+                {
+                    const int32_t id = m == 0 ? node : static_cast<int32_t>(g.aln(node, m - 1));
+                    g.sorted[out + m] = static_cast<IdT>(id);
+                    g.pos[id]         = static_cast<IdT>(out + m);
+                }
+                out += members;
+            }
+            if (lane == 0)
+                g.marks[node] = kDone;
+            __syncwarp();
+            if (depth == 0)
+                break;
+            depth--;
+            node = frames[2 * depth];
+            left = frames[2 * depth + 1];
+            __syncwarp(); // the frame's slot is free for the next push
         }
-        g.cpred[node] = static_cast<IdT>(pred);
-        if (pred != -1)
-            score += g.cscore[pred];
-        if (max_score <= score)
-        {
-            max_score = score;
-            max_id    = node;
-        }
-        g.cscore[node] = score;
     }
-    return max_id;
 }
 
-// Heaviest-bundle consensus (cudapoa_generate_consensus.cuh:134-276).  Lane 0 only.  Writes the consensus and
-// its coverage end -> start, NUL-terminated; returns a StatusType value.
-template <typename IdT>
-__device__ int32_t generate_consensus(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus,
-                                      uint16_t* coverage, int32_t max_consensus)
+// ---- heaviest-bundle consensus (cudapoa_generate_consensus.cuh:28-276) ---------------------------------
+// One formulation for every graph size.  All 32 lanes call these.
+//   * the node scores and predecessors of the recurrence live in the warp's scratch when the graph fits it (6 bytes
+//     per node, 16-bit ids) and in the window's arena otherwise (ConsensusStore);
+//   * scoring pass (consensus_scores): the warp stages a block of ranks at a time into shared memory -- node, in-degree,
+//     first three in-edges and their weights; two gather levels, eight ranks per lane in flight -- and lane 0 runs the
+//     recurrence over the staged records.  The first pass scores every rank; after the heaviest node turned out not to
+//     be a sink, its competitors (the other predecessors of its children) are struck out by the lanes together and
+//     the same pass re-scores the ranks after it, now ignoring struck-out predecessors (the reference's
+//     branchCompletion);
+//   * backtrack: lane 0 follows the predecessor chain and records the node ids, then the warp emits bases and
+//     coverages for all of them in parallel.
+// Tie-breaks as in the reference: among the in-edges of a node the heaviest wins, then the one whose source scores
+// higher, then the later one (`<=`, :179-181); among nodes the later rank wins (`<=`, :196).
+constexpr int32_t kConsStageBytes = 4096;
+
+template <typename IdT, bool SMEM>
+struct ConsensusStore
 {
-    int32_t max_id = 0, max_score = -1;
-    for (int32_t p = 0; p < node_count; p++)
+    const Graph<IdT>& g;
+    uint32_t score_s; // int32[cap], by node id
+    uint32_t pred_s;  // u16[cap], by node id (0xffff: none)
+    __device__ __forceinline__ int32_t score(int32_t n) const
     {
-        const int32_t node = g.sorted[p];
-        int32_t pred       = -1;
-        int32_t score      = -1;
-        const int32_t ic   = g.in_cnt[node];
-        for (int32_t e = 0; e < ic; e++)
+        if (SMEM)
+            return static_cast<int32_t>(lds_u32(score_s + 4u * static_cast<uint32_t>(n)));
+        return g.cscore[n];
+    }
+    __device__ __forceinline__ void set_score(int32_t n, int32_t v) const
+    {
+        if (SMEM)
+            sts_u32(score_s + 4u * static_cast<uint32_t>(n), static_cast<uint32_t>(v));
+        else
+            g.cscore[n] = v;
+    }
+    __device__ __forceinline__ int32_t pred(int32_t n) const // -1: none
+    {
+        if (SMEM)
         {
-            const int32_t w     = g.weight(node, e);
-            const int32_t begin = g.in_edge(node, e);
-            if (score < w || (score == w && g.cscore[pred] <= g.cscore[begin]))
-            {
-                score = w;
-                pred  = begin;
-            }
+            const uint32_t p = lds_u16(pred_s + 2u * static_cast<uint32_t>(n));
+            return p == 0xffffu ? -1 : static_cast<int32_t>(p);
         }
-        g.cpred[node] = static_cast<IdT>(pred);
-        if (pred != -1)
-            score += g.cscore[pred];
-        if (max_score <= score)
-        {
-            max_id    = node;
-            max_score = score;
-        }
-        g.cscore[node] = score;
+        return static_cast<int32_t>(g.cpred[n]);
     }
-    int32_t loops = 0;
-    while (g.out_cnt[max_id] != 0 && loops < node_count)
+    __device__ __forceinline__ void set_pred(int32_t n, int32_t p) const
     {
-        max_id = branch_completion<IdT>(g, g.pos[max_id], node_count);
-        loops++;
+        if (SMEM)
+            sts_u16(pred_s + 2u * static_cast<uint32_t>(n), static_cast<uint32_t>(p) & 0xffffu);
+        else
+            g.cpred[n] = static_cast<IdT>(p);
     }
-    if (loops >= node_count)
-        return kStLoopCountExceeded;
+};
 
-    int32_t at = 0, count = 0;
-    while (true)
-    {
-        consensus[at] = g.nodes[max_id];
-        uint16_t cov  = g.cov[max_id];
-        const int32_t na = g.aln_cnt[max_id];
-        for (int32_t a = 0; a < na; a++)
-            cov = static_cast<uint16_t>(cov + g.cov[g.aln(max_id, a)]);
-        coverage[at] = cov;
-        const int32_t pred = g.cpred[max_id];
-        if (pred == -1)
-            break;
-        max_id = pred;
-        at     = min(at + 1, max_consensus - 1);
-        count++;
-    }
-    if (count >= max_consensus - 1)
-        return kStSeqSizeExceeded;
-    consensus[at + 1] = 0;
-    return kStSuccess;
-}
-
-// The same consensus out of the warp's shared-memory scratch.  All lanes call this.
-//   * forward pass: the warp stages 256 ranks at a time (node, in-degree, first three in-edges and their weights;
-//     two gather levels, eight ranks per lane in flight), lane 0 runs the recurrence with node scores and
-//     predecessors in shared memory (and mirrors them to global memory for branch_completion);
-//   * backtrack: lane 0 follows the predecessor chain in shared memory and records the node ids, then the warp
-//     emits bases and coverages for all of them in parallel.
-// Returns -1 when the graph or the consensus does not fit the scratch (nothing written: use generate_consensus).
-constexpr int32_t kConsStageRanks = 256;
-constexpr int32_t kConsStageBytes = kConsStageRanks * 16;
-
-template <typename IdT>
-__device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus,
-                                           uint16_t* coverage, int32_t max_consensus, uint32_t smem,
-                                           int32_t smem_bytes, int32_t lane)
+// Scores ranks first_rank .. node_count - 1 and returns the heaviest node among them (`best_id` if none reaches
+// `best_score`).  `skip_struck`: predecessors whose score is -1 do not count.
+template <typename IdT, bool SMEM>
+__device__ int32_t consensus_scores(const ConsensusStore<IdT, SMEM>& store, int32_t first_rank, int32_t node_count,
+                                    bool skip_struck, int32_t best_score, int32_t best_id, uint32_t stage, int32_t lane)
 {
-    if (sizeof(IdT) != 2)
-        return -1;
-    const int32_t cap = ((smem_bytes - kConsStageBytes) / 6) & ~7;
-    if (node_count > cap || max_consensus > kConsStageBytes / 2)
-        return -1;
-    const uint32_t stage  = smem;                        // uint4[256], later the path as u16[]
-    const uint32_t cscore = stage + kConsStageBytes;     // int32[cap], by node id
-    const uint32_t cpred  = cscore + 4 * cap;            // u16[cap], by node id (0xffff: none)
-
-    int32_t max_id = 0, max_score = -1;
-    for (int32_t c0 = 0; c0 < node_count; c0 += kConsStageRanks)
+    const Graph<IdT>& g = store.g;
+    // staged record of a rank: 16 bytes with 16-bit ids, 32 with 32-bit ids
+    constexpr int32_t kRecBytes = sizeof(IdT) == 2 ? 16 : 32;
+    constexpr int32_t kRanks    = kConsStageBytes / kRecBytes;
+    constexpr int32_t kPerLane  = kRanks / 32;
+    for (int32_t c0 = first_rank; c0 < node_count; c0 += kRanks)
     {
-        // stage ranks c0 .. c0 + 255
-        int32_t node[8];
+        int32_t node[kPerLane];
 #pragma unroll
-        for (int u = 0; u < 8; u++)
+        for (int u = 0; u < kPerLane; u++)
             node[u] = g.sorted[min(c0 + lane + 32 * u, node_count - 1)];
 #pragma unroll
-        for (int u = 0; u < 8; u++)
+        for (int u = 0; u < kPerLane; u++)
         {
-            const uint32_t n  = static_cast<uint32_t>(node[u]);
+            const int32_t n   = node[u];
             const uint32_t ic = g.in_cnt[n];
             // slots beyond the in-degree hold stale but readable values
-            const uint32_t e0 = static_cast<uint16_t>(g.in_edge(n, 0)), e1 = static_cast<uint16_t>(g.in_edge(n, 1)),
-                           e2 = static_cast<uint16_t>(g.in_edge(n, 2));
             const uint32_t w0 = g.weight(n, 0), w1 = g.weight(n, 1), w2 = g.weight(n, 2);
-            sts_v4(stage + 16u * (lane + 32 * u), make_uint4(n | (ic << 16), e0 | (e1 << 16), w0 | (w1 << 16), e2 | (w2 << 16)));
+            const uint32_t at = stage + static_cast<uint32_t>(kRecBytes * (lane + 32 * u));
+            if (sizeof(IdT) == 2)
+            {
+                const uint32_t e0 = static_cast<uint16_t>(g.in_edge(n, 0)), e1 = static_cast<uint16_t>(g.in_edge(n, 1)),
+                               e2 = static_cast<uint16_t>(g.in_edge(n, 2));
+                sts_v4(at, make_uint4(static_cast<uint32_t>(n) | (ic << 16), e0 | (e1 << 16), w0 | (w1 << 16), e2 | (w2 << 16)));
+            }
+            else
+            {
+                sts_v4(at, make_uint4(static_cast<uint32_t>(n), ic, static_cast<uint32_t>(g.in_edge(n, 0)),
+                                      static_cast<uint32_t>(g.in_edge(n, 1))));
+                sts_v4(at + 16u, make_uint4(static_cast<uint32_t>(g.in_edge(n, 2)), w0 | (w1 << 16), w2, 0u));
+            }
         }
         __syncwarp();
         if (lane == 0)
         {
-            const int32_t cend = min(kConsStageRanks, node_count - c0);
+            const int32_t cend = min(kRanks, node_count - c0);
             for (int32_t q = 0; q < cend; q++)
             {
-                const uint4 rec    = lds_v4(stage + 16u * q);
-                const int32_t n    = static_cast<int32_t>(rec.x & 0xffffu);
-                const int32_t ic   = static_cast<int32_t>(rec.x >> 16);
+                const uint4 ra = lds_v4(stage + static_cast<uint32_t>(kRecBytes * q));
+                uint4 rb       = make_uint4(0u, 0u, 0u, 0u);
+                int32_t n, ic;
+                if (sizeof(IdT) == 2)
+                {
+                    n  = static_cast<int32_t>(ra.x & 0xffffu);
+                    ic = static_cast<int32_t>(ra.x >> 16);
+                }
+                else
+                {
+                    rb = lds_v4(stage + static_cast<uint32_t>(kRecBytes * q) + 16u);
+                    n  = static_cast<int32_t>(ra.x);
+                    ic = static_cast<int32_t>(ra.y);
+                }
                 int32_t pred       = -1;
                 int32_t score      = -1;
-                int32_t pred_score = 0; // cscore[pred]
+                int32_t pred_score = 0; // score of `pred`
                 for (int32_t e = 0; e < ic; e++)
                 {
                     int32_t begin, w;
-                    if (e == 0)
+                    if (e > 2)
                     {
-                        begin = static_cast<int32_t>(rec.y & 0xffffu);
-                        w     = static_cast<int32_t>(rec.z & 0xffffu);
+                        begin = static_cast<int32_t>(g.in_edge(n, e));
+                        w     = g.weight(n, e);
                     }
-                    else if (e == 1)
+                    else if (sizeof(IdT) == 2)
                     {
-                        begin = static_cast<int32_t>(rec.y >> 16);
-                        w     = static_cast<int32_t>(rec.z >> 16);
-                    }
-                    else if (e == 2)
-                    {
-                        begin = static_cast<int32_t>(rec.w & 0xffffu);
-                        w     = static_cast<int32_t>(rec.w >> 16);
+                        begin = static_cast<int32_t>(e == 0 ? (ra.y & 0xffffu) : e == 1 ? (ra.y >> 16) : (ra.w & 0xffffu));
+                        w     = static_cast<int32_t>(e == 0 ? (ra.z & 0xffffu) : e == 1 ? (ra.z >> 16) : (ra.w >> 16));
                     }
                     else
                     {
-                        begin = static_cast<uint16_t>(g.in_edge(n, e));
-                        w     = g.weight(n, e);
+                        begin = static_cast<int32_t>(e == 0 ? ra.z : e == 1 ? ra.w : rb.x);
+                        w     = static_cast<int32_t>(e == 0 ? (rb.y & 0xffffu) : e == 1 ? (rb.y >> 16) : rb.z);
                     }
-                    const int32_t bsc = static_cast<int32_t>(lds_u32(cscore + 4u * begin));
+                    const int32_t bsc = store.score(begin);
+                    if (skip_struck && bsc == -1)
+                        continue;
                     if (score < w || (score == w && pred_score <= bsc))
                     {
                         score      = w;
@@ -1229,51 +1223,60 @@ __device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_cou
                 }
                 if (pred != -1)
                     score += pred_score;
-                if (max_score <= score)
+                if (best_score <= score)
                 {
-                    max_id    = n;
-                    max_score = score;
+                    best_id    = n;
+                    best_score = score;
                 }
-                sts_u32(cscore + 4u * n, static_cast<uint32_t>(score));
-                sts_u16(cpred + 2u * n, static_cast<uint32_t>(pred) & 0xffffu);
-                g.cscore[n] = score; // mirrors for branch_completion
-                g.cpred[n]  = static_cast<IdT>(pred);
+                store.set_score(n, score);
+                store.set_pred(n, pred);
             }
         }
         __syncwarp();
     }
-    int32_t loops = 0;
-    if (lane == 0)
+    return __shfl_sync(kFull, best_id, 0);
+}
+
+template <typename IdT, bool SMEM>
+__device__ int32_t consensus_with_store(const ConsensusStore<IdT, SMEM>& store, int32_t node_count, uint8_t* consensus,
+                                        uint16_t* coverage, int32_t max_consensus, uint32_t stage, int32_t lane)
+{
+    const Graph<IdT>& g = store.g;
+    int32_t best        = consensus_scores<IdT, SMEM>(store, 0, node_count, false, -1, 0, stage, lane);
+    int32_t rounds      = 0;
+    while (g.out_cnt[best] != 0 && rounds < node_count) // uniform
     {
-        while (g.out_cnt[max_id] != 0 && loops < node_count)
+        // the heaviest node is not a sink: strike out the other predecessors of its children, score what follows it again
+        const int32_t fanout = g.out_cnt[best];
+        for (int32_t oe = 0; oe < fanout; oe++)
         {
-            max_id = branch_completion<IdT>(g, g.pos[max_id], node_count);
-            loops++;
+            const int32_t child = g.out_edge(best, oe);
+            const int32_t ic    = g.in_cnt[child];
+            for (int32_t ie = lane; ie < ic; ie += 32)
+            {
+                const int32_t rival = g.in_edge(child, ie);
+                if (rival != best)
+                    store.set_score(rival, -1);
+            }
         }
+        __syncwarp();
+        best = consensus_scores<IdT, SMEM>(store, static_cast<int32_t>(g.pos[best]) + 1, node_count, true, 0, 0, stage, lane);
+        rounds++;
     }
-    loops  = __shfl_sync(kFull, loops, 0);
-    max_id = __shfl_sync(kFull, max_id, 0);
-    if (loops >= node_count)
+    if (rounds >= node_count)
         return kStLoopCountExceeded;
-    if (loops > 0) // predecessors changed in global memory: refresh the shared copy
-    {
-        __syncwarp();
-        for (int32_t n = lane; n < node_count; n += 32)
-            sts_u16(cpred + 2u * n, static_cast<uint32_t>(static_cast<int32_t>(g.cpred[n])) & 0xffffu);
-        __syncwarp();
-    }
-    // backtrack: node ids of the path, end -> start
-    const uint32_t path = stage;
-    int32_t count       = 0;
+    // backtrack: node ids of the path, end -> start, into the arena's stack area (4 M ids; a path has at most M)
+    IdT* path     = g.stack;
+    int32_t count = 0;
     if (lane == 0)
     {
-        uint32_t id = static_cast<uint32_t>(max_id);
-        while (true)
+        int32_t id = best;
+        for (;;)
         {
             if (count < max_consensus)
-                sts_u16(path + 2u * count, id);
-            const uint32_t pred = lds_u16(cpred + 2u * id);
-            if (pred == 0xffffu)
+                path[count] = static_cast<IdT>(id);
+            const int32_t pred = store.pred(id);
+            if (pred == -1)
                 break;
             id = pred;
             count++;
@@ -1285,7 +1288,7 @@ __device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_cou
     __syncwarp();
     for (int32_t k = lane; k <= count; k += 32)
     {
-        const int32_t id = static_cast<int32_t>(lds_u16(path + 2u * k));
+        const int32_t id = path[k];
         consensus[k]     = g.nodes[id];
         uint16_t cov     = g.cov[id];
         const int32_t na = g.aln_cnt[id];
@@ -1298,21 +1301,53 @@ __device__ int32_t generate_consensus_smem(const Graph<IdT>& g, int32_t node_cou
     return kStSuccess;
 }
 
-// MSA column of every node (cudapoa_generate_msa.cuh:27-46); needs the SPOA-order sort.  Lane 0 only.
-template <typename IdT>
-__device__ int32_t msa_columns(const Graph<IdT>& g, int32_t node_count)
+// Nodes a graph may have for its consensus scores to live in `smem_bytes` of scratch.
+__host__ __device__ inline int32_t consensus_smem_nodes(int32_t smem_bytes)
 {
-    int32_t col = 0;
-    for (int32_t rank = 0; rank < node_count; rank++)
+    return ((smem_bytes - kConsStageBytes) / 6) & ~7;
+}
+
+// Writes the consensus and its coverage end -> start, NUL-terminated; returns a StatusType value.  Needs at least
+// kConsStageBytes of scratch at `smem`.
+template <typename IdT>
+__device__ int32_t generate_consensus(const Graph<IdT>& g, int32_t node_count, uint8_t* consensus, uint16_t* coverage,
+                                      int32_t max_consensus, uint32_t smem, int32_t smem_bytes, int32_t lane)
+{
+    const int32_t cap = consensus_smem_nodes(smem_bytes);
+    if (sizeof(IdT) == 2 && node_count <= cap)
     {
-        const int32_t node = g.sorted[rank];
-        g.msa_pos[node]    = static_cast<IdT>(col);
-        const int32_t na   = g.aln_cnt[node];
-        for (int32_t k = 0; k < na; k++)
-            g.msa_pos[g.sorted[++rank]] = static_cast<IdT>(col);
-        col++;
+        const ConsensusStore<IdT, true> store{g, smem + kConsStageBytes, smem + kConsStageBytes + 4u * static_cast<uint32_t>(cap)};
+        return consensus_with_store<IdT, true>(store, node_count, consensus, coverage, max_consensus, smem, lane);
     }
-    return col;
+    const ConsensusStore<IdT, false> store{g, 0u, 0u};
+    return consensus_with_store<IdT, false>(store, node_count, consensus, coverage, max_consensus, smem, lane);
+}
+
+// MSA column of every node (cudapoa_generate_msa.cuh:27-46): the nodes of an aligned group share a column, columns
+// count the groups in sorted order.  After topsort_spoa_order a group's ranks are contiguous and start with its leader,
+// the one member with check[] == 1, so the column of a rank is the number of leaders up to it: a ballot per 32 ranks.
+template <typename IdT>
+__device__ int32_t msa_columns(const Graph<IdT>& g, int32_t node_count, int32_t lane)
+{
+    const unsigned upto = 0xffffffffu >> (31 - lane);
+    int32_t columns     = 0;
+    for (int32_t r0 = 0; r0 < node_count; r0 += 32)
+    {
+        const int32_t r = r0 + lane;
+        int32_t node    = 0;
+        bool leader     = false;
+        if (r < node_count)
+        {
+            node   = g.sorted[r];
+            leader = g.check[node] != 0;
+        }
+        const unsigned mask = __ballot_sync(kFull, leader);
+        if (r < node_count)
+            g.msa_pos[node] = static_cast<IdT>(columns + __popc(mask & upto) - 1);
+        columns += __popc(mask);
+    }
+    __syncwarp();
+    return columns;
 }
 
 // One MSA row per read (cudapoa_generate_msa.cuh:48-118): the whole warp writes row s -- '-' everywhere, then

@@ -127,16 +127,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
             if (rc == kStSuccess)
             {
                 if (P.spoa_accurate)
-                {
-                    if (lane == 0 && !topsort_spoa_order<IdT>(g, node_count))
-                        rc = kStGenericError;
-                    rc = __shfl_sync(kFull, rc, 0);
-                }
+                    topsort_spoa_order<IdT>(g, node_count, lane);
                 else if (!topsort_kahn_smem<IdT>(g, node_count, smem, P.smem_per_warp, lane))
-                {
-                    if (lane == 0)
-                        topsort_kahn<IdT>(g, node_count);
-                }
+                    topsort_kahn_warp<IdT>(g, node_count, lane);
             }
             __syncwarp();
             if (rc != kStSuccess) // cudapoa_kernels.cuh:314-319
@@ -153,33 +146,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) poa_window_kernel(cons
         {
             uint8_t* cons_out  = P.consensus + static_cast<int64_t>(w) * P.max_consensus;
             uint16_t* cov_out  = P.coverage + static_cast<int64_t>(w) * P.max_consensus;
-            int32_t rc         = generate_consensus_smem<IdT>(g, node_count, cons_out, cov_out, P.max_consensus, smem,
-                                                              P.smem_per_warp, lane);
-            if (rc < 0) // does not fit the scratch: serial version out of global memory
-            {
-                if (lane == 0)
-                    rc = generate_consensus<IdT>(g, node_count, cons_out, cov_out, P.max_consensus);
-                rc = __shfl_sync(kFull, rc, 0);
-            }
-            status = rc;
+            status = generate_consensus<IdT>(g, node_count, cons_out, cov_out, P.max_consensus, smem, P.smem_per_warp, lane);
         }
         else
         {
-            int32_t msa_len = 0;
-            if (lane == 0)
-            {
-                if (!topsort_spoa_order<IdT>(g, node_count))
-                    status = kStGenericError;
-                else
-                {
-                    msa_len = msa_columns<IdT>(g, node_count);
-                    if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
-                        status = kStSeqSizeExceeded;
-                }
-            }
-            status  = __shfl_sync(kFull, status, 0);
-            msa_len = __shfl_sync(kFull, msa_len, 0);
-            __syncwarp();
+            topsort_spoa_order<IdT>(g, node_count, lane);
+            const int32_t msa_len = msa_columns<IdT>(g, node_count, lane);
+            if (msa_len >= P.max_consensus) // cudapoa_generate_msa.cuh:200-204
+                status = kStSeqSizeExceeded;
             if (status == kStSuccess)
                 msa_rows<IdT>(g, P.bases + wd.base_off, rlen, wd.n_reads,
                               P.msa + static_cast<int64_t>(w) * P.max_reads * P.max_consensus, msa_len,

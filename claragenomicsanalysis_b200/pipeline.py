@@ -10,14 +10,13 @@ from . import _cabi
 from ._cabi import OUTPUT_CONSENSUS, OUTPUT_MSA, BatchSizeC, StatsC
 from .cudapoa import band_mode_value
 
-_configured = False
+_configured = set()
 
 
-def _dll():
-    global _configured
-    lib = _cabi.native()
+def _dll(lib=None):
+    lib = lib or _cabi.native()
     dll = lib._dll
-    if not _configured:
+    if id(dll) not in _configured:
         dll.cudapoa_b200_pipeline_last_error.restype = ctypes.c_char_p
         dll.cudapoa_b200_pipeline_create.restype = ctypes.c_void_p
         dll.cudapoa_b200_pipeline_create.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_size_t,
@@ -41,7 +40,7 @@ def _dll():
         dll.cudapoa_b200_pipeline_total_chars.restype = ctypes.c_int64
         dll.cudapoa_b200_pipeline_digest.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32]
         dll.cudapoa_b200_pipeline_digest.restype = ctypes.c_uint64
-        _configured = True
+        _configured.add(id(dll))
     return dll
 
 
@@ -56,9 +55,9 @@ def shard_bounds(n_items, n_shards, shard):
 class WindowPipeline:
     def __init__(self, max_sequences_per_poa, max_sequence_size, mem_per_worker, devices=(0,), workers_per_device=2,
                  output_type="consensus", gap_score=-8, mismatch_score=-6, match_score=8, cuda_banded_alignment=True,
-                 alignment_band_width=256):
-        self._dll = _dll()
-        lib = _cabi.native()
+                 alignment_band_width=256, lib=None):
+        lib = lib or _cabi.native()
+        self._dll = _dll(lib)
         self._mask = OUTPUT_CONSENSUS if output_type == "consensus" else OUTPUT_MSA
         bs = BatchSizeC()
         lib.check(lib.batch_size_default(ctypes.byref(bs), max_sequence_size, max_sequences_per_poa,

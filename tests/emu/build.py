@@ -1,5 +1,5 @@
 """TEST INFRASTRUCTURE ONLY.  Builds tests/emu/_build/libcudapoa_emu.so: the engine's host and device code
-(csrc/engine.cu, csrc/c_api.cpp) compiled by g++ against the SIMT emulator in tests/emu (no GPU, no nvcc), exposing
+(csrc/engine.cu, csrc/c_api.cpp, csrc/pipeline.cpp) compiled by g++ against the SIMT emulator in tests/emu (no GPU, no nvcc), exposing
 the same C ABI as the product library.  Used by tests/test_emu_parity.py to check kernel logic on the CPU."""
 import os
 import subprocess
@@ -28,7 +28,8 @@ def build(force=False):
         return LIB
     os.makedirs(OUT_DIR, exist_ok=True)
     objs = []
-    for src, lang in (("engine.cu", ["-x", "c++"]), ("c_api.cpp", []), (os.path.join(HERE, "poa_emu.cpp"), [])):
+    for src, lang in (("engine.cu", ["-x", "c++"]), ("c_api.cpp", []), ("pipeline.cpp", []),
+                      (os.path.join(HERE, "poa_emu.cpp"), [])):
         path = src if os.path.isabs(src) else os.path.join(CSRC, src)
         obj = os.path.join(OUT_DIR, os.path.splitext(os.path.basename(src))[0] + ".o")
         cmd = ["g++"] + FLAGS + lang + ["-c", path, "-o", obj]
@@ -37,7 +38,7 @@ def build(force=False):
             sys.stderr.write(res.stdout)
             raise RuntimeError("emulator build failed on " + src)
         objs.append(obj)
-    subprocess.check_call(["g++", "-shared", "-o", LIB] + objs)
+    subprocess.check_call(["g++", "-shared", "-o", LIB] + objs + ["-lpthread"])
     return LIB
 
 

@@ -144,6 +144,13 @@ static inline cudaError_t cudaMemset(void* d, int v, size_t n)
     return cudaSuccess;
 }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+constexpr unsigned cudaStreamNonBlocking = 1u;
+static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned)
+{
+    *s = nullptr; // every launch runs to completion inside the call: streams carry no state
+    return cudaSuccess;
+}
+static inline cudaError_t cudaStreamDestroy(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 static inline cudaError_t cudaEventCreate(cudaEvent_t* e)
 {

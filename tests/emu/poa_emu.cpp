@@ -3,6 +3,7 @@
 #include "poa_emu.hpp"
 
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -251,6 +252,9 @@ static void run_warp(const std::function<void()>& body, unsigned first_thread)
 
 void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()>& body)
 {
+    // one kernel at a time, whatever host thread launches it (the window pipeline's workers): the machine is a singleton
+    static std::mutex launch_mutex;
+    std::lock_guard<std::mutex> lock(launch_mutex);
     Machine& m = machine();
     if (block.x % 32 != 0)
         fail("block size must be a multiple of 32", 0);

@@ -79,3 +79,25 @@ def test_emulated_cfg2_window_matches_reference_golden(emu):
     ws = cases.case_windows("cfg2_banded16_consensus").slice(0, 1)
     n = parity.run_abi(emu, ws, max_mem=1 << 30, **c["engine"])
     assert parity.digests(n, "consensus") == g["digest"][:1]
+
+
+def test_emulated_pipeline_worker_pool(emu):
+    """The window pipeline (csrc/pipeline.cpp: persistent workers, cost-ordered guided chunks) over the emulated engine:
+    mixed window sizes, three workers, two runs on the same pool; results indexed by window and equal to the oracle."""
+    from claragenomicsanalysis_b200.pipeline import WindowPipeline
+
+    emu.set_schedule(0)
+    ws = generate_windows(14, start_index=900, template_length=(60, 240), n_reads_range=(3, 7))
+    eng = dict(max_seq=320, max_reads=8, band=256, banded=True, output="consensus")
+    o = parity.run_oracle(ws, **eng)
+    p = WindowPipeline(8, 320, 1 << 28, devices=(0,), workers_per_device=3, output_type="consensus", lib=emu)
+    try:
+        assert p.workers == 3
+        for chunk in (4, 0):
+            p.run(ws, chunk_windows=chunk)
+            assert p.statuses() == [int(s) for s in o["status"]]
+            for w in range(len(ws)):
+                assert p.consensus(w) == (o["consensus"][w], list(o["coverage"][w])), "window %d" % w
+            assert p.stats()["windows"] == len(ws)
+    finally:
+        p.close()

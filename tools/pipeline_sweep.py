@@ -10,7 +10,7 @@ import bench  # noqa: E402
 from claragenomicsanalysis_b200.pipeline import WindowPipeline  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 37888
-ws, base = bench.make_windows(n, 1024, 0)
+ws, base = bench.make_windows("cfg2", n, 4096, 0)
 for spec in sys.argv[2:]:
     workers, chunk, mem = (int(x) for x in spec.split(","))
     pipe = WindowPipeline(30, 640, mem << 30, devices=(0,), workers_per_device=workers, output_type="consensus",
