@@ -33,6 +33,7 @@ constexpr unsigned kFull = 0xffffffffu;
 // emulated block's shared memory.
 #define POA_DYNAMIC_SMEM(name) uint8_t* name = poa_emu::smem_base()
 #define POA_COUNT(name) poa_emu::count(name)
+#define POA_COUNT_N(name, n) poa_emu::count(name, n)
 template <typename T>
 inline T* emu_shared(uint32_t a, int line)
 {
@@ -77,6 +78,7 @@ inline uint32_t prmt(uint32_t x, uint32_t y, uint32_t s) { return poa_emu_prmt(x
 #else
 #define POA_DYNAMIC_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
 #define POA_COUNT(name)
+#define POA_COUNT_N(name, n)
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -846,9 +848,10 @@ __device__ void topsort_kahn_warp(const Graph<IdT>& g, int32_t node_count, int32
 //   * lane 0 runs the FIFO.  The queue is a 256-entry ring (a POA graph's frontier is a handful of nodes), sorted[] and
 //     node_id_to_pos[] are written as nodes leave it: the walk is a chain of dependent shared-memory accesses, so
 //     the stores ride along for free, and 4 bytes per node is what lets ~48 windows per SM sort at the same time.
-//     A POA graph is mostly chains: the node popped next is usually the one pushed last, whose record the push has
-//     just had in registers -- it is kept there, so a chain step is one shared-memory load (the child's record)
-//     and one store (its decremented in-degree).
+//     A POA graph is mostly chains: when the node in hand has one child and nothing else is queued, the child -- if
+//     this was its last open in-edge -- is the next node and its record is already in a register: such a step is one
+//     shared-memory load and no store.  Otherwise the next queued node and its record are fetched before the
+//     children are visited, so the two dependent loads of a pop hide under the visits.
 // Returns false when the graph does not fit the scratch or the ring is overrun (sorted[] / node_id_to_pos[] may then
 // be partly written); the caller then runs topsort_kahn_warp, which rewrites both.
 constexpr int32_t kKahnBytesPerNode = 4;
@@ -907,8 +910,8 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         uint32_t pushed = static_cast<uint32_t>(tail);
         uint32_t node   = lds_u16(queue);   // a graph always has a source
         uint32_t v      = lds_u32(rec + 4u * node);
-        uint32_t last_node = 0, last_rec = 0, last_at = 0xffffffffu; // the node pushed last, its record and push index
-        IdT* sorted_out = g.sorted;
+        IdT* const sorted_out = g.sorted;
+        IdT* const pos_out    = g.pos;
         // visit(child): one in-edge of child is satisfied; queue it when it was the last one
 #define POA_KAHN_VISIT(child_expr)                                   \
     {                                                                \
@@ -919,34 +922,57 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
         if (left_ < kOne)                                            \
         {                                                            \
             sts_u16(queue + 2u * (pushed & kQMask), child_);         \
-            last_node = child_;                                      \
-            last_rec  = left_;                                       \
-            last_at   = pushed;                                      \
             pushed++;                                                \
         }                                                            \
     }
         for (;;)
         {
-            *sorted_out++ = static_cast<IdT>(node);
-            g.pos[node]   = static_cast<IdT>(head);
-            const uint32_t oc = (v >> 24) & 3u;
-            uint32_t more = 0, e2 = 0;
-            if (oc > 2) // rare: the out-degree and the third child come from global memory, under the first two visits
-            {
-                more = static_cast<uint32_t>(g.out_cnt[node]) - 2u;
-                e2   = static_cast<uint16_t>(g.out_edge(node, 2));
-            }
-            if (oc > 0)
-                POA_KAHN_VISIT(v & 0xfffu)
-            if (oc > 1)
-                POA_KAHN_VISIT((v >> 12) & 0xfffu)
-            if (oc > 2)
-            {
-                POA_KAHN_VISIT(e2)
-                for (uint32_t e = 1; e < more; e++)
-                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(2u + e))))
-            }
+            sorted_out[head] = static_cast<IdT>(node);
+            pos_out[node]    = static_cast<IdT>(head);
             head++;
+            const uint32_t oc = (v >> 24) & 3u;
+            if (oc == 1 && head == pushed)
+            {
+                // a chain step with nothing else waiting (most of a POA graph): if the only child becomes ready it is
+                // the next node, and its record is in hand -- no queue traffic, nothing stored
+                const uint32_t child = v & 0xfffu;
+                const uint32_t at    = rec + 4u * child;
+                const uint32_t left  = lds_u32(at) - kOne;
+                if (left < kOne)
+                {
+                    pushed++;
+                    node = child;
+                    v    = left;
+                    continue;
+                }
+                sts_u32(at, left);
+                break; // the queue is empty and nothing became ready: every node is out
+            }
+            // the next queued node and its record are fetched under the visits (a queued node's record is final)
+            const bool have_next = head < pushed;
+            uint32_t next_node = 0, next_v = 0;
+            if (have_next)
+            {
+                next_node = lds_u16(queue + 2u * (head & kQMask));
+                next_v    = lds_u32(rec + 4u * next_node);
+            }
+            if (oc > 2) // rare: the out-degree and the further children come from global memory
+            {
+                const uint32_t more = static_cast<uint32_t>(g.out_cnt[node]);
+                const uint32_t e2   = static_cast<uint16_t>(g.out_edge(node, 2));
+                POA_KAHN_VISIT(v & 0xfffu)
+                POA_KAHN_VISIT((v >> 12) & 0xfffu)
+                POA_KAHN_VISIT(e2)
+                for (uint32_t e = 3; e < more; e++)
+                    POA_KAHN_VISIT(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(e))))
+            }
+            else
+            {
+                if (oc > 0)
+                    POA_KAHN_VISIT(v & 0xfffu)
+                if (oc > 1)
+                    POA_KAHN_VISIT((v >> 12) & 0xfffu)
+            }
             if (head == pushed)
                 break;
             if (pushed - head > kKahnQueueEntries) // the ring was overrun: give up, the caller sorts again
@@ -954,10 +980,10 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
                 ok = 0;
                 break;
             }
-            if (last_at == head)
+            if (have_next)
             {
-                node = last_node;
-                v    = last_rec;
+                node = next_node;
+                v    = next_v;
             }
             else
             {

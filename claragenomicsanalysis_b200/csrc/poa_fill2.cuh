@@ -259,11 +259,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             __syncwarp();
             nrec = records[min(r + 32 + lane, node_count)];
         }
-        uint4 rec = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
-        if (debug_flags & 8)
-            rec = records[r];
-        if (debug_flags & 4)
-            rec.z &= ~kRecChain;
+        const uint4 rec = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
         const int32_t bs = static_cast<int32_t>(rec.w & 0xffffu);
         const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
 

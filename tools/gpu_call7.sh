@@ -1,0 +1,25 @@
+#!/bin/bash
+# GPU call: GPU test suite, bench (full line), end-to-end sweep of the window pipeline, ncu launch list.
+cd "$(dirname "$0")/.."
+TAG=${1:-c7}
+B="python bench.py --no-cpu-baseline --no-other-configs"
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest.log
+tail -4 gpurun_out/${TAG}_pytest.log
+timeout 900 python bench.py --steps 5 --warmup 3 ${BENCH_FLAGS:-} > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
+python - <<PY
+import json
+try:
+    d=json.loads(open("gpurun_out/${TAG}_bench.json").read().strip().splitlines()[-1])
+    g=d["kernels"]["graph_kernels"]
+    print("BENCH value %.0f e2e %.0f ms %.1f fill %.1f graph %.1f (trace %.1f fuse %.1f sort %.1f final %.1f) frac %.4f" % (d["value"], d["e2e"]["value"], d["ms_per_step"], d["kernels"]["poa_fill_kernel"]["ms_per_step"], g["ms_per_step"], g["poa_trace_kernel_ms"], g["poa_fuse_kernel_ms"], g["poa_sort_kernel_ms"], g["poa_final_kernel_ms"], d["roofline"]["frac"]))
+    for k,v in (d.get("configs") or {}).items(): print(k, "value %.0f e2e %.0f ms %.1f" % (v["value"], v["e2e"], v["ms_per_step"]), v.get("phase_ms_per_step"))
+except Exception as e:
+    print("bench parse failed", e); print(open("gpurun_out/${TAG}_bench.err").read()[-2000:])
+PY
+timeout 900 python tools/pipeline_sweep.py 18944 8,1184,6 8,2368,8 4,2368,8 4,4736,14 12,1184,5 16,592,4 6,1600,8 > gpurun_out/${TAG}_sweep.log 2>&1
+cat gpurun_out/${TAG}_sweep.log | tail -9
+timeout 600 $B --steps 1 --warmup 0 > gpurun_out/${TAG}_plain.log 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum --clock-control none -c 900 --csv --log-file gpurun_out/${TAG}_launches.csv $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_launches.log 2>&1
+ls -la gpurun_out | tail -8
