@@ -575,7 +575,7 @@ struct PhaseScratch
 {
     int32_t fill, trace, sort_small, sort_large, final_;
 };
-constexpr int32_t kCountersPerStep = 8;
+constexpr int32_t kCountersPerStep = 9;
 
 template <typename ScoreT, typename IdT, bool MSA>
 static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScratch& scratch,
@@ -612,6 +612,13 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
         P.next_window   = c + 3;
         P.smem_per_warp = scratch.trace;
         launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream);
+        if (P.adaptive_max_band > 0)
+        {
+            P.next_window   = c + 8;
+            P.smem_per_warp = 0;
+            launch_phase(poa_widen_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
+            launches++;
+        }
         if (timeline)
             timeline->mark(stream, 1);
         P.next_window   = c + 4;
@@ -651,7 +658,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
 }
 
 // Phase-split schedule (poa_phases.cuh) for banded batches: two launches per read instead of one launch per batch.
-// Returns false when the batch has to take the single launch (full alignment, adaptive banding, very deep windows,
+// Returns false when the batch has to take the single launch (full alignment, 32-bit node ids, very deep windows,
 // or CUDAPOA_B200_SCHEDULE=fused).
 bool B200Batch::launch_split(KernelParams& P)
 {
@@ -660,7 +667,7 @@ bool B200Batch::launch_split(KernelParams& P)
         return env != nullptr && std::strcmp(env, "fused") == 0;
     }();
     const int32_t mode = g_schedule_override.load();
-    if (!banded_ || adaptive_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
+    if (!banded_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
         return false;
     // A lone batch that does not fill the device about twice over is latency-bound either way, and then one launch
     // (no per-launch tails) is ~10 % faster; measured crossover on a B200 between 4 736 and 9 472 cfg 2 windows
@@ -678,14 +685,14 @@ bool B200Batch::launch_split(KernelParams& P)
     for (int32_t i = 0; i < poa_count_; i++)
         ends_at[static_cast<size_t>(std::min(std::max(windows_h_[i].n_reads - 1, 1), steps))] = 1;
     // shared memory per window and launch: the fill needs the row ring, the record buffer and the profile; the
-    // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 024 nodes,
+    // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 536 nodes -- all but the outliers of a 500-base polishing window,
     // large class: the single launch's scratch); the consensus its staging area and 6 bytes per node
     const int32_t L = std::max(batch_size_.max_sequence_size, 1);
     PhaseScratch scratch{};
     scratch.fill       = (fill2_smem_bytes(L) + 255) & ~255;
     scratch.trace      = (trace2_smem_bytes(L) + 255) & ~255;
     scratch.sort_large = kSmemPerWarp;
-    scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, 1024) + 2 * kKahnQueueEntries + 255) & ~255);
+    scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, 1536) + 2 * kKahnQueueEntries + 255) & ~255);
     if (kahn_smem_nodes(scratch.sort_small) >= plan_.M)
         scratch.sort_large = scratch.sort_small; // one class serves every graph of this batch
     scratch.final_ = kSmemPerWarp;

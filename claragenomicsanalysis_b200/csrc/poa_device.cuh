@@ -33,6 +33,7 @@ constexpr unsigned kFull = 0xffffffffu;
 // emulated block's shared memory.
 #define POA_DYNAMIC_SMEM(name) uint8_t* name = poa_emu::smem_base()
 #define POA_COUNT(name) poa_emu::count(name)
+#define POA_NOINLINE __attribute__((noinline))
 #define POA_COUNT_N(name, n) poa_emu::count(name, n)
 template <typename T>
 inline T* emu_shared(uint32_t a, int line)
@@ -79,6 +80,7 @@ inline uint32_t prmt(uint32_t x, uint32_t y, uint32_t s) { return poa_emu_prmt(x
 #define POA_DYNAMIC_SMEM(name) extern __shared__ __align__(16) uint8_t name[]
 #define POA_COUNT(name)
 #define POA_COUNT_N(name, n)
+#define POA_NOINLINE __noinline__
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -69,8 +69,8 @@ __device__ __forceinline__ int32_t record_pred_row(const Graph<IdT>& g, uint32_t
 template <typename IdT, bool REBASED>
 __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                               uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
-                              int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t beta_arg,
-                              int32_t debug_flags = 0)
+                              int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t& start_score,
+                              int32_t beta_arg)
 {
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
@@ -593,14 +593,16 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         // the start cell must be a real score (the walk compares nothing, but the exact path decides sentinel rows)
         if (!REBASED && best <= kNegThreshold)
             return kFastNotTaken;
-        start_row = best_row;
+        start_row   = best_row;
+        start_score = best + gap * read_len; // un-tilted: the alignment's score
     }
     else
     {
         // no sink row: the reference starts from row 0, whose cell at column read_len is inside its band up to column band
         if (read_len > kFastBand)
             return kFastNotTaken;
-        start_row = 0;
+        start_row   = 0;
+        start_score = gap * read_len;
     }
     return 0;
 }

@@ -27,7 +27,7 @@ struct WindowDesc
     int32_t read_off;     // first read of the window in read_len[]
     int32_t n_reads;      // reads accepted into the window
     int32_t scores_width; // full alignment: row stride of this window's score matrix
-    int32_t reserved;
+    int32_t aln_score;  // score of the pending alignment (adaptive banding decides on it)
 };
 
 // Byte offsets of the per-window arrays inside the window's arena slice.
@@ -68,7 +68,7 @@ struct PhaseState
     unsigned long long cells;
     int64_t seq_off;    // offset of the current read's first base from the window's first base
     int32_t beta;       // row-offset slope of the packed fill that produced the pending alignment (0: none)
-    int32_t reserved;
+    int32_t aln_score;  // score of the pending alignment (adaptive banding decides on it)
 };
 constexpr int32_t kAlnPendingTraceback = -3;
 constexpr int32_t kAlnNeedsExact       = -4;  // the packed fill declined: poa_exact_kernel aligns this read

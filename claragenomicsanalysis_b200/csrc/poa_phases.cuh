@@ -94,6 +94,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
                 int32_t aln_len     = kFastNotTaken;
                 int32_t start_row   = 0;
+                int32_t start_score = 0;
                 // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
                 // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
                 // registers and instruction cache of this one belong to the loop the benchmark spends half its time in.
@@ -105,12 +106,13 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 else if (beta == 0 &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                                P.gap, P.mismatch, P.match, smem, lane, start_row, 0, P.debug_flags) == 0)
+                                                P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
                 st.aln_len   = aln_len;
                 st.start_row = start_row;
+                st.aln_score = start_score;
                 st.beta      = 0;
                 st.rows += static_cast<uint32_t>(st.node_count);
                 st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(P.band);
@@ -153,13 +155,15 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
         const uint8_t* seq  = P.bases + wd.base_off + st.seq_off;
         ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
         int32_t start_row   = 0;
+        int32_t start_score = 0;
         const int32_t beta  = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
         if (beta > 0 && fill2_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                               P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                              P.gap, P.mismatch, P.match, smem, lane, start_row, beta, P.debug_flags) == 0)
+                                              P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, beta) == 0)
         {
             st.aln_len   = kAlnPendingTraceback;
             st.start_row = start_row;
+            st.aln_score = start_score;
             st.beta      = beta;
         }
         else
@@ -203,6 +207,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
         int32_t aln_score   = 0;
         st.aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, rlen[s], scores, P.band + kBandRowPad, P.band,
                                                     P.gap, P.mismatch, P.match, lane, &aln_score);
+        st.aln_score = aln_score;
         st.exact++;
         if (lane == 0)
             *ps = st;
@@ -257,6 +262,61 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_TRACE_MIN_BLOCKS
         if (lane == 0)
             ps->aln_len = aln_len;
         __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// Adaptive banding (extension, no counterpart in the reference; the rule is poa_window.cuh's): after the traceback of a
+// step, an alignment that scores below 3/4 of a perfect match or that runs within kAdaptiveBandMargin cells of a band
+// edge is repeated with the band doubled, while that raises the score or the path still hugs an edge, up to
+// P.adaptive_max_band.  The first alignment comes from the packed fill like every other; repeats (rare on ordinary
+// windows) use the exact-arithmetic alignment, whose band is a parameter.  Launched only for adaptive batches.
+template <typename ScoreT, typename IdT>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_widen_kernel(const KernelParams P)
+{
+    int32_t lane = threadIdx.x & 31;
+    asm volatile("" : "+r"(lane));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        PhaseState st  = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        const WindowDesc wd = P.windows[w];
+        if (st.status != kStSuccess || st.finalized || s >= wd.n_reads || st.aln_len < 0)
+            continue;
+        const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t len  = P.read_len[wd.read_off + s];
+        const uint8_t* seq = P.bases + wd.base_off + st.seq_off;
+        ScoreT* scores     = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
+        int32_t band_now   = P.band;
+        int32_t aln_len    = st.aln_len;
+        int32_t aln_score  = st.aln_score;
+        bool again = 4 * aln_score < 3 * P.match * len || alignment_touches_band<IdT>(g, st.node_count, len, band_now, lane);
+        if (!again)
+            continue;
+        while (again && band_now < P.adaptive_max_band)
+        {
+            band_now *= 2;
+            const int32_t before = aln_score;
+            __syncwarp();
+            aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, len, scores, band_now + kBandRowPad, band_now,
+                                                     P.gap, P.mismatch, P.match, lane, &aln_score);
+            st.exact += 0x10000u; // high half: widened alignments
+            st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(band_now);
+            again = aln_len >= 0 &&
+                    (aln_score > before || alignment_touches_band<IdT>(g, st.node_count, len, band_now, lane));
+        }
+        st.aln_len   = aln_len;
+        st.aln_score = aln_score;
+        if (lane == 0)
+            *ps = st;
+        __syncwarp();
     }
 }
 

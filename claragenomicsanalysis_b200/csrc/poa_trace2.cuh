@@ -12,6 +12,8 @@
 
 #include "poa_fill2.cuh"
 
+#include <type_traits>
+
 namespace poa_b200
 {
 
@@ -28,6 +30,14 @@ __host__ __device__ inline int32_t trace2_smem_bytes(int32_t read_len)
     return kT2Bytes + ((2 * read_len + 15) & ~15);
 }
 
+// Code of cell `cell` of a row that stores a byte per cell (more than kWidePreds predecessors).  Out of line on purpose:
+// the walk's loop should not carry the address arithmetic of a load it almost never issues.
+__device__ POA_NOINLINE uint32_t wide_row_code(const uint8_t* codes, int32_t row, int32_t cell)
+{
+    POA_COUNT("trace2.wide_steps");
+    return __ldcg(codes + static_cast<int64_t>(row) * kCodeRowBytes + cell);
+}
+
 // Returns the alignment length (> 0), or -1 if a code is not a move (cannot happen for codes the fill wrote; kept as the
 // reference's loop-count guard).  All 32 lanes.  `smem_bytes` of scratch at `tile`.
 template <typename IdT>
@@ -39,14 +49,6 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
     const uint32_t tile_desc = tile + kT2TileBytes;
     const uint32_t rows_s    = tile + kT2Bytes;                        // u16[read_len]: row paired with each base
     const bool in_smem       = smem_bytes >= trace2_smem_bytes(read_len);
-    // record(k, row): read position k pairs with `row` (0: inserted base)
-    auto record = [&](int32_t k, int32_t row) {
-        if (in_smem)
-            sts_u16(rows_s + 2u * static_cast<uint32_t>(k), static_cast<uint32_t>(row));
-        else
-            g.aln_node[k] = static_cast<IdT>(row);
-    };
-
     int32_t i = start_row, j = read_len;
     int32_t steps = 0;
     bool broken   = false;
@@ -102,46 +104,56 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
             // (32-bit arithmetic; it may wrap)
             const uint32_t desc_base = tile_desc - 16u * static_cast<uint32_t>(tile_r0);
             const uint32_t code_base = tile - static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(tile_r0);
-            while (i >= row_floor && j >= tile_c0 && j > 0)
-            {
-                // descriptor and code word are fetched together: one shared-memory latency per step
-                const int32_t x     = j - tile_c0; // 0 .. 63
-                const uint4 dd      = lds_v4(desc_base + 16u * static_cast<uint32_t>(i));
-                const uint32_t cw   = lds_u32(code_base + static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(i) +
-                                            static_cast<uint32_t>((x >> 3) << 2));
-                const int32_t pc    = static_cast<int32_t>((dd.z >> 16) & 0x3fu);
-                uint32_t code       = (cw >> ((x & 7) * 4)) & 0xfu;
-                if (pc > kWidePreds)
+            // the walk proper, instantiated for both homes of the recorded rows so that the choice costs nothing per step
+            auto walk = [&](auto rows_in_smem) {
+                while (i >= row_floor && j >= tile_c0 && j > 0)
                 {
-                    POA_COUNT("trace2.wide_steps");
-                    const int32_t b = static_cast<int32_t>(dd.w & 0xffffu);
-                    code            = __ldcg(codes + static_cast<int64_t>(i) * kCodeRowBytes + (j - b - 1));
-                }
-                steps++;
-                if (code & 2u)
-                {
-                    record(j - 1, 0); // horizontal: an inserted base
-                    j--;
-                    continue;
-                }
-                const int32_t p = static_cast<int32_t>(code >> 2);
-                int32_t pi      = static_cast<int32_t>(dd.x & 0xffffu);
-                if (p != 0)
-                {
-                    if (p >= pc)
+                    // descriptor and code word are fetched together: one shared-memory latency per step
+                    const int32_t x   = j - tile_c0; // 0 .. 63
+                    const uint4 dd    = lds_v4(desc_base + 16u * static_cast<uint32_t>(i));
+                    const uint32_t cw = lds_u32(code_base + static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(i) +
+                                                static_cast<uint32_t>((x >> 3) << 2));
+                    const int32_t pc  = static_cast<int32_t>((dd.z >> 16) & 0x3fu);
+                    uint32_t code     = (cw >> ((x & 7) * 4)) & 0xfu;
+                    if (pc > kWidePreds) // rare: such rows keep a byte per cell in global memory
+                        code = wide_row_code(codes, i, j - static_cast<int32_t>(dd.w & 0xffffu) - 1);
+                    steps++;
+                    const uint32_t at = rows_s + 2u * static_cast<uint32_t>(j - 1); // where read position j - 1 is recorded
+                    if (code & 2u) // horizontal: an inserted base
                     {
-                        broken = true; // not a code the fill writes
-                        break;
+                        if (rows_in_smem.value)
+                            sts_u16(at, 0u);
+                        else
+                            g.aln_node[j - 1] = 0;
+                        j--;
+                        continue;
                     }
-                    pi = record_pred_row<IdT>(g, dd.x, dd.y, i, p);
+                    const int32_t p = static_cast<int32_t>(code >> 2);
+                    int32_t pi      = static_cast<int32_t>(dd.x & 0xffffu);
+                    if (p != 0)
+                    {
+                        if (p >= pc)
+                        {
+                            broken = true; // not a code the fill writes
+                            break;
+                        }
+                        pi = record_pred_row<IdT>(g, dd.x, dd.y, i, p);
+                    }
+                    if ((code & 1u) == 0u) // diagonal: the base pairs with this row's node
+                    {
+                        if (rows_in_smem.value)
+                            sts_u16(at, static_cast<uint32_t>(i));
+                        else
+                            g.aln_node[j - 1] = static_cast<IdT>(i);
+                        j--;
+                    }
+                    i = pi;
                 }
-                if ((code & 1u) == 0u)
-                {
-                    record(j - 1, i); // diagonal: the base pairs with this row's node
-                    j--;
-                }
-                i = pi;
-            }
+            };
+            if (in_smem)
+                walk(std::true_type{});
+            else
+                walk(std::false_type{});
         }
         i      = __shfl_sync(kFull, i, 0);
         j      = __shfl_sync(kFull, j, 0);

@@ -47,8 +47,39 @@ def test_oracle_adaptive_leaves_ordinary_windows_alone():
     assert r.widened <= len(ws)  # a handful of low-scoring reads may be re-aligned; the result is the same
 
 
+@pytest.fixture
+def schedule(native_lib):
+    """Process-wide schedule override (1: single launch, 2: one launch per phase and read) for one test."""
+    def set_mode(mode):
+        native_lib._dll.cudapoa_b200_debug_set_schedule(int(mode))
+    yield set_mode
+    native_lib._dll.cudapoa_b200_debug_set_schedule(0)
+
+
 @pytest.mark.gpu
-def test_engine_adaptive_matches_oracle_and_full_alignment(native_lib):
+@pytest.mark.parametrize("mode,band", [(1, 128), (2, 128), (1, 256), (2, 256)])
+def test_engine_adaptive_matches_oracle_and_full_alignment(native_lib, schedule, mode, band):
+    """Both device schedules: the single launch re-aligns inside the window's loop, the phase-split schedule in
+    poa_widen_kernel after the packed fill + traceback of the step (band 256) or the exact alignment (band 128)."""
+    schedule(mode)
+    ws = cases.structural_windows(12)
+    got = parity.run_abi(native_lib, ws, band=band, banded="adaptive", **KW)
+    r, want = _oracle_adaptive(ws, band, **KW)
+    assert got["status"] == r.statuses()
+    assert got["consensus"] == [w[0] for w in want]
+    assert [list(c) for c in got["coverage"]] == [list(w[1]) for w in want]
+    assert sum(s["widened"] for s in got["stats"]) == r.widened > 0
+    if band != 128:
+        return
+    full = parity.run_abi(native_lib, ws, banded=False, **KW)
+    static = parity.run_abi(native_lib, ws, band=128, banded=True, **KW)
+    agree_static = sum(a == b for a, b in zip(static["consensus"], full["consensus"]))
+    agree_adaptive = sum(a == b for a, b in zip(got["consensus"], full["consensus"]))
+    assert agree_adaptive >= agree_static and agree_adaptive >= len(ws) - 1
+
+
+@pytest.mark.gpu
+def test_engine_adaptive_default_schedule(native_lib):
     ws = cases.structural_windows(12)
     got = parity.run_abi(native_lib, ws, band=128, banded="adaptive", **KW)
     r, want = _oracle_adaptive(ws, 128, **KW)
@@ -64,7 +95,9 @@ def test_engine_adaptive_matches_oracle_and_full_alignment(native_lib):
 
 
 @pytest.mark.gpu
-def test_engine_adaptive_on_ordinary_windows(native_lib):
+@pytest.mark.parametrize("mode", [1, 2])
+def test_engine_adaptive_on_ordinary_windows(native_lib, schedule, mode):
+    schedule(mode)
     ws = cases.case_windows("cfg2_banded16_consensus")
     got = parity.run_abi(native_lib, ws, 640, 30, banded="adaptive")
     static = parity.run_abi(native_lib, ws, 640, 30, banded=True)
