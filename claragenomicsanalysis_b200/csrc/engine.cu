@@ -465,19 +465,19 @@ StatusType B200Batch::add_poa_group(std::vector<StatusType>& per_seq_status, con
     return StatusType::success;
 }
 
+static int32_t phase_blocks_per_sm(const void* kernel, int32_t threads, size_t smem);
+
 template <typename ScoreT, typename IdT, bool BANDED, bool MSA>
 static void launch_one(const KernelParams& P, int32_t sm_count, cudaStream_t stream)
 {
     const dim3 block(kWarpsPerBlock * 32);
     const size_t smem = static_cast<size_t>(kWarpsPerBlock) * static_cast<size_t>(P.smem_per_warp);
     auto kernel       = poa_window_kernel<ScoreT, IdT, BANDED, MSA>;
-    // per device and cheap; batches on several devices share this code
-    GW_CU_CHECK_ERR(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    // persistent warps: at most one resident wave of CTAs, windows are pulled from P.next_window
+    // persistent warps: at most one resident wave of CTAs, windows are pulled from P.next_window.  The function
+    // attribute and the occupancy query are paid once per kernel and device (phase_blocks_per_sm).
     const int32_t needed = (P.n_windows + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    int per_sm           = 1;
-    GW_CU_CHECK_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, static_cast<int>(block.x), smem));
-    const dim3 grid(std::max(1, std::min(needed, sm_count * std::max(per_sm, 1))));
+    const int32_t per_sm = phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem);
+    const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
     POA_LAUNCH(kernel, grid, block, smem, stream, P);
 }
 
@@ -989,46 +989,67 @@ void B200Batch::get_graphs(std::vector<DirectedGraph>& graphs, std::vector<Statu
     if (launched_)
         sync_and_collect();
     const ArenaLayout& L = plan_.layout;
-    const int32_t idb    = plan_.size32 ? 4 : 2;
+    const size_t idb     = plan_.size32 ? 4 : 2;
+    const size_t M       = static_cast<size_t>(L.M);
+    // Groups of windows, four strided copies per group (cudaMemcpy2DAsync, pitch = a window's arena) and two waits:
+    // bases + in-degrees first, then the in-edge and weight planes up to the group's largest in-degree (slot-major
+    // planes: the first k planes of a window are contiguous).  The host staging stays below ~256 MB.
+    const size_t per_window_guess = M * (3 + 4 * (idb + 2));
+    const int32_t group = static_cast<int32_t>(std::max<size_t>(1, std::min<size_t>(poa_count_, (size_t(256) << 20) / per_window_guess)));
     std::vector<uint8_t> nodes, in_cnt, in_edge, in_w;
-    for (int32_t poa = 0; poa < poa_count_; poa++)
+    for (int32_t first = 0; first < poa_count_; first += group)
     {
-        push_status(output_status, poa);
-        if (status_h_[poa] != 0)
-            continue;
-        const int32_t n      = node_count_h_[poa];
-        const uint8_t* arena = arena_d_ + static_cast<int64_t>(poa) * L.stride;
-        nodes.resize(n);
-        in_cnt.resize(static_cast<size_t>(n) * 2);
-        GW_CU_CHECK_ERR(cudaMemcpy(nodes.data(), arena + L.nodes, n, cudaMemcpyDeviceToHost));
-        GW_CU_CHECK_ERR(cudaMemcpy(in_cnt.data(), arena + L.in_cnt, static_cast<size_t>(n) * 2, cudaMemcpyDeviceToHost));
-        const uint16_t* cnt = reinterpret_cast<const uint16_t*>(in_cnt.data());
-        int32_t max_slots   = 0;
-        for (int32_t i = 0; i < n; i++)
-            max_slots = std::max<int32_t>(max_slots, cnt[i]);
-        // slot-major planes: copy the first max_slots planes (n entries of each)
-        in_edge.resize(static_cast<size_t>(max_slots) * n * idb);
-        in_w.resize(static_cast<size_t>(max_slots) * n * 2);
+        const int32_t count  = std::min(group, poa_count_ - first);
+        const uint8_t* arena = arena_d_ + static_cast<int64_t>(first) * L.stride;
+        nodes.resize(static_cast<size_t>(count) * M);
+        in_cnt.resize(static_cast<size_t>(count) * M * 2);
+        GW_CU_CHECK_ERR(cudaMemcpy2DAsync(nodes.data(), M, arena + L.nodes, static_cast<size_t>(L.stride), M, count,
+                                          cudaMemcpyDeviceToHost, stream_));
+        GW_CU_CHECK_ERR(cudaMemcpy2DAsync(in_cnt.data(), M * 2, arena + L.in_cnt, static_cast<size_t>(L.stride), M * 2, count,
+                                          cudaMemcpyDeviceToHost, stream_));
+        GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
+        size_t max_slots = 0;
+        for (int32_t k = 0; k < count; k++)
+        {
+            if (status_h_[first + k] != 0)
+                continue;
+            const uint16_t* cnt = reinterpret_cast<const uint16_t*>(in_cnt.data()) + static_cast<size_t>(k) * M;
+            for (int32_t i = 0; i < node_count_h_[first + k]; i++)
+                max_slots = std::max<size_t>(max_slots, cnt[i]);
+        }
+        in_edge.resize(static_cast<size_t>(count) * max_slots * M * idb);
+        in_w.resize(static_cast<size_t>(count) * max_slots * M * 2);
         if (max_slots > 0)
         {
-            GW_CU_CHECK_ERR(cudaMemcpy2D(in_edge.data(), static_cast<size_t>(n) * idb, arena + L.in_edges,
-                                         static_cast<size_t>(L.M) * idb, static_cast<size_t>(n) * idb, max_slots,
-                                         cudaMemcpyDeviceToHost));
-            GW_CU_CHECK_ERR(cudaMemcpy2D(in_w.data(), static_cast<size_t>(n) * 2, arena + L.in_w,
-                                         static_cast<size_t>(L.M) * 2, static_cast<size_t>(n) * 2, max_slots,
-                                         cudaMemcpyDeviceToHost));
+            GW_CU_CHECK_ERR(cudaMemcpy2DAsync(in_edge.data(), max_slots * M * idb, arena + L.in_edges,
+                                              static_cast<size_t>(L.stride), max_slots * M * idb, count,
+                                              cudaMemcpyDeviceToHost, stream_));
+            GW_CU_CHECK_ERR(cudaMemcpy2DAsync(in_w.data(), max_slots * M * 2, arena + L.in_w, static_cast<size_t>(L.stride),
+                                              max_slots * M * 2, count, cudaMemcpyDeviceToHost, stream_));
+            GW_CU_CHECK_ERR(cudaStreamSynchronize(stream_));
         }
-        DirectedGraph& graph = graphs[poa];
-        for (int32_t sink = 0; sink < n; sink++)
+        for (int32_t k = 0; k < count; k++)
         {
-            graph.set_node_label(sink, std::string(1, static_cast<char>(nodes[sink])));
-            for (int32_t e = 0; e < cnt[sink]; e++)
+            const int32_t poa = first + k;
+            push_status(output_status, poa);
+            if (status_h_[poa] != 0)
+                continue;
+            const int32_t n      = node_count_h_[poa];
+            const uint8_t* base  = nodes.data() + static_cast<size_t>(k) * M;
+            const uint16_t* cnt  = reinterpret_cast<const uint16_t*>(in_cnt.data()) + static_cast<size_t>(k) * M;
+            const uint8_t* edges = in_edge.data() + static_cast<size_t>(k) * max_slots * M * idb;
+            const uint16_t* wts  = reinterpret_cast<const uint16_t*>(in_w.data()) + static_cast<size_t>(k) * max_slots * M;
+            DirectedGraph& graph = graphs[poa];
+            for (int32_t sink = 0; sink < n; sink++)
             {
-                const size_t at = static_cast<size_t>(e) * n + sink;
-                const int32_t src = (idb == 2) ? reinterpret_cast<const int16_t*>(in_edge.data())[at]
-                                               : reinterpret_cast<const int32_t*>(in_edge.data())[at];
-                const int32_t w = reinterpret_cast<const uint16_t*>(in_w.data())[at];
-                graph.add_edge(src, sink, w);
+                graph.set_node_label(sink, std::string(1, static_cast<char>(base[sink])));
+                for (int32_t e = 0; e < cnt[sink]; e++)
+                {
+                    const size_t at   = static_cast<size_t>(e) * M + static_cast<size_t>(sink);
+                    const int32_t src = (idb == 2) ? reinterpret_cast<const int16_t*>(edges)[at]
+                                                   : reinterpret_cast<const int32_t*>(edges)[at];
+                    graph.add_edge(src, sink, wts[at]);
+                }
             }
         }
     }

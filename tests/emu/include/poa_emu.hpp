@@ -133,6 +133,11 @@ static inline cudaError_t cudaMemcpy2D(void* d, size_t dpitch, const void* s, si
         std::memcpy(static_cast<char*>(d) + r * dpitch, static_cast<const char*>(s) + r * spitch, width);
     return cudaSuccess;
 }
+static inline cudaError_t cudaMemcpy2DAsync(void* d, size_t dpitch, const void* s, size_t spitch, size_t width,
+                                            size_t height, cudaMemcpyKind kind, cudaStream_t = nullptr)
+{
+    return cudaMemcpy2D(d, dpitch, s, spitch, width, height, kind);
+}
 static inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t = nullptr)
 {
     std::memset(d, v, n);
