@@ -526,13 +526,22 @@ static int32_t phase_blocks_per_sm(const void* kernel, int32_t threads, size_t s
     return std::max(per_sm, 1);
 }
 
+// Development switch: CUDAPOA_B200_BLOCKS_<FILL|TRACE|FUSE|SORT|FINAL>=n caps the resident blocks per SM of a phase
+// (the walks of the graph phases run faster below their maximum occupancy; the defaults below were measured).
+static int32_t blocks_cap_from_env(const char* name, int32_t fallback)
+{
+    const char* v = std::getenv(name);
+    const int32_t n = v ? std::atoi(v) : 0;
+    return n > 0 ? n : fallback;
+}
+
 template <typename Kernel>
 static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per_block, int32_t sm_count,
-                         cudaStream_t stream)
+                         cudaStream_t stream, int32_t blocks_cap = INT32_MAX)
 {
     const dim3 block(warps_per_block * 32);
     const size_t smem    = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
-    const int32_t per_sm = phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem);
+    const int32_t per_sm = std::min(blocks_cap, phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem));
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
     const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
     POA_LAUNCH(kernel, grid, block, smem, stream, P);
@@ -573,7 +582,7 @@ struct PhaseTimeline
 // Scratch sizes of the launches of one step (bytes per warp == per window).
 struct PhaseScratch
 {
-    int32_t fill, trace, sort_small, sort_large, final_;
+    int32_t fill, fill_long, trace, sort_small, sort_large, final_;
 };
 constexpr int32_t kCountersPerStep = 9;
 
@@ -585,6 +594,10 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
     int32_t launches = 0;
     if (timeline)
         timeline->mark(stream, -1);
+    static const int32_t cap_fill  = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_FILL", INT32_MAX);
+    static const int32_t cap_trace = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_TRACE", 6);
+    static const int32_t cap_fuse  = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_FUSE", INT32_MAX);
+    static const int32_t cap_sort  = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_SORT", INT32_MAX);
     const bool two = scratch.sort_large > scratch.sort_small;
     P.class_cap    = two ? kahn_smem_nodes(scratch.sort_small) : INT32_MAX;
     P.lean_class0  = two ? 1 : 0;
@@ -600,8 +613,9 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
         P.step          = s;
         P.next_window   = c + 0;
         P.smem_per_warp = scratch.fill;
-        launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        P.next_window = c + 1;
+        launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
+        P.next_window   = c + 1;
+        P.smem_per_warp = scratch.fill_long;
         launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
         P.next_window   = c + 2;
         P.smem_per_warp = 0;
@@ -611,7 +625,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
             timeline->mark(stream, 0);
         P.next_window   = c + 3;
         P.smem_per_warp = scratch.trace;
-        launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream);
+        launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
         if (P.adaptive_max_band > 0)
         {
             P.next_window   = c + 8;
@@ -623,16 +637,16 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
             timeline->mark(stream, 1);
         P.next_window   = c + 4;
         P.smem_per_warp = 0;
-        launch_phase(poa_fuse_kernel<IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream);
+        launch_phase(poa_fuse_kernel<IdT, MSA>, P, kGraphWarpsPerBlock, sm_count, stream, cap_fuse);
         if (timeline)
             timeline->mark(stream, 2);
         P.next_window   = c + 5;
         P.smem_per_warp = scratch.sort_small;
         P.phase_class   = 0;
         if (two)
-            launch_phase(poa_sort_kernel<IdT, true>, P, kGraphWarpsPerBlock, sm_count, stream);
+            launch_phase(poa_sort_kernel<IdT, true>, P, kGraphWarpsPerBlock, sm_count, stream, cap_sort);
         else
-            launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream);
+            launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream, cap_sort);
         launches += 3;
         if (two)
         {
@@ -685,18 +699,26 @@ bool B200Batch::launch_split(KernelParams& P)
     for (int32_t i = 0; i < poa_count_; i++)
         ends_at[static_cast<size_t>(std::min(std::max(windows_h_[i].n_reads - 1, 1), steps))] = 1;
     // shared memory per window and launch: the fill needs the row ring, the record buffer and the profile; the
-    // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 536 nodes -- all but the outliers of a 500-base polishing window,
+    // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 264 nodes -- a 500-base polishing window ends at 1 130 +- 25,
     // large class: the single launch's scratch); the consensus its staging area and 6 bytes per node
     const int32_t L = std::max(batch_size_.max_sequence_size, 1);
     PhaseScratch scratch{};
-    scratch.fill       = (fill2_smem_bytes(L) + 255) & ~255;
-    scratch.trace      = (trace2_smem_bytes(L) + 255) & ~255;
+    // (the packed fill keeps the whole profile of a read only for windows whose scores need no rebasing, i.e. reads of
+    // less than 20 000 / max(|gap|, |mismatch|, match) bases; longer ones slide a 512-column window)
+    const int32_t a_max   = std::max(std::max(std::abs(static_cast<int32_t>(gap_)), std::abs(static_cast<int32_t>(mismatch_))),
+                                   std::max(static_cast<int32_t>(match_), 1));
+    scratch.fill          = (fill2_smem_bytes(std::min(L, 20000 / a_max)) + 255) & ~255;
+    scratch.fill_long     = (fill2_smem_bytes_sliding() + 255) & ~255;
+    scratch.trace      = (trace2_smem_bytes(std::min(L, 1024)) + 255) & ~255; // longer reads record their rows in global memory
     scratch.sort_large = kSmemPerWarp;
-    scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, 1536) + 2 * kKahnQueueEntries + 255) & ~255);
+    // (1 264 nodes: 5.5 KB per window, the most that leaves ten blocks per SM next to the 1 KB the system reserves per
+    // block -- the sort is bound by windows in flight: 36 ms per cfg 2 step at eight blocks, 41 at six, 53 at four)
+    static const int32_t sort_nodes = blocks_cap_from_env("CUDAPOA_B200_SORT_NODES", 1264);
+    scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, sort_nodes) + 2 * kKahnQueueEntries + 15) & ~15);
     if (kahn_smem_nodes(scratch.sort_small) >= plan_.M)
         scratch.sort_large = scratch.sort_small; // one class serves every graph of this batch
     scratch.final_ = kSmemPerWarp;
-    if (4 * std::max(std::max(scratch.fill, scratch.trace), scratch.sort_large) > kPhaseSmemLimit)
+    if (4 * std::max(std::max(std::max(scratch.fill, scratch.fill_long), scratch.trace), scratch.sort_large) > kPhaseSmemLimit)
         return false;
     P.phase = phase_d_;
     int32_t launches = 0;

@@ -46,6 +46,14 @@ __host__ __device__ inline int32_t fill2_smem_bytes(int32_t read_len)
 {
     return kRingBytes + kDescBufBytes + kProfRows * fill2_profile_stride(read_len);
 }
+// Long windows (the REBASED instance) keep a sliding window of the profile instead: kProfWindow read positions per base,
+// addressed modulo the window and refilled 256 positions at a time as the band moves right -- shared memory does not
+// grow with the read, so a 6 400-base read leaves as many windows per SM as a 640-base one.
+constexpr int32_t kProfWindow = 512;
+__host__ __device__ inline int32_t fill2_smem_bytes_sliding()
+{
+    return kRingBytes + kDescBufBytes + kProfRows * kProfWindow;
+}
 
 __device__ __forceinline__ uint32_t vminu2_1(uint32_t x) // per half: 0 if zero, else 1
 {
@@ -75,7 +83,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
     const int32_t pd_x = mismatch - gap; // bases differ
-    const int32_t pstride = fill2_profile_stride(read_len);
+    const int32_t pstride = REBASED ? kProfWindow : fill2_profile_stride(read_len);
     if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > 65535)
         return kFastNotTaken;
     const int64_t code_bytes  = static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
@@ -118,15 +126,22 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         }
     }
     const uint32_t alpha_valid = (nalpha >= 4) ? 0xffffffffu : ((1u << (8 * nalpha)) - 1u);
-    // rows beyond the alphabet hold "mismatch" everywhere: the first of them serves graph bases the read does not have
-    for (int32_t k = lane; k < pstride; k += 32)
-    {
-        const uint32_t b  = (k < read_len) ? read[k] : 0u;
-        const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
+    // rows beyond the alphabet hold "mismatch" everywhere: the first of them serves graph bases the read does not have.
+    // profile_fill(first, count): read positions first .. first + count - 1 (slot = position modulo the stride for the
+    // sliding window; the whole padded read otherwise)
+    auto profile_fill = [&](int32_t first, int32_t count) {
+        for (int32_t k = first + lane; k < first + count; k += 32)
+        {
+            const uint32_t b  = (k < read_len) ? read[k] : 0u;
+            const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
+            const int32_t at  = REBASED ? (k & (kProfWindow - 1)) : k;
 #pragma unroll
-        for (int a = 0; a < kProfRows; a++)
-            sts_u8(prof + static_cast<uint32_t>(a * pstride + k), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
-    }
+            for (int a = 0; a < kProfRows; a++)
+                sts_u8(prof + static_cast<uint32_t>(a * pstride + at), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
+        }
+    };
+    profile_fill(0, pstride);
+    int32_t prof_loaded = pstride; // sliding window: positions below this are in the window (the last kProfWindow of them)
 
     const int32_t max_column = read_len + 1;
     const float gradient     = band_gradient(read_len, node_count);
@@ -179,7 +194,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 {
                     const int32_t bs  = band_start(r, gradient, kFastBand, max_column);
                     const int32_t bsp = band_start(r - 1, gradient, kFastBand, max_column);
-                    uint32_t z        = zw[u] + static_cast<uint32_t>(bs);
+                    uint32_t z        = zw[u] + (REBASED ? 0u : static_cast<uint32_t>(bs)); // sliding window: bs is added at use
                     if (r > 1 && static_cast<int32_t>(pr[0]) == r - 1 && bs == bsp)
                         z |= kRecChain;
                     records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs));
@@ -266,9 +281,27 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
         uint32_t Q0, Q1, Q2, Q3;
         {
-            const uint32_t at = prof_l + (rec.z & 0xffffu); // profile row + band start: 4-byte aligned, not always 8
-            const uint32_t lo = lds_u32(at);
-            const uint32_t hi = lds_u32(at + 4);
+            uint32_t at_lo, at_hi;
+            if (REBASED)
+            {
+                while (bs + kFastBand > prof_loaded) // uniform; the band moved past what the window holds
+                {
+                    profile_fill(prof_loaded, kFastBand);
+                    prof_loaded += kFastBand;
+                    __syncwarp();
+                }
+                const uint32_t row = prof + (rec.z & 0xffffu);
+                const uint32_t off = static_cast<uint32_t>(bs) + 8u * static_cast<uint32_t>(lane);
+                at_lo              = row + (off & (kProfWindow - 1));
+                at_hi              = row + ((off + 4u) & (kProfWindow - 1));
+            }
+            else
+            {
+                at_lo = prof_l + (rec.z & 0xffffu); // profile row + band start: 4-byte aligned, not always 8
+                at_hi = at_lo + 4u;
+            }
+            const uint32_t lo = lds_u32(at_lo);
+            const uint32_t hi = lds_u32(at_hi);
             Q0                = prmt(lo, hi, 0xC480u);
             Q1                = prmt(lo, hi, 0xD591u);
             Q2                = prmt(lo, hi, 0xE6A2u);

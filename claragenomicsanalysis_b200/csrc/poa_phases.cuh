@@ -98,12 +98,10 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
                 // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
                 // registers and instruction cache of this one belong to the loop the benchmark spends half its time in.
-                const int32_t beta = (P.smem_per_warp >= fill2_smem_bytes(len))
-                                         ? fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match)
-                                         : -1;
+                const int32_t beta = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
                 if (beta > 0)
                     aln_len = kAlnNeedsRebased;
-                else if (beta == 0 &&
+                else if (beta == 0 && P.smem_per_warp >= fill2_smem_bytes(len) &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
                                                 P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0) == 0)
@@ -222,7 +220,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
 // sort, and the other way round.
 
 #ifndef POA_TRACE_MIN_BLOCKS
-#define POA_TRACE_MIN_BLOCKS 10
+#define POA_TRACE_MIN_BLOCKS 6
 #endif
 #ifndef POA_FUSE_MIN_BLOCKS
 #define POA_FUSE_MIN_BLOCKS 8

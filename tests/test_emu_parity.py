@@ -61,11 +61,13 @@ def test_emulated_noisy_reads_phase_split(emu):
     _check(emu, ws, dict(max_seq=448, max_reads=10, band=256, banded=True, output="consensus"))
 
 
-def test_emulated_long_window_rebased_rows(emu):
-    """Reference int32-score range (L >= 1490): the packed fill stores rows relative to a per-row offset."""
+@pytest.mark.parametrize("length,reads", [(1600, 4), (2600, 4)])
+def test_emulated_long_window_rebased_rows(emu, length, reads):
+    """Reference int32-score range (L >= 1490): the packed fill stores rows relative to a per-row offset and keeps a
+    sliding 512-column window of the read's profile (2 600 bases: the window is refilled eight times per read)."""
     emu.set_schedule(2)
-    ws = generate_windows(1, start_index=7000, template_length=1600, n_reads=4)
-    n = _check(emu, ws, dict(max_seq=2048, max_reads=4, band=256, banded=True, output="consensus"))
+    ws = generate_windows(1, start_index=7000, template_length=length, n_reads=reads)
+    n = _check(emu, ws, dict(max_seq=3200, max_reads=4, band=256, banded=True, output="consensus"))
     assert sum(s["exact_path"] for s in n["stats"]) == 0
 
 
