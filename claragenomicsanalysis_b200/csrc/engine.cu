@@ -582,13 +582,13 @@ struct PhaseTimeline
 // Scratch sizes of the launches of one step (bytes per warp == per window).
 struct PhaseScratch
 {
-    int32_t fill, fill_long, trace, sort_small, sort_large, final_;
+    int32_t fill, fill_long, trace, sort_small, sort_large, sort_big, final_; // sort_big: 0 = no third class
 };
-constexpr int32_t kCountersPerStep = 9;
+constexpr int32_t kCountersPerStep = 10;
 
 template <typename ScoreT, typename IdT, bool MSA>
 static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScratch& scratch,
-                                  const std::vector<uint8_t>& ends_at, int32_t* counters, int32_t sm_count,
+                                  int32_t* counters, int32_t sm_count,
                                   cudaStream_t stream, PhaseTimeline* timeline)
 {
     int32_t launches = 0;
@@ -600,6 +600,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
     static const int32_t cap_sort  = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_SORT", INT32_MAX);
     const bool two = scratch.sort_large > scratch.sort_small;
     P.class_cap    = two ? kahn_smem_nodes(scratch.sort_small) : INT32_MAX;
+    P.class_cap2   = scratch.sort_big > 0 ? kahn_smem_nodes(scratch.sort_large) : INT32_MAX;
     P.lean_class0  = two ? 1 : 0;
     {
         const int32_t blocks = std::max(1, std::min((P.n_windows + kFillWarpsPerBlock - 1) / kFillWarpsPerBlock, sm_count * 16));
@@ -656,9 +657,17 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
             launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream);
             launches++;
         }
+        if (scratch.sort_big > 0)
+        {
+            P.next_window   = c + 9;
+            P.smem_per_warp = scratch.sort_big;
+            P.phase_class   = 2;
+            launch_phase(poa_sort_big_kernel<IdT>, P, 1, sm_count, stream);
+            launches++;
+        }
         if (timeline)
             timeline->mark(stream, 3);
-        if (s == steps || ends_at[static_cast<size_t>(s)])
+        if (s == steps) // windows that ended earlier keep their graph untouched until here: one launch finalises all
         {
             P.next_window   = c + 7;
             P.smem_per_warp = scratch.final_;
@@ -671,7 +680,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
     return launches;
 }
 
-// Phase-split schedule (poa_phases.cuh) for banded batches: two launches per read instead of one launch per batch.
+// Phase-split schedule (poa_phases.cuh) for banded batches: one launch per phase and read instead of one per batch.
 // Returns false when the batch has to take the single launch (full alignment, 32-bit node ids, very deep windows,
 // or CUDAPOA_B200_SCHEDULE=fused).
 bool B200Batch::launch_split(KernelParams& P)
@@ -686,7 +695,10 @@ bool B200Batch::launch_split(KernelParams& P)
     // A lone batch that does not fill the device about twice over is latency-bound either way, and then one launch
     // (no per-launch tails) is ~10 % faster; measured crossover on a B200 between 4 736 and 9 472 cfg 2 windows
     // (tools/schedule_crossover.py).
-    if (mode == 0 && !overlapped_ && poa_count_ < 2 * 16 * sm_count_ + sm_count_)
+    // (window counts in units of a 500-base window: long windows fill a launch with fewer of them)
+    const int64_t bases_per_read = num_reads_ > 0 ? num_bases_ / num_reads_ : 0;
+    const int64_t weight         = std::max<int64_t>(500, bases_per_read);
+    if (mode == 0 && !overlapped_ && static_cast<int64_t>(poa_count_) * weight < static_cast<int64_t>(2 * 16 * sm_count_ + sm_count_) * 500)
         return false;
     int32_t max_reads = 1;
     for (int32_t i = 0; i < poa_count_; i++)
@@ -694,20 +706,14 @@ bool B200Batch::launch_split(KernelParams& P)
     const int32_t steps = std::max(max_reads - 1, 1);
     if (kCountersPerStep * steps > kPhaseCounters)
         return false;
-    // steps after which some window is complete (its last read; a window of one read ends at step 1)
-    std::vector<uint8_t> ends_at(static_cast<size_t>(steps) + 1, 0);
-    for (int32_t i = 0; i < poa_count_; i++)
-        ends_at[static_cast<size_t>(std::min(std::max(windows_h_[i].n_reads - 1, 1), steps))] = 1;
     // shared memory per window and launch: the fill needs the row ring, the record buffer and the profile; the
     // traceback its tile and the rows it records; the sort 4 bytes per node (small class: graphs of up to 1 264 nodes -- a 500-base polishing window ends at 1 130 +- 25,
     // large class: the single launch's scratch); the consensus its staging area and 6 bytes per node
     const int32_t L = std::max(batch_size_.max_sequence_size, 1);
     PhaseScratch scratch{};
-    // (the packed fill keeps the whole profile of a read only for windows whose scores need no rebasing, i.e. reads of
-    // less than 20 000 / max(|gap|, |mismatch|, match) bases; longer ones slide a 512-column window)
-    const int32_t a_max   = std::max(std::max(std::abs(static_cast<int32_t>(gap_)), std::abs(static_cast<int32_t>(mismatch_))),
-                                   std::max(static_cast<int32_t>(match_), 1));
-    scratch.fill          = (fill2_smem_bytes(std::min(L, 20000 / a_max)) + 255) & ~255;
+    // (the plain packed fill keeps the whole profile of a read in shared memory: reads of up to 768 bases, which leaves
+    // six blocks per SM; longer reads take the rebased fill, which slides a 512-column window of the profile)
+    scratch.fill          = (fill2_smem_bytes(std::min(L, 768)) + 255) & ~255;
     scratch.fill_long     = (fill2_smem_bytes_sliding() + 255) & ~255;
     scratch.trace      = (trace2_smem_bytes(std::min(L, 1024)) + 255) & ~255; // longer reads record their rows in global memory
     scratch.sort_large = kSmemPerWarp;
@@ -717,6 +723,11 @@ bool B200Batch::launch_split(KernelParams& P)
     scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, sort_nodes) + 2 * kKahnQueueEntries + 15) & ~15);
     if (kahn_smem_nodes(scratch.sort_small) >= plan_.M)
         scratch.sort_large = scratch.sort_small; // one class serves every graph of this batch
+    // long windows: graphs beyond the 4-byte records (3 456 nodes in 14 KB) sort out of 5-byte wide records, one warp
+    // per block with up to 10 240 nodes of scratch (four such blocks per SM)
+    scratch.sort_big = 0;
+    if (plan_.M > kahn_smem_nodes(scratch.sort_large))
+        scratch.sort_big = (kKahnWideBytesPerNode * std::min((plan_.M + 15) & ~15, 10240) + 2 * kKahnQueueEntries + 15) & ~15;
     scratch.final_ = kSmemPerWarp;
     if (4 * std::max(std::max(std::max(scratch.fill, scratch.fill_long), scratch.trace), scratch.sort_large) > kPhaseSmemLimit)
         return false;
@@ -726,16 +737,16 @@ bool B200Batch::launch_split(KernelParams& P)
     if (!plan_.score32)
     {
         if (msa_)
-            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     else
     {
         if (msa_)
-            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
         else
-            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, scratch, ends_at, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
     }
     kernel_launches_ += launches;
     return true;

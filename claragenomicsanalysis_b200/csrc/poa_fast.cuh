@@ -98,6 +98,23 @@ __device__ __forceinline__ int32_t fast_path_beta(int32_t node_count, int32_t re
     return beta;
 }
 
+// The slope of the rebased formulation for these scores (> 0), or -1 if it cannot serve them.  Rebased rows are exact
+// for every window size, so a window whose scores would also fit the plain formulation may use them (the phase-split
+// schedule does when the read is longer than the plain fill's shared-memory profile).
+__device__ __forceinline__ int32_t fast_path_rebased_beta(int32_t node_count, int32_t band, int32_t gap, int32_t mismatch,
+                                                          int32_t match)
+{
+    if (band != kFastBand || gap >= 0 || match <= 0)
+        return -1;
+    const int32_t a = max(max(-gap, abs(mismatch)), match);
+    if (a > 127 || node_count + 1 >= 32768)
+        return -1;
+    const int32_t beta = -gap + (5 * match) / 8;
+    if (beta > 30 || (match - gap) * (kFastBand + 16) > 12000)
+        return -1;
+    return beta;
+}
+
 // Per-row descriptors, three 32-bit words in three global arrays of stride g.M + 40:
 //   d0 = base | in-degree << 8 | sink << 14 | row of predecessor 0 << 16
 //   d1 = row of predecessor 1 | row of predecessor 2 << 16

@@ -74,7 +74,7 @@ constexpr int32_t kAlnPendingTraceback = -3;
 constexpr int32_t kAlnNeedsExact       = -4;  // the packed fill declined: poa_exact_kernel aligns this read
 constexpr int32_t kAlnNeedsRebased     = -5;  // long window: poa_fill_rebased_kernel fills this read
 constexpr int32_t kClassMargin         = 64;  // nodes one fusion is allowed to add before the scratch is outgrown
-constexpr int32_t kPhaseCounters       = 1024; // one window counter per launch of a batch
+constexpr int32_t kPhaseCounters       = 4096; // one window counter per launch of a batch
 
 struct KernelParams
 {
@@ -111,6 +111,7 @@ struct KernelParams
     int32_t step;          // phase-split schedule: the read (1 .. n_reads - 1) this launch works on
     int32_t phase_class;   // graph launches come in two shared-memory sizes: 0 takes the windows whose graph fits
     int32_t class_cap;     // ... the smaller scratch (node_count + kClassMargin <= class_cap), 1 the others
+    int32_t class_cap2;    // ... and graphs beyond this go to launch 2 (one warp per block, 5-byte wide records)
     int32_t class_cap_final; // the same bound for a window's last read, whose launch also runs the consensus
     int32_t lean_class0;   // launch 0 is the lean instance: rebased rows and the SPOA_ACCURATE order go to launch 1
     int32_t debug_flags;   // development switches (CUDAPOA_B200_DEBUG_FLAGS), 0 in production

@@ -98,10 +98,12 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 // This kernel holds the packed fill of the short windows only.  Long windows (rebased rows) and the
                 // exact-arithmetic alignment run in launches of their own (poa_fill_rebased_kernel, poa_exact_kernel):
                 // registers and instruction cache of this one belong to the loop the benchmark spends half its time in.
-                const int32_t beta = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
+                int32_t beta = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
+                if (beta == 0 && P.smem_per_warp < fill2_smem_bytes(len)) // the read outgrows this launch's profile
+                    beta = fast_path_rebased_beta(st.node_count, P.band, P.gap, P.mismatch, P.match);
                 if (beta > 0)
                     aln_len = kAlnNeedsRebased;
-                else if (beta == 0 && P.smem_per_warp >= fill2_smem_bytes(len) &&
+                else if (beta == 0 &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
                                                 P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0) == 0)
@@ -154,7 +156,9 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
         ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
         int32_t start_row   = 0;
         int32_t start_score = 0;
-        const int32_t beta  = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
+        int32_t beta        = fast_path_beta(st.node_count, len, P.band, P.gap, P.mismatch, P.match);
+        if (beta == 0) // sent here for its length (poa_fill_kernel): rebased rows are exact for every size
+            beta = fast_path_rebased_beta(st.node_count, P.band, P.gap, P.mismatch, P.match);
         if (beta > 0 && fill2_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                               P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
                                               P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, beta) == 0)
@@ -395,13 +399,52 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_SORT_MIN_BLOCKS)
         if (s >= wd.n_reads)
             continue;
         const int32_t node_count = st.node_count;
-        const bool other         = node_count > P.class_cap || (P.lean_class0 && P.spoa_accurate);
-        if (other != (P.phase_class == 1))
+        const int32_t cls = (P.lean_class0 && P.spoa_accurate) ? 1 : (node_count > P.class_cap) + (node_count > P.class_cap2);
+        if (cls != P.phase_class)
             continue;
         const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         if (!LEAN && P.spoa_accurate)
             topsort_spoa_order<IdT>(g, node_count, lane);
         else if ((P.debug_flags & 1) || !topsort_kahn_smem<IdT>(g, node_count, smem, P.smem_per_warp, lane))
+            topsort_kahn_warp<IdT>(g, node_count, lane);
+        if (lane == 0)
+            ps->graph_step = s;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
+// Third sort class: graphs that outgrew the 4-byte records (long windows: thousands of nodes).  One warp per block, the
+// block's whole scratch for one graph, 5 bytes per node (topsort_kahn_smem_wide); beyond that, global memory.
+template <typename IdT>
+__global__ void __launch_bounds__(32) poa_sort_big_kernel(const KernelParams P)
+{
+    POA_DYNAMIC_SMEM(smem_block);
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        PhaseState* ps = P.phase + w;
+        const PhaseState st = *ps;
+        __syncwarp(); // every lane has read the state before lane 0 changes it
+        if (st.status != kStSuccess || st.finalized || st.graph_step == s)
+            continue;
+        const WindowDesc wd = P.windows[w];
+        if (s >= wd.n_reads)
+            continue;
+        const int32_t node_count = st.node_count;
+        if ((P.lean_class0 && P.spoa_accurate) || node_count <= P.class_cap2)
+            continue;
+        const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        if (!topsort_kahn_smem_wide<IdT>(g, node_count, smem, P.smem_per_warp, lane))
             topsort_kahn_warp<IdT>(g, node_count, lane);
         if (lane == 0)
             ps->graph_step = s;

@@ -61,10 +61,11 @@ def test_emulated_noisy_reads_phase_split(emu):
     _check(emu, ws, dict(max_seq=448, max_reads=10, band=256, banded=True, output="consensus"))
 
 
-@pytest.mark.parametrize("length,reads", [(1600, 4), (2600, 4)])
+@pytest.mark.parametrize("length,reads", [(900, 4), (1600, 4), (2600, 4)])
 def test_emulated_long_window_rebased_rows(emu, length, reads):
     """Reference int32-score range (L >= 1490): the packed fill stores rows relative to a per-row offset and keeps a
-    sliding 512-column window of the read's profile (2 600 bases: the window is refilled eight times per read)."""
+    sliding 512-column window of the read's profile (2 600 bases: the window is refilled eight times per read).  Reads
+    of more than 768 bases take this fill too, whatever their score range (900)."""
     emu.set_schedule(2)
     ws = generate_windows(1, start_index=7000, template_length=length, n_reads=reads)
     n = _check(emu, ws, dict(max_seq=3200, max_reads=4, band=256, banded=True, output="consensus"))
@@ -103,3 +104,13 @@ def test_emulated_pipeline_worker_pool(emu):
             assert p.stats()["windows"] == len(ws)
     finally:
         p.close()
+
+
+def test_emulated_big_graphs_third_sort_class(emu):
+    """Graphs of more than 3 456 nodes (long windows) take the third sort class of the phase-split schedule: one warp
+    per block, 5-byte wide records (topsort_kahn_smem_wide)."""
+    emu.set_schedule(2)
+    ws = generate_windows(1, start_index=177, template_length=3300, n_reads=6)
+    n = _check(emu, ws, dict(max_seq=4000, max_reads=8, band=256, banded=True, output="consensus"))
+    assert len(n["graphs"][0][0]) > 3456
+    assert sum(s["exact_path"] for s in n["stats"]) == 0
