@@ -582,9 +582,9 @@ struct PhaseTimeline
 // Scratch sizes of the launches of one step (bytes per warp == per window).
 struct PhaseScratch
 {
-    int32_t fill, fill_long, trace, sort_small, sort_large, sort_big, final_; // sort_big: 0 = no third class
+    int32_t fill, fill_long, trace, sort_small, sort_large, final_;
 };
-constexpr int32_t kCountersPerStep = 10;
+constexpr int32_t kCountersPerStep = 9;
 
 template <typename ScoreT, typename IdT, bool MSA>
 static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScratch& scratch,
@@ -600,7 +600,6 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
     static const int32_t cap_sort  = blocks_cap_from_env("CUDAPOA_B200_BLOCKS_SORT", INT32_MAX);
     const bool two = scratch.sort_large > scratch.sort_small;
     P.class_cap    = two ? kahn_smem_nodes(scratch.sort_small) : INT32_MAX;
-    P.class_cap2   = scratch.sort_big > 0 ? kahn_smem_nodes(scratch.sort_large) : INT32_MAX;
     P.lean_class0  = two ? 1 : 0;
     {
         const int32_t blocks = std::max(1, std::min((P.n_windows + kFillWarpsPerBlock - 1) / kFillWarpsPerBlock, sm_count * 16));
@@ -655,14 +654,6 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
             P.smem_per_warp = scratch.sort_large;
             P.phase_class   = 1;
             launch_phase(poa_sort_kernel<IdT, false>, P, kGraphWarpsPerBlock, sm_count, stream);
-            launches++;
-        }
-        if (scratch.sort_big > 0)
-        {
-            P.next_window   = c + 9;
-            P.smem_per_warp = scratch.sort_big;
-            P.phase_class   = 2;
-            launch_phase(poa_sort_big_kernel<IdT>, P, 1, sm_count, stream);
             launches++;
         }
         if (timeline)
@@ -723,11 +714,9 @@ bool B200Batch::launch_split(KernelParams& P)
     scratch.sort_small = std::min(kSmemPerWarp, (kKahnBytesPerNode * std::min(plan_.M, sort_nodes) + 2 * kKahnQueueEntries + 15) & ~15);
     if (kahn_smem_nodes(scratch.sort_small) >= plan_.M)
         scratch.sort_large = scratch.sort_small; // one class serves every graph of this batch
-    // long windows: graphs beyond the 4-byte records (3 456 nodes in 14 KB) sort out of 5-byte wide records, one warp
-    // per block with up to 10 240 nodes of scratch (four such blocks per SM)
-    scratch.sort_big = 0;
-    if (plan_.M > kahn_smem_nodes(scratch.sort_large))
-        scratch.sort_big = (kKahnWideBytesPerNode * std::min((plan_.M + 15) & ~15, 10240) + 2 * kKahnQueueEntries + 15) & ~15;
+    // (measured dead end, profiles/r2_wide_sort_class_and_pipeline_connections.txt: a third class with 5-byte records
+    // and one warp per block for graphs of 3 456 .. 10 240 nodes -- cfg 4's sort got slower, 841 against 682 ms at 592
+    // windows: four such windows per SM lose to sixteen walking global memory)
     scratch.final_ = kSmemPerWarp;
     if (4 * std::max(std::max(std::max(scratch.fill, scratch.fill_long), scratch.trace), scratch.sort_large) > kPhaseSmemLimit)
         return false;

@@ -1000,147 +1000,6 @@ __device__ bool topsort_kahn_smem(const Graph<IdT>& g, int32_t node_count, uint3
     return ok != 0;
 }
 
-// The same sort for graphs of more than 4 095 nodes (long windows): node ids no longer fit 12 bits, so a node takes two
-// records -- its first two out-edges as 2 x 16 bits, and one byte `min(out-degree, 3) | open in-edges << 2` -- 5 bytes
-// per node.  The launch that runs it gives a whole block's scratch to one warp (engine.cu: the third sort class).
-constexpr int32_t kKahnWideBytesPerNode = 5;
-__host__ __device__ inline int32_t kahn_wide_smem_nodes(int32_t smem_bytes)
-{
-    const int32_t n = ((smem_bytes - 2 * kKahnQueueEntries) / kKahnWideBytesPerNode) & ~15;
-    return n < 32767 ? n : 32752;
-}
-
-template <typename IdT>
-__device__ bool topsort_kahn_smem_wide(const Graph<IdT>& g, int32_t node_count, uint32_t smem, int32_t smem_bytes,
-                                       int32_t lane)
-{
-    if (sizeof(IdT) != 2)
-        return false;
-    const int32_t cap = kahn_wide_smem_nodes(smem_bytes);
-    if (node_count > cap)
-        return false;
-    POA_COUNT("kahn.wide_sorts");
-    const uint32_t edges = smem;                // u32[cap]: out-edge 0 | out-edge 1 << 16
-    const uint32_t cnts  = edges + 4u * cap;    // u8[cap]
-    const uint32_t queue = cnts + cap;          // u16[kKahnQueueEntries]; cap is a multiple of 16
-    constexpr uint32_t kQMask = kKahnQueueEntries - 1;
-    const unsigned lt = (1u << lane) - 1u;
-    int32_t tail      = 0;
-    for (int32_t n0 = 0; n0 < node_count; n0 += 32)
-    {
-        const int32_t n = n0 + lane;
-        bool source     = false;
-        if (n < node_count)
-        {
-            const uint32_t ic = g.in_cnt[n];
-            const uint32_t oc = g.out_cnt[n];
-            const uint32_t e0 = static_cast<uint16_t>(g.out_edge(n, 0)), e1 = static_cast<uint16_t>(g.out_edge(n, 1));
-            sts_u32(edges + 4u * n, e0 | (e1 << 16));
-            sts_u8(cnts + n, min(oc, 3u) | (ic << 2));
-            source = (ic == 0);
-        }
-        const unsigned mask = __ballot_sync(kFull, source);
-        if (tail + __popc(mask) > kKahnQueueEntries)
-            return false;
-        if (source)
-            sts_u16(queue + 2u * (tail + __popc(mask & lt)), static_cast<uint32_t>(n));
-        tail += __popc(mask);
-    }
-    __syncwarp();
-    int32_t ok = 1;
-    if (lane == 0)
-    {
-        uint32_t head   = 0;
-        uint32_t pushed = static_cast<uint32_t>(tail);
-        uint32_t node   = lds_u16(queue);
-        uint32_t ve     = lds_u32(edges + 4u * node);
-        uint32_t vc     = lds_u8(cnts + node);
-        IdT* const sorted_out = g.sorted;
-        IdT* const pos_out    = g.pos;
-#define POA_KAHN_VISIT_WIDE(child_expr)                              \
-    {                                                                \
-        const uint32_t child_ = (child_expr);                        \
-        const uint32_t left_  = lds_u8(cnts + child_) - 4u;          \
-        sts_u8(cnts + child_, left_);                                \
-        if (left_ < 4u)                                              \
-        {                                                            \
-            sts_u16(queue + 2u * (pushed & kQMask), child_);         \
-            pushed++;                                                \
-        }                                                            \
-    }
-        for (;;)
-        {
-            sorted_out[head] = static_cast<IdT>(node);
-            pos_out[node]    = static_cast<IdT>(head);
-            head++;
-            const uint32_t oc = vc & 3u;
-            if (oc == 1 && head == pushed) // chain step, nothing else waiting (see topsort_kahn_smem)
-            {
-                const uint32_t child = ve & 0xffffu;
-                const uint32_t left  = lds_u8(cnts + child) - 4u;
-                if (left < 4u)
-                {
-                    pushed++;
-                    node = child;
-                    ve   = lds_u32(edges + 4u * child);
-                    vc   = left;
-                    continue;
-                }
-                sts_u8(cnts + child, left);
-                break;
-            }
-            const bool have_next = head < pushed;
-            uint32_t next_node = 0, next_e = 0, next_c = 0;
-            if (have_next)
-            {
-                next_node = lds_u16(queue + 2u * (head & kQMask));
-                next_e    = lds_u32(edges + 4u * next_node);
-                next_c    = lds_u8(cnts + next_node);
-            }
-            if (oc > 2)
-            {
-                const uint32_t more = static_cast<uint32_t>(g.out_cnt[node]);
-                const uint32_t e2   = static_cast<uint16_t>(g.out_edge(node, 2));
-                POA_KAHN_VISIT_WIDE(ve & 0xffffu)
-                POA_KAHN_VISIT_WIDE(ve >> 16)
-                POA_KAHN_VISIT_WIDE(e2)
-                for (uint32_t e = 3; e < more; e++)
-                    POA_KAHN_VISIT_WIDE(static_cast<uint16_t>(g.out_edge(node, static_cast<int32_t>(e))))
-            }
-            else
-            {
-                if (oc > 0)
-                    POA_KAHN_VISIT_WIDE(ve & 0xffffu)
-                if (oc > 1)
-                    POA_KAHN_VISIT_WIDE(ve >> 16)
-            }
-            if (head == pushed)
-                break;
-            if (pushed - head > kKahnQueueEntries)
-            {
-                ok = 0;
-                break;
-            }
-            if (have_next)
-            {
-                node = next_node;
-                ve   = next_e;
-                vc   = next_c;
-            }
-            else
-            {
-                node = lds_u16(queue + 2u * (head & kQMask));
-                ve   = lds_u32(edges + 4u * node);
-                vc   = lds_u8(cnts + node);
-            }
-        }
-#undef POA_KAHN_VISIT_WIDE
-    }
-    ok = __shfl_sync(kFull, ok, 0);
-    __syncwarp();
-    return ok != 0;
-}
-
 // Topological order that keeps aligned nodes next to each other (the SPOA_ACCURATE build of the reference and every
 // MSA: cudapoa_topsort.cuh:94-189).  The reference's order is that of a depth-first walk towards predecessors in which
 // a node first visits its aligned nodes (last to first), then its predecessors (last to first), and a group of

@@ -399,52 +399,14 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_SORT_MIN_BLOCKS)
         if (s >= wd.n_reads)
             continue;
         const int32_t node_count = st.node_count;
-        const int32_t cls = (P.lean_class0 && P.spoa_accurate) ? 1 : (node_count > P.class_cap) + (node_count > P.class_cap2);
+        // class 0: fits the small scratch; class 1: the 14 KB scratch or, beyond it, global memory
+        const int32_t cls = ((P.lean_class0 && P.spoa_accurate) || node_count > P.class_cap) ? 1 : 0;
         if (cls != P.phase_class)
             continue;
         const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         if (!LEAN && P.spoa_accurate)
             topsort_spoa_order<IdT>(g, node_count, lane);
         else if ((P.debug_flags & 1) || !topsort_kahn_smem<IdT>(g, node_count, smem, P.smem_per_warp, lane))
-            topsort_kahn_warp<IdT>(g, node_count, lane);
-        if (lane == 0)
-            ps->graph_step = s;
-        __syncwarp(); // the scratch is reused by the next window
-    }
-}
-
-// Third sort class: graphs that outgrew the 4-byte records (long windows: thousands of nodes).  One warp per block, the
-// block's whole scratch for one graph, 5 bytes per node (topsort_kahn_smem_wide); beyond that, global memory.
-template <typename IdT>
-__global__ void __launch_bounds__(32) poa_sort_big_kernel(const KernelParams P)
-{
-    POA_DYNAMIC_SMEM(smem_block);
-    int32_t lane  = threadIdx.x & 31;
-    uint32_t smem = smem_u32(smem_block);
-    asm volatile("" : "+r"(lane));
-    asm volatile("" : "+r"(smem));
-    const int32_t s = P.step;
-    for (;;)
-    {
-        int32_t w = 0;
-        if (lane == 0)
-            w = atomicAdd(P.next_window, 1);
-        w = __shfl_sync(kFull, w, 0);
-        if (w >= P.n_windows)
-            break;
-        PhaseState* ps = P.phase + w;
-        const PhaseState st = *ps;
-        __syncwarp(); // every lane has read the state before lane 0 changes it
-        if (st.status != kStSuccess || st.finalized || st.graph_step == s)
-            continue;
-        const WindowDesc wd = P.windows[w];
-        if (s >= wd.n_reads)
-            continue;
-        const int32_t node_count = st.node_count;
-        if ((P.lean_class0 && P.spoa_accurate) || node_count <= P.class_cap2)
-            continue;
-        const Graph<IdT> g = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
-        if (!topsort_kahn_smem_wide<IdT>(g, node_count, smem, P.smem_per_warp, lane))
             topsort_kahn_warp<IdT>(g, node_count, lane);
         if (lane == 0)
             ps->graph_step = s;

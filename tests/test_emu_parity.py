@@ -105,12 +105,3 @@ def test_emulated_pipeline_worker_pool(emu):
     finally:
         p.close()
 
-
-def test_emulated_big_graphs_third_sort_class(emu):
-    """Graphs of more than 3 456 nodes (long windows) take the third sort class of the phase-split schedule: one warp
-    per block, 5-byte wide records (topsort_kahn_smem_wide)."""
-    emu.set_schedule(2)
-    ws = generate_windows(1, start_index=177, template_length=3300, n_reads=6)
-    n = _check(emu, ws, dict(max_seq=4000, max_reads=8, band=256, banded=True, output="consensus"))
-    assert len(n["graphs"][0][0]) > 3456
-    assert sum(s["exact_path"] for s in n["stats"]) == 0
