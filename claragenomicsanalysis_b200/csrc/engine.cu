@@ -683,18 +683,20 @@ bool B200Batch::launch_split(KernelParams& P)
     const int32_t mode = g_schedule_override.load();
     if (!banded_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
         return false;
-    // A lone batch that does not fill the device about twice over is latency-bound either way, and then one launch
-    // (no per-launch tails) is ~10 % faster; measured crossover on a B200 between 4 736 and 9 472 cfg 2 windows
-    // (tools/schedule_crossover.py).
-    // (window counts in units of a 500-base window: long windows fill a launch with fewer of them)
-    const int64_t bases_per_read = num_reads_ > 0 ? num_bases_ / num_reads_ : 0;
-    const int64_t weight         = std::max<int64_t>(500, bases_per_read);
-    if (mode == 0 && !overlapped_ && static_cast<int64_t>(poa_count_) * weight < static_cast<int64_t>(2 * 16 * sm_count_ + sm_count_) * 500)
-        return false;
     int32_t max_reads = 1;
     for (int32_t i = 0; i < poa_count_; i++)
         max_reads = std::max(max_reads, windows_h_[i].n_reads);
     const int32_t steps = std::max(max_reads - 1, 1);
+    // A lone batch that keeps fewer than about 15 windows per SM busy per step is bound by the latency of a step's kernel
+    // chain, and then the single launch (no barrier between the steps of different windows) is as fast or faster.
+    // Work per step in units of a 500-base read: ragged batches (windows with few reads drop out early) and long reads
+    // are what the plain window count misses.  Measured on a B200 (profiles/r2_fill_cap_costream_and_crossover.txt,
+    // profiles/r2_other_shapes_both_schedules.txt): cfg 2 2 368 windows 35.9 against 37.3 ms, 3 552 windows 45 against
+    // 68 ms (the single launch holds 16 windows per SM: a second wave); cfg 5b 2 368 windows (1 970 units) 444 against
+    // 402 ms, 9 472 windows 583 against 766 ms; cfg 4 592 windows (4 190 units) 2 045 against 2 131 ms.
+    const int64_t units = num_bases_ / (static_cast<int64_t>(500) * steps);
+    if (mode == 0 && !overlapped_ && units < static_cast<int64_t>(15) * sm_count_)
+        return false;
     if (kCountersPerStep * steps > kPhaseCounters)
         return false;
     // shared memory per window and launch: the fill needs the row ring, the record buffer and the profile; the

@@ -16,7 +16,7 @@ dll = ctypes.CDLL(_cabi.NATIVE_LIB_PATH)
 dll.cudapoa_b200_bench_relaunch.restype = ctypes.c_double
 dll.cudapoa_b200_bench_relaunch.argtypes = [ctypes.c_void_p, ctypes.c_int32]
 sizes = [int(x) for x in sys.argv[1:]] or [148, 592, 1184, 2368, 4736, 9472]
-ws_all, _ = bench.make_windows(max(sizes), 1024, 0)
+ws_all, _ = bench.make_windows("cfg2", max(sizes), 4096, 0)
 batch = CudaPoaBatch(30, 640, 40 << 30, output_type="consensus", cuda_banded_alignment=True, alignment_band_width=256,
                      lib=lib)
 for n in sizes:
