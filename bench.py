@@ -50,6 +50,9 @@ OTHER_CONFIGS = {
                  workload="cfg4: 2-5 kb x 100 reads, band 256, int32 scores in the reference"),
     "cfg5b": dict(gen="cfg5b", max_seq=2560, max_reads=60, output="consensus", windows=2368, steps=2,
                   workload="cfg5b: templates 250/500/1000/2000 bp (p .2/.5/.2/.1) x 10..60 reads in one batch"),
+    "cfg2_full": dict(gen="cfg2", max_seq=640, max_reads=30, output="consensus", windows=9472, steps=2, banded=False,
+                      workload="cfg2 windows, full alignment (the reference's default mode; cudapoa/benchmarks/"
+                               "single_batch.hpp:48-50): packed fill in column chunks of 256 cells"),
 }
 
 
@@ -338,7 +341,7 @@ def measure_other_config(name, spec, ws, lib, dll, device, ranks, max_mem, dpx_p
     from claragenomicsanalysis_b200.cudapoa import CudaPoaBatch
 
     batch = CudaPoaBatch(spec["max_reads"], spec["max_seq"], max_mem, output_type=spec["output"], device_id=device,
-                         cuda_banded_alignment=True, alignment_band_width=256, lib=lib)
+                         cuda_banded_alignment=spec.get("banded", True), alignment_band_width=256, lib=lib)
     try:
         if batch.max_poas < len(ws):
             ws = ws.slice(0, batch.max_poas)
@@ -394,7 +397,7 @@ def run_native(args, rank, world, local_rank):
     other_ws = {}
     if not args.no_other_configs:
         for name, spec in OTHER_CONFIGS.items():
-            if name == "cfg3":
+            if spec["gen"] in ("cfg2", "cfg3"):
                 other_ws[name] = ws.slice(0, spec["windows"])
             else:
                 other_ws[name] = make_windows(spec["gen"], spec["windows"], args.distinct, rank * args.distinct)[0]

@@ -589,7 +589,7 @@ constexpr int32_t kCountersPerStep = 9;
 template <typename ScoreT, typename IdT, bool MSA>
 static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScratch& scratch,
                                   int32_t* counters, int32_t sm_count,
-                                  cudaStream_t stream, PhaseTimeline* timeline)
+                                  cudaStream_t stream, PhaseTimeline* timeline, bool full)
 {
     int32_t launches = 0;
     if (timeline)
@@ -613,19 +613,34 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
         P.step          = s;
         P.next_window   = c + 0;
         P.smem_per_warp = scratch.fill;
-        launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
-        P.next_window   = c + 1;
-        P.smem_per_warp = scratch.fill_long;
-        launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        P.next_window   = c + 2;
-        P.smem_per_warp = 0;
-        launch_phase(poa_exact_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
-        launches += 3;
+        if (full)
+        {
+            // full alignment: the chunked packed fill, the exact full alignment for what it declines
+            launch_phase(poa_fill_full_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
+            P.next_window   = c + 2;
+            P.smem_per_warp = 0;
+            launch_phase(poa_exact_kernel<ScoreT, IdT, true>, P, kFillWarpsPerBlock, sm_count, stream);
+            launches += 2;
+        }
+        else
+        {
+            launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
+            P.next_window   = c + 1;
+            P.smem_per_warp = scratch.fill_long;
+            launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
+            P.next_window   = c + 2;
+            P.smem_per_warp = 0;
+            launch_phase(poa_exact_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);
+            launches += 3;
+        }
         if (timeline)
             timeline->mark(stream, 0);
         P.next_window   = c + 3;
         P.smem_per_warp = scratch.trace;
-        launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
+        if (full)
+            launch_phase(poa_trace_kernel<ScoreT, IdT, true>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
+        else
+            launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
         if (P.adaptive_max_band > 0)
         {
             P.next_window   = c + 8;
@@ -681,7 +696,11 @@ bool B200Batch::launch_split(KernelParams& P)
         return env != nullptr && std::strcmp(env, "fused") == 0;
     }();
     const int32_t mode = g_schedule_override.load();
-    if (!banded_ || plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
+    if (plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
+        return false;
+    // full alignment: the chunked packed fill keeps a read's whole profile in shared memory (reads of up to 768 bases:
+    // three column chunks); longer full alignments stay with the single launch
+    if (!banded_ && batch_size_.max_sequence_size > 768)
         return false;
     int32_t max_reads = 1;
     for (int32_t i = 0; i < poa_count_; i++)
@@ -728,16 +747,16 @@ bool B200Batch::launch_split(KernelParams& P)
     if (!plan_.score32)
     {
         if (msa_)
-            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_, !banded_);
         else
-            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int16_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_, !banded_);
     }
     else
     {
         if (msa_)
-            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, true>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_, !banded_);
         else
-            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_);
+            launches = launch_split_typed<int32_t, int16_t, false>(P, steps, scratch, phase_counters_d_, sm_count_, stream_, timeline_, !banded_);
     }
     kernel_launches_ += launches;
     return true;
@@ -756,6 +775,7 @@ void B200Batch::launch()
     P.scores              = scores_d_;
     P.banded_score_stride = static_cast<int64_t>(plan_.band_cells + kBandRowPad) * plan_.G;
     P.adaptive_max_band   = adaptive_ ? plan_.band_cells : 0;
+    P.score_rows          = plan_.G;
     P.status              = status_d_;
     P.node_count          = node_count_d_;
     P.consensus           = consensus_d_;

@@ -74,7 +74,14 @@ __device__ __forceinline__ int32_t record_pred_row(const Graph<IdT>& g, uint32_t
 
 // Returns 0 and the row the traceback starts from in start_row, or kFastNotTaken (nothing the caller needs was
 // written: the exact path redoes the read).  All 32 lanes.
-template <typename IdT, bool REBASED>
+//
+// FULL: full alignment (cudapoa_nw.cuh:41-466; no band): the matrix is cut into column chunks of 256 cells and the row
+// loop runs once per chunk -- chunk c is a "band" whose start is 256 c in every row, so rows never shift against each
+// other, the row above is the previous row of the same pass, and the 8-row ring and the profile serve as they are.
+// What a chunk hands to the next is one value per row, the cell at its right edge (the horizontal carry and, for the
+// rows below, the diagonal corner): int32 per row in g.cscore, written by lane 31, read 32 rows at a time.  Codes of
+// chunk c, row r live in code row c * (node_count + 1) + r.
+template <typename IdT, bool REBASED, bool FULL = false>
 __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                               uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
                               int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t& start_score,
@@ -86,7 +93,10 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const int32_t pstride = REBASED ? kProfWindow : fill2_profile_stride(read_len);
     if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > 65535)
         return kFastNotTaken;
-    const int64_t code_bytes  = static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
+    static_assert(!(FULL && REBASED), "full alignment is served by the plain formulation only");
+    const int32_t n_chunks    = FULL ? max((read_len + kFastBand - 1) / kFastBand, 1) : 1;
+    const int64_t code_bytes  = FULL ? static_cast<int64_t>(n_chunks) * (node_count + 1) * kCodeRowBytes
+                                     : static_cast<int64_t>(max_nodes + 1) * kCodeRowBytes;
     const int32_t spill_slots = static_cast<int32_t>(min(static_cast<long long>(65535),
                                                          static_cast<long long>((area_bytes - code_bytes) / kSpillRowBytes)));
     if (spill_slots < 2)
@@ -192,8 +202,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 const int32_t r = rb + lane + 32 * u;
                 if (r <= node_count)
                 {
-                    const int32_t bs  = band_start(r, gradient, kFastBand, max_column);
-                    const int32_t bsp = band_start(r - 1, gradient, kFastBand, max_column);
+                    const int32_t bs  = FULL ? 0 : band_start(r, gradient, kFastBand, max_column);
+                    const int32_t bsp = FULL ? 0 : band_start(r - 1, gradient, kFastBand, max_column);
                     uint32_t z        = zw[u] + (REBASED ? 0u : static_cast<uint32_t>(bs)); // sliding window: bs is added at use
                     if (r > 1 && static_cast<int32_t>(pr[0]) == r - 1 && bs == bsp)
                         z |= kRecChain;
@@ -256,14 +266,27 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     uint8_t* code_lane4   = codes + 4 * lane; // nibble rows: one word per lane
     uint8_t* code_lane8   = codes + 8 * lane; // byte rows: two words per lane
 
-    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last and its left boundary
-    int32_t prev_left_t = 0;
     const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
     int32_t best = best_floor, best_row = 0;
     bool unranked = false;
+    int32_t* edge_cell = g.cscore; // FULL: per row, the cell at the right edge of the chunk before
 
-    // records of the next 32 rows, one per lane, loaded a chunk ahead
-    uint4 nrec = records[min(1 + lane, node_count)];
+    for (int32_t chunk = 0; chunk < n_chunks; chunk++)
+    {
+    const int32_t chunk_bs = chunk * kFastBand; // FULL: the band start of every row of this pass
+    if (FULL && chunk > 0)
+    {
+        // row 0 holds T == 0 in every column: only its band start moves
+        if (lane == 0)
+            __stcg(reinterpret_cast<uint4*>(spill), make_uint4(static_cast<uint32_t>(chunk_bs), 0u, 0u, 0u));
+        __syncwarp();
+    }
+    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last and its left boundary
+    int32_t prev_left_t = 0;
+    // records of the next 32 rows, one per lane, loaded a chunk ahead (FULL: and their left-edge cells)
+    uint4 nrec    = records[min(1 + lane, node_count)];
+    int32_t nedge = (FULL && chunk > 0) ? __ldcg(edge_cell + min(1 + lane, node_count)) : 0;
+    int32_t cedge = 0;
 
     for (int32_t r = 1; r <= node_count; r++)
     {
@@ -273,9 +296,14 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             sts_v4(dbuf + 16u * static_cast<uint32_t>(lane), nrec);
             __syncwarp();
             nrec = records[min(r + 32 + lane, node_count)];
+            if (FULL && chunk > 0)
+            {
+                cedge = nedge;
+                nedge = __ldcg(edge_cell + min(r + 32 + lane, node_count));
+            }
         }
         const uint4 rec = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
-        const int32_t bs = static_cast<int32_t>(rec.w & 0xffffu);
+        const int32_t bs = FULL ? chunk_bs : static_cast<int32_t>(rec.w & 0xffffu);
         const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
 
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
@@ -298,6 +326,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             else
             {
                 at_lo = prof_l + (rec.z & 0xffffu); // profile row + band start: 4-byte aligned, not always 8
+                if (FULL)
+                    at_lo += static_cast<uint32_t>(chunk_bs); // the records carry band start 0
                 at_hi = at_lo + 4u;
             }
             const uint32_t lo = lds_u32(at_lo);
@@ -499,7 +529,9 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             return kFastNotTaken;
 
         // left boundary of this row in the tilted domain (a source node's predecessor is row 0, whose boundary is 0)
-        const int32_t left_t = (bs == 0) ? static_cast<int32_t>(static_cast<int16_t>(left_best + gap)) : kNegT;
+        int32_t left_t = (bs == 0) ? static_cast<int32_t>(static_cast<int16_t>(left_best + gap)) : kNegT;
+        if (FULL && chunk > 0)
+            left_t = __shfl_sync(kFull, cedge, k); // this row's cell at column 256 * chunk, from the pass before
 
         // horizontal pass = prefix maximum, both halves at once
         const uint32_t P1 = __vmaxs2(S1, S0);
@@ -552,7 +584,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         K2 += 2u * vminu2_1(out.z ^ S2);
         K3 += 2u * vminu2_1(out.w ^ S3);
         POA_COUNT(pc <= 1 ? "fill2.rows_1pred" : pc <= kWidePreds ? "fill2.rows_2to4pred" : "fill2.rows_wide");
-        const int64_t code_row = static_cast<int64_t>(r) * kCodeRowBytes;
+        const int64_t code_row = (FULL ? static_cast<int64_t>(chunk) * (node_count + 1) + r : static_cast<int64_t>(r)) * kCodeRowBytes;
         if (pc <= kWidePreds)
         {
             // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
@@ -582,7 +614,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 if (lane == 0)
                     __stcg(dst, lead);
             }
-            if (rec.z & kRecSink)
+            if ((rec.z & kRecSink) && (!FULL || chunk == n_chunks - 1))
             {
                 // sink row: its score at column read_len (all candidates share the column, so tilted scores compare
                 // like the scores themselves); first strict maximum in row order (cudapoa_nw_banded.cuh:372-383)
@@ -614,10 +646,13 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 }
             }
         }
+        if (FULL && chunk + 1 < n_chunks && lane == 31)
+            __stcg(edge_cell + r, hi16(out.w)); // the row's cell at column 256 * (chunk + 1)
         prev_out    = out;
         prev_left_t = left_t;
         __syncwarp();
     }
+    } // chunk
 
     if (unranked)
         return kFastNotTaken; // a sink row whose band misses the last column cannot be ranked on rebased scores

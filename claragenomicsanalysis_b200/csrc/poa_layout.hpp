@@ -111,6 +111,7 @@ struct KernelParams
     int32_t step;          // phase-split schedule: the read (1 .. n_reads - 1) this launch works on
     int32_t phase_class;   // graph launches come in two shared-memory sizes: 0 takes the windows whose graph fits
     int32_t class_cap;     // ... the smaller scratch (node_count + kClassMargin <= class_cap), 1 the others
+    int32_t score_rows;    // rows of a window's score matrix (full alignment: its area is scores_width x score_rows cells)
     int32_t class_cap_final; // the same bound for a window's last read, whose launch also runs the consensus
     int32_t lean_class0;   // launch 0 is the lean instance: rebased rows and the SPOA_ACCURATE order go to launch 1
     int32_t debug_flags;   // development switches (CUDAPOA_B200_DEBUG_FLAGS), 0 in production

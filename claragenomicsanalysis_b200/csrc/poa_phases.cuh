@@ -124,6 +124,69 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
     }
 }
 
+// Full alignment (the reference's default mode, cudapoa_nw.cuh): this launch takes the place of poa_fill_kernel.  The
+// packed fill runs the matrix in column chunks of 256 cells (fill2_impl<.., FULL>); a window's score area
+// (scores_width x score_rows cells at its own offset) holds the chunks' move codes and the spill slots.
+template <typename ScoreT, typename IdT>
+__global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) poa_fill_full_kernel(const KernelParams P)
+{
+    POA_DYNAMIC_SMEM(smem_block);
+    int32_t lane  = threadIdx.x & 31;
+    uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lane));
+    asm volatile("" : "+r"(smem));
+    const int32_t s = P.step;
+    for (;;)
+    {
+        int32_t w = 0;
+        if (lane == 0)
+            w = atomicAdd(P.next_window, 1);
+        w = __shfl_sync(kFull, w, 0);
+        if (w >= P.n_windows)
+            break;
+        const WindowDesc wd = P.windows[w];
+        const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+        const int32_t* rlen = P.read_len + wd.read_off;
+        PhaseState* ps      = P.phase + w;
+        PhaseState st       = *ps;
+        if (st.status == kStSuccess && s < wd.n_reads)
+        {
+            st.seq_off += rlen[s - 1];
+            const uint8_t* seq = P.bases + wd.base_off + st.seq_off;
+            const int32_t len  = rlen[s];
+            if (st.node_count >= P.max_nodes) // cudapoa_kernels.cuh:220-226
+            {
+                st.status = kStNodeCountExceeded;
+            }
+            else
+            {
+                uint8_t* area       = reinterpret_cast<uint8_t*>(static_cast<ScoreT*>(P.scores) + wd.score_off);
+                int64_t area_bytes  = static_cast<int64_t>(wd.scores_width) * P.score_rows * static_cast<int64_t>(sizeof(ScoreT));
+                const int64_t skew  = (16 - (reinterpret_cast<uintptr_t>(area) & 15)) & 15; // code rows want 16-byte alignment
+                area += skew;
+                area_bytes -= skew;
+                int32_t start_row   = 0;
+                int32_t start_score = 0;
+                const int32_t beta  = fast_path_beta(st.node_count, len, kFastBand, P.gap, P.mismatch, P.match);
+                if (beta == 0 && P.smem_per_warp >= fill2_smem_bytes(len) &&
+                    fill2_impl<IdT, false, true>(g, st.node_count, seq, len, area, area_bytes, P.max_nodes, P.gap, P.mismatch,
+                                                 P.match, smem, lane, start_row, start_score, 0) == 0)
+                    st.aln_len = kAlnPendingTraceback;
+                else
+                    st.aln_len = kAlnNeedsExact;
+                st.start_row = start_row;
+                st.aln_score = start_score;
+                st.beta      = 0;
+                st.rows += static_cast<uint32_t>(st.node_count);
+                st.cells += static_cast<unsigned long long>(st.node_count) * static_cast<unsigned long long>(len);
+            }
+        }
+        if (lane == 0)
+            *ps = st;
+        __syncwarp(); // the scratch is reused by the next window
+    }
+}
+
 // The packed fill of long windows (rows stored relative to a per-row offset, poa_fast.cuh fast_path_beta), for the
 // reads poa_fill_kernel marked kAlnNeedsRebased.
 template <typename ScoreT, typename IdT>
@@ -181,7 +244,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
 // The reads the packed fill declined (other band widths, scores outside its range, rows decided by sentinel
 // arithmetic): the exact-arithmetic alignment, traceback included.  Launched after every fill launch; a warp that
 // finds nothing to do for a window moves on after one 4-byte load.
-template <typename ScoreT, typename IdT>
+template <typename ScoreT, typename IdT, bool FULL = false>
 __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(const KernelParams P)
 {
     int32_t lane = threadIdx.x & 31;
@@ -205,10 +268,12 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         const int32_t* rlen = P.read_len + wd.read_off;
         const uint8_t* seq  = P.bases + wd.base_off + st.seq_off;
-        ScoreT* scores      = static_cast<ScoreT*>(P.scores) + static_cast<int64_t>(w) * P.banded_score_stride;
+        ScoreT* scores      = static_cast<ScoreT*>(P.scores) +
+                         (FULL ? wd.score_off : static_cast<int64_t>(w) * P.banded_score_stride);
         int32_t aln_score   = 0;
-        st.aln_len = align_exact<ScoreT, IdT, true>(g, st.node_count, seq, rlen[s], scores, P.band + kBandRowPad, P.band,
-                                                    P.gap, P.mismatch, P.match, lane, &aln_score);
+        st.aln_len = align_exact<ScoreT, IdT, !FULL>(g, st.node_count, seq, rlen[s], scores,
+                                                     FULL ? wd.scores_width : P.band + kBandRowPad, P.band, P.gap,
+                                                     P.mismatch, P.match, lane, &aln_score);
         st.aln_score = aln_score;
         st.exact++;
         if (lane == 0)
@@ -234,7 +299,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 4) poa_exact_kernel(c
 #endif
 
 // Traceback over the move codes of the read the fill launch has just aligned (poa_trace2.cuh).
-template <typename ScoreT, typename IdT>
+template <typename ScoreT, typename IdT, bool FULL = false>
 __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_TRACE_MIN_BLOCKS) poa_trace_kernel(const KernelParams P)
 {
     POA_DYNAMIC_SMEM(smem_block);
@@ -258,9 +323,11 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_TRACE_MIN_BLOCKS
         const WindowDesc wd = P.windows[w];
         const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
         const int32_t len   = P.read_len[wd.read_off + P.step];
-        const uint8_t* area = reinterpret_cast<const uint8_t*>(static_cast<ScoreT*>(P.scores) +
-                                                               static_cast<int64_t>(w) * P.banded_score_stride);
-        const int32_t aln_len = trace2_impl<IdT>(g, st.node_count, len, area, smem, P.smem_per_warp, st.start_row, lane);
+        const uint8_t* area = reinterpret_cast<const uint8_t*>(
+            static_cast<ScoreT*>(P.scores) + (FULL ? wd.score_off : static_cast<int64_t>(w) * P.banded_score_stride));
+        if (FULL)
+            area += (16 - (reinterpret_cast<uintptr_t>(area) & 15)) & 15; // as poa_fill_full_kernel aligned it
+        const int32_t aln_len = trace2_impl<IdT, FULL>(g, st.node_count, len, area, smem, P.smem_per_warp, st.start_row, lane);
         if (lane == 0)
             ps->aln_len = aln_len;
         __syncwarp(); // the scratch is reused by the next window

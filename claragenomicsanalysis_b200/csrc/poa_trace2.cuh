@@ -32,15 +32,18 @@ __host__ __device__ inline int32_t trace2_smem_bytes(int32_t read_len)
 
 // Code of cell `cell` of a row that stores a byte per cell (more than kWidePreds predecessors).  Out of line on purpose:
 // the walk's loop should not carry the address arithmetic of a load it almost never issues.
-__device__ POA_NOINLINE uint32_t wide_row_code(const uint8_t* codes, int32_t row, int32_t cell)
+__device__ POA_NOINLINE uint32_t wide_row_code(const uint8_t* codes, int64_t row, int32_t cell)
 {
     POA_COUNT("trace2.wide_steps");
-    return __ldcg(codes + static_cast<int64_t>(row) * kCodeRowBytes + cell);
+    return __ldcg(codes + row * kCodeRowBytes + cell);
 }
 
 // Returns the alignment length (> 0), or -1 if a code is not a move (cannot happen for codes the fill wrote; kept as the
 // reference's loop-count guard).  All 32 lanes.  `smem_bytes` of scratch at `tile`.
-template <typename IdT>
+// FULL (full alignment, fill2_impl<.., FULL>): the codes of column chunk c, row r are code row c * (node_count + 1) + r
+// and every row's "band start" is 256 c; the walk stops at a chunk's left edge and the next tile is staged from the
+// chunk before.
+template <typename IdT, bool FULL = false>
 __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t read_len, const uint8_t* area,
                                uint32_t tile, int32_t smem_bytes, int32_t start_row, int32_t lane)
 {
@@ -59,6 +62,8 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
         POA_COUNT("trace2.tiles");
         const int32_t tile_r0 = i - (kT2Rows - 1);
         const int32_t tile_c0 = ((j - 1) & ~7) + 1 - (kT2Cols - 8);
+        const int32_t chunk_lo = FULL ? ((j - 1) & ~(kFastBand - 1)) : 0;          // the walk stays right of this column
+        const int64_t chunk_row0 = FULL ? static_cast<int64_t>(chunk_lo / kFastBand) * (node_count + 1) : 0;
 #pragma unroll
         for (int32_t u = 0; u < kT2Rows / 32; u++)
         {
@@ -70,10 +75,10 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
             if (r >= 1)
             {
                 dsc              = records[r];
-                const int32_t b  = static_cast<int32_t>(dsc.w & 0xffffu);
+                const int32_t b  = FULL ? chunk_lo : static_cast<int32_t>(dsc.w & 0xffffu);
                 c0               = tile_c0 - b - 1;       // band cell under the tile's first column, a multiple of 4
                 const int32_t w0 = c0 >> 3;               // first word of the row the tile needs (floor division)
-                const uint32_t* row = reinterpret_cast<const uint32_t*>(codes + static_cast<int64_t>(r) * kCodeRowBytes);
+                const uint32_t* row = reinterpret_cast<const uint32_t*>(codes + (chunk_row0 + r) * kCodeRowBytes);
 #pragma unroll
                 for (int32_t q = 0; q <= kT2Cols / 8; q++)
                 {
@@ -106,7 +111,7 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
             const uint32_t code_base = tile - static_cast<uint32_t>(kT2RowBytes) * static_cast<uint32_t>(tile_r0);
             // the walk proper, instantiated for both homes of the recorded rows so that the choice costs nothing per step
             auto walk = [&](auto rows_in_smem) {
-                while (i >= row_floor && j >= tile_c0 && j > 0)
+                while (i >= row_floor && j >= tile_c0 && j > chunk_lo)
                 {
                     // descriptor and code word are fetched together: one shared-memory latency per step
                     const int32_t x   = j - tile_c0; // 0 .. 63
@@ -116,7 +121,7 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
                     const int32_t pc  = static_cast<int32_t>((dd.z >> 16) & 0x3fu);
                     uint32_t code     = (cw >> ((x & 7) * 4)) & 0xfu;
                     if (pc > kWidePreds) // rare: such rows keep a byte per cell in global memory
-                        code = wide_row_code(codes, i, j - static_cast<int32_t>(dd.w & 0xffffu) - 1);
+                        code = wide_row_code(codes, chunk_row0 + i, j - (FULL ? chunk_lo : static_cast<int32_t>(dd.w & 0xffffu)) - 1);
                     steps++;
                     const uint32_t at = rows_s + 2u * static_cast<uint32_t>(j - 1); // where read position j - 1 is recorded
                     if (code & 2u) // horizontal: an inserted base

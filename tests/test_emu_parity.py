@@ -105,3 +105,13 @@ def test_emulated_pipeline_worker_pool(emu):
     finally:
         p.close()
 
+
+
+@pytest.mark.parametrize("length,reads", [(300, 6), (520, 5)])
+def test_emulated_full_alignment_packed_chunks(emu, length, reads):
+    """Full alignment on the phase-split schedule: the packed fill runs the matrix in column chunks of 256 cells
+    (two and three chunks here), the traceback follows the codes across chunk edges; nothing goes to the exact path."""
+    emu.set_schedule(2)
+    ws = generate_windows(2, start_index=8800, template_length=length, n_reads=reads)
+    n = _check(emu, ws, dict(max_seq=640, max_reads=8, band=256, banded=False, output="consensus"))
+    assert sum(s["exact_path"] for s in n["stats"]) == 0

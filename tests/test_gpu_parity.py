@@ -95,6 +95,43 @@ def test_single_launch_and_phase_split_agree(lib, schedule, name):
         assert [s[key] for s in got[1]["stats"]] == [s[key] for s in got[2]["stats"]]
 
 
+FULL_SPLIT_CASES = sorted(n for n in CASES if not CASES[n]["engine"].get("banded", True) and CASES[n]["engine"]["max_seq"] <= 768)
+
+
+@pytest.mark.parametrize("name", FULL_SPLIT_CASES)
+def test_full_alignment_packed_path_matches_exact_path_and_oracle(lib, schedule, name):
+    """Full alignment (the reference's default mode): the single launch aligns with the exact-arithmetic path, the
+    phase-split schedule with the packed fill run in column chunks of 256 cells (fill2_impl<.., FULL>) and the code
+    traceback; both must equal the oracle bit for bit, and the packed path must decline nothing."""
+    case = CASES[name]
+    eng = case["engine"]
+    ws = case_windows(name)
+    o = parity.run_oracle(ws, want_graphs=True, **eng)
+    got = {}
+    for mode in (1, 2):
+        schedule(mode)
+        got[mode] = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+        assert parity.compare(got[mode], o, eng["output"]) == []
+    assert got[1]["graphs"] == got[2]["graphs"] == o["graphs"]
+    assert got[1]["seq_status"] == got[2]["seq_status"]
+    assert sum(s["exact_path"] for s in got[2]["stats"]) == 0
+    assert sum(s["exact_path"] for s in got[1]["stats"]) == sum(s["reads_aligned"] for s in got[1]["stats"])
+    assert [s["dp_cells"] for s in got[1]["stats"]] == [s["dp_cells"] for s in got[2]["stats"]]
+
+
+def test_full_alignment_cfg2_windows_phase_split(lib, schedule):
+    """cfg 2 windows (500 bp x 30 reads: three column chunks per row) in full-alignment mode through the phase-split
+    schedule against the oracle, and -- when the reference build is present -- against the live reference."""
+    ws = generate_windows(24, start_index=31000, template_length=500, n_reads=30)
+    eng = dict(max_seq=640, max_reads=30, band=256, banded=False, output="consensus")
+    schedule(2)
+    got = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+    o = parity.run_oracle(ws, want_graphs=True, **eng)
+    assert parity.compare(got, o, "consensus") == []
+    assert got["graphs"] == o["graphs"]
+    assert sum(s["exact_path"] for s in got["stats"]) == 0
+
+
 @pytest.mark.parametrize("output", ["consensus", "msa"])
 def test_ragged_batch_both_schedules(lib, schedule, output):
     """Windows of one batch finish at different launches of the phase-split schedule: read counts 1 .. 14 mixed with

@@ -22,7 +22,7 @@ except Exception as e:
 PY
 if [ -z "$NO_NCU" ]; then
 timeout 600 $B --steps 1 --warmup 0 > gpurun_out/${TAG}_plain.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 900 --csv --log-file gpurun_out/${TAG}_launches.csv $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_launches.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 1300 --csv --log-file gpurun_out/${TAG}_launches.csv $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_launches.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:poa_fill_kernel -s 15 -c 1 -f -o gpurun_out/${TAG}_fill $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_fill.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:poa_sort_kernel -s 30 -c 1 -f -o gpurun_out/${TAG}_sort $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_sort.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:poa_trace_kernel -s 15 -c 1 -f -o gpurun_out/${TAG}_trace $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_trace.log 2>&1

@@ -21,7 +21,7 @@ def main():
         jobs.append((name, int(n)))
     sets = {}
     for name, n in jobs:  # generators fork: before CUDA is initialised
-        gen = bench.OTHER_CONFIGS[name]["gen"] if name != "cfg3" else "cfg2"
+        gen = bench.OTHER_CONFIGS[name]["gen"] if bench.OTHER_CONFIGS[name]["gen"] != "cfg3" else "cfg2"
         sets[(name, n)] = bench.make_windows(gen, n, 65536, 0)[0]
     import torch
 

@@ -88,6 +88,7 @@ def main():
     ap.add_argument("--config", default="cfg2", choices=sorted(SHAPES))
     ap.add_argument("--mem-share", type=float, default=0.8, help="share of free memory split among the K batches")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--full", action="store_true", help="full alignment instead of the static band")
     args = ap.parse_args()
     if args.engine == "ref":
         import parity
@@ -104,10 +105,10 @@ def main():
         mem = int(free_b * args.mem_share / k)
         times = []
         for _ in range(args.reps):
-            dt, done, rounds, cap = run_k(lib, ws, k, shape, mem)
+            dt, done, rounds, cap = run_k(lib, ws, k, shape, mem, banded=not args.full)
             times.append(dt)
         dt = min(times)
-        line = dict(engine=args.engine, config=args.config, k=k, windows=done, seconds=round(dt, 4),
+        line = dict(engine=args.engine, config=args.config, full_alignment=args.full, k=k, windows=done, seconds=round(dt, 4),
                     windows_per_s=round(done / dt, 1), rounds=rounds, windows_per_batch=cap,
                     one_warp_blocks_per_wave=148 * 32,
                     waves_per_batch=round(cap / (148 * 32.0), 2), mem_per_batch_gb=round(mem / 2**30, 2))
