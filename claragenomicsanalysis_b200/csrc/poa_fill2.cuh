@@ -429,6 +429,15 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
 
         // S_i: best diagonal / vertical candidate per cell; K_i: its move code (kind | predecessor slot << 2) under the
         // assumption that the cell is not reached horizontally.
+        //
+        // Several predecessors: every predecessor p offers cell j the candidates V^p[j-1] + pd[j] (diagonal) and
+        // V^p[j] + gap (vertical), V^p being its row aligned to this row's band.  Both additions are the same for every
+        // p, so the best candidates follow from the element-wise maximum M = max_p V^p alone, and the slot the
+        // reference's traceback would pick (the first predecessor that explains the cell, cudapoa_nw_banded.cuh:
+        // 404-455) is the first p that attains M at the operand's column: one maximum and one index update per cell
+        // and predecessor instead of two candidates and two updates.  (Candidates that the clamp at the sentinel
+        // makes equal can get another slot than a candidate-wise comparison would give them; a walk never enters
+        // sentinel cells.)
         uint32_t S0, S1, S2, S3, K0, K1, K2, K3;
         {
             uint32_t V0, V1, V2, V3, D0;
@@ -451,50 +460,28 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             {
                 min_d = load_pred(static_cast<int32_t>(rec.x & 0xffffu), V0, V1, V2, V3, D0); // row 0 for a source node
             }
-            const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
-            const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
-            const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
-            const uint32_t dq3 = __viaddmax_s16x2(V2, Q3, NEG2);
-            if (pc <= 1)
+            uint32_t I0 = 0u, I1 = 0u, I2 = 0u, I3 = 0u, ID = 0u; // slot of the first predecessor that attains V_i / D0
+            if (pc > 1)
             {
-                S0 = __viaddmax_s16x2(V0, gapv, dq0);
-                S1 = __viaddmax_s16x2(V1, gapv, dq1);
-                S2 = __viaddmax_s16x2(V2, gapv, dq2);
-                S3 = __viaddmax_s16x2(V3, gapv, dq3);
-                K0 = vminu2_1(S0 ^ dq0); // 0: the diagonal explains the cell, 1: only the vertical move does
-                K1 = vminu2_1(S1 ^ dq1);
-                K2 = vminu2_1(S2 ^ dq2);
-                K3 = vminu2_1(S3 ^ dq3);
-            }
-            else
-            {
-                // several predecessors: the best diagonal and the best vertical candidate with the slot of the FIRST
-                // predecessor that attains each (the reference tries predecessors in slot order)
-                uint32_t bD0 = dq0, bD1 = dq1, bD2 = dq2, bD3 = dq3;
-                uint32_t bV0 = __viaddmax_s16x2(V0, gapv, NEG2), bV1 = __viaddmax_s16x2(V1, gapv, NEG2),
-                         bV2 = __viaddmax_s16x2(V2, gapv, NEG2), bV3 = __viaddmax_s16x2(V3, gapv, NEG2);
-                uint32_t iD0, iD1, iD2, iD3, iV0, iV1, iV2, iV3;
+                uint32_t W0, W1, W2, W3, WD;
                 {
-                    // predecessor 1: the slot index is just "strictly better than predecessor 0"
-                    const int32_t d = load_pred(static_cast<int32_t>(rec.x >> 16), V0, V1, V2, V3, D0);
+                    // predecessor 1: the slot is just "strictly better than predecessor 0"
+                    const int32_t d = load_pred(static_cast<int32_t>(rec.x >> 16), W0, W1, W2, W3, WD);
                     min_d           = min(min_d, d);
                     auto second = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb = __vmaxs2(bestv, cand);
                         idx               = vminu2_1(nb ^ bestv);
                         bestv             = nb;
                     };
-                    second(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
-                    second(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));
-                    second(bD2, iD2, __viaddmax_s16x2(V1, Q2, NEG2));
-                    second(bD3, iD3, __viaddmax_s16x2(V2, Q3, NEG2));
-                    second(bV0, iV0, __viaddmax_s16x2(V0, gapv, NEG2));
-                    second(bV1, iV1, __viaddmax_s16x2(V1, gapv, NEG2));
-                    second(bV2, iV2, __viaddmax_s16x2(V2, gapv, NEG2));
-                    second(bV3, iV3, __viaddmax_s16x2(V3, gapv, NEG2));
+                    second(V0, I0, W0);
+                    second(V1, I1, W1);
+                    second(V2, I2, W2);
+                    second(V3, I3, W3);
+                    second(D0, ID, WD);
                 }
                 for (int32_t p = 2; p < pc; p++)
                 {
-                    const int32_t d = load_pred(record_pred_row<IdT>(g, rec.x, rec.y, r, p), V0, V1, V2, V3, D0);
+                    const int32_t d = load_pred(record_pred_row<IdT>(g, rec.x, rec.y, r, p), W0, W1, W2, W3, WD);
                     min_d           = min(min_d, d);
                     const uint32_t pp = pack2(p, p);
                     auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
@@ -503,25 +490,37 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                         idx                = (idx & ~chg) | (pp & chg);      // (first slot wins ties)
                         bestv              = nb;
                     };
-                    better(bD0, iD0, __viaddmax_s16x2(D0, Q0, NEG2));
-                    better(bD1, iD1, __viaddmax_s16x2(V0, Q1, NEG2));
-                    better(bD2, iD2, __viaddmax_s16x2(V1, Q2, NEG2));
-                    better(bD3, iD3, __viaddmax_s16x2(V2, Q3, NEG2));
-                    better(bV0, iV0, __viaddmax_s16x2(V0, gapv, NEG2));
-                    better(bV1, iV1, __viaddmax_s16x2(V1, gapv, NEG2));
-                    better(bV2, iV2, __viaddmax_s16x2(V2, gapv, NEG2));
-                    better(bV3, iV3, __viaddmax_s16x2(V3, gapv, NEG2));
+                    better(V0, I0, W0);
+                    better(V1, I1, W1);
+                    better(V2, I2, W2);
+                    better(V3, I3, W3);
+                    better(D0, ID, WD);
                 }
-                auto join = [&](uint32_t& S, uint32_t& K, uint32_t bD, uint32_t iD, uint32_t bV, uint32_t iV) {
-                    S                   = __vmaxs2(bD, bV);
-                    const uint32_t vert = vminu2_1(S ^ bD); // 1 where no diagonal candidate reaches S
-                    const uint32_t vm   = vert * 0xffffu;
-                    K                   = vert + 4u * ((iD & ~vm) | (iV & vm));
+            }
+            const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
+            const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
+            const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
+            const uint32_t dq3 = __viaddmax_s16x2(V2, Q3, NEG2);
+            S0 = __viaddmax_s16x2(V0, gapv, dq0);
+            S1 = __viaddmax_s16x2(V1, gapv, dq1);
+            S2 = __viaddmax_s16x2(V2, gapv, dq2);
+            S3 = __viaddmax_s16x2(V3, gapv, dq3);
+            K0 = vminu2_1(S0 ^ dq0); // 0: a diagonal move explains the cell, 1: only a vertical move does
+            K1 = vminu2_1(S1 ^ dq1);
+            K2 = vminu2_1(S2 ^ dq2);
+            K3 = vminu2_1(S3 ^ dq3);
+            if (pc > 1)
+            {
+                // the slot: that of the diagonal operand (the cell to the left: register i - 1, the corner register for
+                // i == 0) or of the vertical operand
+                auto slot = [&](uint32_t& K, uint32_t iD, uint32_t iV) {
+                    const uint32_t vm = K * 0xffffu;
+                    K += 4u * ((iD & ~vm) | (iV & vm));
                 };
-                join(S0, K0, bD0, iD0, bV0, iV0);
-                join(S1, K1, bD1, iD1, bV1, iV1);
-                join(S2, K2, bD2, iD2, bV2, iV2);
-                join(S3, K3, bD3, iD3, bV3, iV3);
+                slot(K0, ID, I0);
+                slot(K1, I0, I1);
+                slot(K2, I1, I2);
+                slot(K3, I2, I3);
             }
         }
         // every predecessor wholly left of this row's band: sentinel arithmetic would decide the row
