@@ -32,6 +32,12 @@ constexpr int32_t kProfRows      = 4;  // distinct read bases the profile holds
 constexpr uint32_t kRecChain     = 1u << 24; // record.z: predecessor 0 is the previous row and the band did not move
 constexpr uint32_t kRecSink      = 1u << 25; //           the row's node has no out-edge
 constexpr uint32_t kRecSpill     = 1u << 26; //           a later row reads this row from beyond the ring
+constexpr uint32_t kRecMulti     = 1u << 27; //           more than one predecessor
+constexpr uint32_t kRecWide      = 1u << 28; //           more than kWidePreds predecessors (a code byte per cell)
+constexpr uint32_t kRecFar0      = 1u << 29; //           predecessor 0 / 1 / 2 is read from its spilled copy (beyond the
+constexpr uint32_t kRecFar1      = 1u << 30; //           ring, or row 0); predecessor 3: bit 22
+constexpr uint32_t kRecFar2      = 1u << 31;
+constexpr uint32_t kRecFar3      = 1u << 22;
 constexpr int32_t kDescBufBytes  = 32 * 16;  // descriptor records of 32 rows
 constexpr int32_t kMoveDiag      = 0;
 constexpr int32_t kMoveVert      = 1;
@@ -161,6 +167,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         far_mark[r] = 0;
     __syncwarp();
     bool foreign = false; // a graph base the read does not have, and no spare profile row for it
+    bool apart   = false; // a row none of whose predecessors' bands overlaps its own: sentinel arithmetic would decide it
     {
         constexpr int32_t kPre = 4;
         for (int32_t rb = 1; rb <= node_count; rb += 32 * kPre)
@@ -207,23 +214,40 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     uint32_t z        = zw[u] + (REBASED ? 0u : static_cast<uint32_t>(bs)); // sliding window: bs is added at use
                     if (r > 1 && static_cast<int32_t>(pr[0]) == r - 1 && bs == bsp)
                         z |= kRecChain;
-                    records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs));
-                    // predecessors the ring (rows r - 8 .. r - 1) will no longer hold; row 0 is always in slot 0
+                    if (pc[u] > 1u)
+                        z |= kRecMulti;
+                    if (pc[u] > static_cast<uint32_t>(kWidePreds))
+                        z |= kRecWide;
+                    // predecessors the ring (rows r - 8 .. r - 1) will no longer hold; row 0 is always in slot 0.
+                    // min_d: the smallest band shift against a predecessor (a node without in-edges reads row 0).
+                    int32_t min_d = (pc[u] == 0u) ? bs : INT32_MAX;
 #pragma unroll
                     for (int k = 0; k < 4; k++)
-                        if (static_cast<uint32_t>(k) < pc[u] && static_cast<int32_t>(pr[k]) < r - kRingRows && pr[k] != 0u)
-                            far_mark[pr[k]] = 1;
+                    {
+                        const bool have = static_cast<uint32_t>(k) < pc[u] || k == 0;
+                        if (have && (static_cast<int32_t>(pr[k]) < r - kRingRows || pr[k] == 0u))
+                        {
+                            z |= (k == 0) ? kRecFar0 : (k == 1) ? kRecFar1 : (k == 2) ? kRecFar2 : kRecFar3;
+                            if (pr[k] != 0u)
+                                far_mark[pr[k]] = 1;
+                        }
+                        if (static_cast<uint32_t>(k) < pc[u])
+                            min_d = min(min_d, bs - (FULL ? 0 : band_start(static_cast<int32_t>(pr[k]), gradient, kFastBand, max_column)));
+                    }
                     for (uint32_t k = 4; k < pc[u]; k++)
                     {
                         const int32_t p = g.pos[g.in_edge(node[u], static_cast<int32_t>(k))] + 1;
                         if (p < r - kRingRows)
                             far_mark[p] = 1;
+                        min_d = min(min_d, bs - (FULL ? 0 : band_start(p, gradient, kFastBand, max_column)));
                     }
+                    apart |= min_d > kFastBand;
+                    records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs));
                 }
             }
         }
     }
-    if (__any_sync(kFull, foreign))
+    if (__any_sync(kFull, foreign || apart))
         return kFastNotTaken;
     {
         int32_t used = 1; // slot 0: row 0
@@ -263,8 +287,6 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const uint32_t gapv   = pack2(gap, gap);
     const uint32_t prof_l = prof + 8u * static_cast<uint32_t>(lane);
     const uint32_t ring_l = ring + 16u + 16u * static_cast<uint32_t>(lane); // this lane's cell block in ring row 0
-    uint8_t* code_lane4   = codes + 4 * lane; // nibble rows: one word per lane
-    uint8_t* code_lane8   = codes + 8 * lane; // byte rows: two words per lane
 
     const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
     int32_t best = best_floor, best_row = 0;
@@ -288,23 +310,26 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     int32_t nedge = (FULL && chunk > 0) ? __ldcg(edge_cell + min(1 + lane, node_count)) : 0;
     int32_t cedge = 0;
 
-    for (int32_t r = 1; r <= node_count; r++)
+    // codes of the row in hand: nibble rows one word per lane (byte rows: two words, at + 4 * lane from here)
+    uint8_t* code_at = codes + (FULL ? static_cast<int64_t>(chunk) * (node_count + 1) + 1 : static_cast<int64_t>(1)) * kCodeRowBytes + 4 * lane;
+
+    for (int32_t r0 = 1; r0 <= node_count; r0 += 32)
     {
-        const int32_t k = (r - 1) & 31;
-        if (k == 0) // the lanes hand over the records of rows r .. r + 31 and fetch the next 32
+        // the lanes hand over the records of rows r0 .. r0 + 31 and fetch the next 32
+        sts_v4(dbuf + 16u * static_cast<uint32_t>(lane), nrec);
+        __syncwarp();
+        nrec = records[min(r0 + 32 + lane, node_count)];
+        if (FULL && chunk > 0)
         {
-            sts_v4(dbuf + 16u * static_cast<uint32_t>(lane), nrec);
-            __syncwarp();
-            nrec = records[min(r + 32 + lane, node_count)];
-            if (FULL && chunk > 0)
-            {
-                cedge = nedge;
-                nedge = __ldcg(edge_cell + min(r + 32 + lane, node_count));
-            }
+            cedge = nedge;
+            nedge = __ldcg(edge_cell + min(r0 + 32 + lane, node_count));
         }
-        const uint4 rec = lds_v4(dbuf + 16u * static_cast<uint32_t>(k)); // broadcast
+        const int32_t r_end = min(r0 + 31, node_count);
+        uint32_t rec_at     = dbuf;
+    for (int32_t r = r0; r <= r_end; r++, rec_at += 16u, code_at += kCodeRowBytes)
+    {
+        const uint4 rec = lds_v4(rec_at); // broadcast
         const int32_t bs = FULL ? chunk_bs : static_cast<int32_t>(rec.w & 0xffffu);
-        const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
 
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
         uint32_t Q0, Q1, Q2, Q3;
@@ -338,19 +363,17 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             Q3                = prmt(lo, hi, 0xF7B3u);
         }
 
-        int32_t min_d     = 0;         // smallest band shift over the predecessors
-        int32_t left_best = INT16_MIN; // max over predecessors of their column-0 value (rows with bs == 0)
-
         // One predecessor row from the ring or from its spilled copy: its cells under this lane's cells (V_i) and the
         // corner (D0 = (corner, V3.lo)); the diagonal operands are D_i = V_{i-1}.  All branches are warp-uniform.
-        auto load_pred = [&](int32_t prow, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) -> int32_t {
+        // (The corner of lane 0 is the predecessor's left boundary while the bands have not moved: the maximum over the
+        // predecessors' corners is what this row's own left boundary follows from.)
+        auto load_pred = [&](int32_t prow, bool far, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) {
             int32_t d;
-            if (prow >= r - kRingRows && prow > 0) // shared-memory ring: rows r - 8 .. r - 1
+            if (!far) // shared-memory ring: rows r - 8 .. r - 1
             {
                 POA_COUNT("fill2.pred_ring");
                 const uint32_t pa_ = ring + static_cast<uint32_t>((prow & (kRingRows - 1)) * (kFastRowWords * 4));
-                const uint4 lead   = lds_v4(pa_);
-                d                  = bs - static_cast<int32_t>(lead.x); // >= 0, multiple of 4
+                d                  = bs - static_cast<int32_t>(lds_u32(pa_)); // lead block: band start; >= 0, multiple of 4
                 const int32_t su   = lane + 1 + (d >> 3);               // block of the first vertical operand
                 const uint4 a      = lds_v4(pa_ + 16u * min(su, kPadBlock));
                 if (d & 4)
@@ -375,7 +398,6 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     V3                = a.w;
                     D0                = __byte_perm(wv, V3, 0x5432);
                 }
-                left_best = max(left_best, hi16(lead.w));
             }
             else // far predecessor: its spilled copy (through L2); pad blocks are implied
             {
@@ -408,7 +430,6 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 V2                  = __byte_perm(a.z, b.z, selV);
                 V3                  = __byte_perm(a.w, b.w, selV);
                 D0                  = __byte_perm(odd ? a.w : wv, V3, odd ? 0x5410u : 0x5432u);
-                left_best           = max(left_best, hi16(lead.w));
             }
             if (REBASED && d != 0)
             {
@@ -424,7 +445,6 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 V3                 = __vadd2(__vmaxs2(V3, fl), c2_);
                 D0                 = __vadd2(__vmaxs2(D0, fl), c2_);
             }
-            return d;
         };
 
         // S_i: best diagonal / vertical candidate per cell; K_i: its move code (kind | predecessor slot << 2) under the
@@ -439,6 +459,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         // makes equal can get another slot than a candidate-wise comparison would give them; a walk never enters
         // sentinel cells.)
         uint32_t S0, S1, S2, S3, K0, K1, K2, K3;
+        int32_t left_t; // this row's left boundary in the tilted domain; LANE 0 holds it, the other lanes do not use it
         {
             uint32_t V0, V1, V2, V3, D0;
             if (rec.z & kRecChain)
@@ -454,20 +475,19 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 if (lane == 0)
                     X = static_cast<uint32_t>(prev_left_t) << 16;
                 D0        = __byte_perm(X, V3, 0x5432);
-                left_best = prev_left_t;
             }
             else
             {
-                min_d = load_pred(static_cast<int32_t>(rec.x & 0xffffu), V0, V1, V2, V3, D0); // row 0 for a source node
+                load_pred(static_cast<int32_t>(rec.x & 0xffffu), (rec.z & kRecFar0) != 0u, V0, V1, V2, V3, D0); // row 0 for a source node
             }
             uint32_t I0 = 0u, I1 = 0u, I2 = 0u, I3 = 0u, ID = 0u; // slot of the first predecessor that attains V_i / D0
-            if (pc > 1)
+            if (rec.z & kRecMulti)
             {
+                const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
                 uint32_t W0, W1, W2, W3, WD;
                 {
                     // predecessor 1: the slot is just "strictly better than predecessor 0"
-                    const int32_t d = load_pred(static_cast<int32_t>(rec.x >> 16), W0, W1, W2, W3, WD);
-                    min_d           = min(min_d, d);
+                    load_pred(static_cast<int32_t>(rec.x >> 16), (rec.z & kRecFar1) != 0u, W0, W1, W2, W3, WD);
                     auto second = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb = __vmaxs2(bestv, cand);
                         idx               = vminu2_1(nb ^ bestv);
@@ -481,8 +501,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 }
                 for (int32_t p = 2; p < pc; p++)
                 {
-                    const int32_t d = load_pred(record_pred_row<IdT>(g, rec.x, rec.y, r, p), W0, W1, W2, W3, WD);
-                    min_d           = min(min_d, d);
+                    const int32_t prow = record_pred_row<IdT>(g, rec.x, rec.y, r, p);
+                    load_pred(prow, prow < r - kRingRows || prow == 0, W0, W1, W2, W3, WD);
                     const uint32_t pp = pack2(p, p);
                     auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb  = __vmaxs2(bestv, cand);
@@ -497,6 +517,9 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     better(D0, ID, WD);
                 }
             }
+            // left boundary (a vertical move in the column left of the band while the band starts at column 0; the
+            // sentinel afterwards): lane 0's corner is the best boundary among the predecessors (row 0's is 0)
+            left_t = (bs == 0) ? lo16(__viaddmax_s16x2(D0, gapv, NEG2)) : kNegT;
             const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
             const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
             const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
@@ -509,7 +532,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             K1 = vminu2_1(S1 ^ dq1);
             K2 = vminu2_1(S2 ^ dq2);
             K3 = vminu2_1(S3 ^ dq3);
-            if (pc > 1)
+            if (rec.z & kRecMulti)
             {
                 // the slot: that of the diagonal operand (the cell to the left: register i - 1, the corner register for
                 // i == 0) or of the vertical operand
@@ -523,14 +546,9 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 slot(K3, I2, I3);
             }
         }
-        // every predecessor wholly left of this row's band: sentinel arithmetic would decide the row
-        if (min_d > kFastBand)
-            return kFastNotTaken;
-
-        // left boundary of this row in the tilted domain (a source node's predecessor is row 0, whose boundary is 0)
-        int32_t left_t = (bs == 0) ? static_cast<int32_t>(static_cast<int16_t>(left_best + gap)) : kNegT;
+        // (a row every predecessor of which lies wholly left of its band was found by the pre-pass)
         if (FULL && chunk > 0)
-            left_t = __shfl_sync(kFull, cedge, k); // this row's cell at column 256 * chunk, from the pass before
+            left_t = __shfl_sync(kFull, cedge, r - r0); // this row's cell at column 256 * chunk, from the pass before
 
         // horizontal pass = prefix maximum, both halves at once
         const uint32_t P1 = __vmaxs2(S1, S0);
@@ -582,19 +600,18 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         K1 += 2u * vminu2_1(out.y ^ S1);
         K2 += 2u * vminu2_1(out.z ^ S2);
         K3 += 2u * vminu2_1(out.w ^ S3);
-        POA_COUNT(pc <= 1 ? "fill2.rows_1pred" : pc <= kWidePreds ? "fill2.rows_2to4pred" : "fill2.rows_wide");
-        const int64_t code_row = (FULL ? static_cast<int64_t>(chunk) * (node_count + 1) + r : static_cast<int64_t>(r)) * kCodeRowBytes;
-        if (pc <= kWidePreds)
+        POA_COUNT(!(rec.z & kRecMulti) ? "fill2.rows_1pred" : !(rec.z & kRecWide) ? "fill2.rows_2to4pred" : "fill2.rows_wide");
+        if (!(rec.z & kRecWide))
         {
             // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
             const uint32_t w = K0 + 16u * K1 + 256u * K2 + 4096u * K3;
-            __stcg(reinterpret_cast<uint32_t*>(code_lane4 + code_row), w);
+            __stcg(reinterpret_cast<uint32_t*>(code_at), w);
         }
         else
         {
             const uint32_t t01 = __byte_perm(K0, K1, 0x6240); // c0 c1 c4 c5
             const uint32_t t23 = __byte_perm(K2, K3, 0x6240); // c2 c3 c6 c7
-            __stcg(reinterpret_cast<uint2*>(code_lane8 + code_row),
+            __stcg(reinterpret_cast<uint2*>(code_at + 4 * lane),
                    make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
         }
 
@@ -628,7 +645,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 }
                 else if (read_len == 0 || c == -1)
                 {
-                    t = static_cast<int16_t>(left_t);
+                    t = static_cast<int16_t>(__shfl_sync(kFull, left_t, 0));
                 }
                 if (t <= kNegThreshold)
                     t = kNegT;
@@ -651,6 +668,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         prev_left_t = left_t;
         __syncwarp();
     }
+    } // 32 rows
     } // chunk
 
     if (unranked)
