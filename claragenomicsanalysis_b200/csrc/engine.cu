@@ -790,6 +790,7 @@ void B200Batch::launch()
     P.max_reads           = std::max(max_sequences_per_poa_, 1);
     P.band                = batch_size_.alignment_band_width;
     P.gap                 = gap_;
+    P.gap_x2              = (static_cast<uint32_t>(P.gap) & 0xffffu) * 0x10001u;
     P.mismatch            = mismatch_;
     P.match               = match_;
     P.smem_per_warp       = kSmemPerWarp;

@@ -312,6 +312,7 @@ extern "C" int32_t cudapoa_b200_consensus_noalloc(int32_t device_id, void* strea
     P.max_reads           = max_sequences_per_poa;
     P.band                = bs.alignment_band_width;
     P.gap                 = gap_score;
+    P.gap_x2              = (static_cast<uint32_t>(P.gap) & 0xffffu) * 0x10001u;
     P.mismatch            = mismatch_score;
     P.match               = match_score;
     P.spoa_accurate       = 0;

@@ -65,6 +65,31 @@ __device__ __forceinline__ uint32_t vminu2_1(uint32_t x) // per half: 0 if zero,
 {
     return __vminu2(x, 0x00010001u);
 }
+// a * b + c as an integer multiply-add: the fill's row loop is bound by the integer ALU pipe (logic, permutes, packed
+// min / max), so additions and subtractions that can be phrased this way go to the other pipe (IMAD).
+__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c)
+{
+#ifdef POA_EMU
+    return a * b + c;
+#else
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#endif
+}
+// Per half: 1 where the two differ, else 0.
+__device__ __forceinline__ uint32_t grew2(uint32_t hi, uint32_t lo)
+{
+    return vminu2_1(hi ^ lo);
+}
+// Byte codes of a row with more than kWidePreds predecessors (rare; out of line so that the row loop does not carry
+// its instructions under a predicate).
+POA_NOINLINE __device__ void store_wide_codes(uint8_t* at, uint32_t K0, uint32_t K1, uint32_t K2, uint32_t K3)
+{
+    const uint32_t t01 = __byte_perm(K0, K1, 0x6240); // c0 c1 c4 c5
+    const uint32_t t23 = __byte_perm(K2, K3, 0x6240); // c2 c3 c6 c7
+    __stcg(reinterpret_cast<uint2*>(at), make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
+}
 
 // Row of predecessor p of row `row` from its record; slots beyond the fourth are looked up in the graph.
 template <typename IdT>
@@ -91,7 +116,7 @@ template <typename IdT, bool REBASED, bool FULL = false>
 __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                               uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
                               int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t& start_score,
-                              int32_t beta_arg)
+                              int32_t beta_arg, uint32_t gapv)
 {
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
@@ -284,7 +309,6 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     }
     __syncwarp();
 
-    const uint32_t gapv   = pack2(gap, gap);
     const uint32_t prof_l = prof + 8u * static_cast<uint32_t>(lane);
     const uint32_t ring_l = ring + 16u + 16u * static_cast<uint32_t>(lane); // this lane's cell block in ring row 0
 
@@ -303,8 +327,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             __stcg(reinterpret_cast<uint4*>(spill), make_uint4(static_cast<uint32_t>(chunk_bs), 0u, 0u, 0u));
         __syncwarp();
     }
-    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last and its left boundary
-    int32_t prev_left_t = 0;
+    uint4 prev_out      = make_uint4(0u, 0u, 0u, 0u); // cells of the row written last and its left boundary (high half)
+    uint32_t prev_left  = 0u;
     // records of the next 32 rows, one per lane, loaded a chunk ahead (FULL: and their left-edge cells)
     uint4 nrec    = records[min(1 + lane, node_count)];
     int32_t nedge = (FULL && chunk > 0) ? __ldcg(edge_cell + min(1 + lane, node_count)) : 0;
@@ -459,7 +483,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         // makes equal can get another slot than a candidate-wise comparison would give them; a walk never enters
         // sentinel cells.)
         uint32_t S0, S1, S2, S3, K0, K1, K2, K3;
-        int32_t left_t; // this row's left boundary in the tilted domain; LANE 0 holds it, the other lanes do not use it
+        uint32_t left_hi; // this row's left boundary in the tilted domain, in the HIGH half; LANE 0 holds it, the other
+                          // lanes do not use theirs
         {
             uint32_t V0, V1, V2, V3, D0;
             if (rec.z & kRecChain)
@@ -473,24 +498,46 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 V3 = prev_out.w;
                 uint32_t X = __shfl_up_sync(kFull, prev_out.w, 1);
                 if (lane == 0)
-                    X = static_cast<uint32_t>(prev_left_t) << 16;
+                    X = prev_left;
                 D0        = __byte_perm(X, V3, 0x5432);
             }
             else
             {
                 load_pred(static_cast<int32_t>(rec.x & 0xffffu), (rec.z & kRecFar0) != 0u, V0, V1, V2, V3, D0); // row 0 for a source node
             }
-            uint32_t I0 = 0u, I1 = 0u, I2 = 0u, I3 = 0u, ID = 0u; // slot of the first predecessor that attains V_i / D0
-            if (rec.z & kRecMulti)
+            // candidates, vertical-or-diagonal kind (0: a diagonal move explains the cell, 1: only a vertical move does)
+            // and the left boundary (a vertical move in the column left of the band while the band starts at column 0,
+            // the sentinel afterwards: lane 0's corner is the best boundary among the predecessors, row 0's being 0)
+            auto cells = [&]() {
+                left_hi = (bs == 0) ? (__viaddmax_s16x2(D0, gapv, NEG2) << 16) : (static_cast<uint32_t>(kNegT) << 16);
+                const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
+                const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
+                const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
+                const uint32_t dq3 = __viaddmax_s16x2(V2, Q3, NEG2);
+                S0 = __viaddmax_s16x2(V0, gapv, dq0);
+                S1 = __viaddmax_s16x2(V1, gapv, dq1);
+                S2 = __viaddmax_s16x2(V2, gapv, dq2);
+                S3 = __viaddmax_s16x2(V3, gapv, dq3);
+                K0 = grew2(S0, dq0);
+                K1 = grew2(S1, dq1);
+                K2 = grew2(S2, dq2);
+                K3 = grew2(S3, dq3);
+            };
+            if (!(rec.z & kRecMulti))
+            {
+                cells();
+            }
+            else
             {
                 const int32_t pc = static_cast<int32_t>((rec.z >> 16) & 0x3fu);
+                uint32_t I0, I1, I2, I3, ID; // slot of the first predecessor that attains V_i / D0
                 uint32_t W0, W1, W2, W3, WD;
                 {
                     // predecessor 1: the slot is just "strictly better than predecessor 0"
                     load_pred(static_cast<int32_t>(rec.x >> 16), (rec.z & kRecFar1) != 0u, W0, W1, W2, W3, WD);
                     auto second = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb = __vmaxs2(bestv, cand);
-                        idx               = vminu2_1(nb ^ bestv);
+                        idx               = grew2(nb, bestv);
                         bestv             = nb;
                     };
                     second(V0, I0, W0);
@@ -506,8 +553,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     const uint32_t pp = pack2(p, p);
                     auto better = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb  = __vmaxs2(bestv, cand);
-                        const uint32_t chg = vminu2_1(nb ^ bestv) * 0xffffu; // 0xffff where cand is strictly better
-                        idx                = (idx & ~chg) | (pp & chg);      // (first slot wins ties)
+                        const uint32_t chg = grew2(nb, bestv) * 0xffffu; // 0xffff where cand is strictly better
+                        idx                = (idx & ~chg) | (pp & chg);   // (first slot wins ties)
                         bestv              = nb;
                     };
                     better(V0, I0, W0);
@@ -516,29 +563,12 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     better(V3, I3, W3);
                     better(D0, ID, WD);
                 }
-            }
-            // left boundary (a vertical move in the column left of the band while the band starts at column 0; the
-            // sentinel afterwards): lane 0's corner is the best boundary among the predecessors (row 0's is 0)
-            left_t = (bs == 0) ? lo16(__viaddmax_s16x2(D0, gapv, NEG2)) : kNegT;
-            const uint32_t dq0 = __viaddmax_s16x2(D0, Q0, NEG2);
-            const uint32_t dq1 = __viaddmax_s16x2(V0, Q1, NEG2);
-            const uint32_t dq2 = __viaddmax_s16x2(V1, Q2, NEG2);
-            const uint32_t dq3 = __viaddmax_s16x2(V2, Q3, NEG2);
-            S0 = __viaddmax_s16x2(V0, gapv, dq0);
-            S1 = __viaddmax_s16x2(V1, gapv, dq1);
-            S2 = __viaddmax_s16x2(V2, gapv, dq2);
-            S3 = __viaddmax_s16x2(V3, gapv, dq3);
-            K0 = vminu2_1(S0 ^ dq0); // 0: a diagonal move explains the cell, 1: only a vertical move does
-            K1 = vminu2_1(S1 ^ dq1);
-            K2 = vminu2_1(S2 ^ dq2);
-            K3 = vminu2_1(S3 ^ dq3);
-            if (rec.z & kRecMulti)
-            {
+                cells();
                 // the slot: that of the diagonal operand (the cell to the left: register i - 1, the corner register for
                 // i == 0) or of the vertical operand
                 auto slot = [&](uint32_t& K, uint32_t iD, uint32_t iV) {
                     const uint32_t vm = K * 0xffffu;
-                    K += 4u * ((iD & ~vm) | (iV & vm));
+                    K                 = mad_u32((iD & ~vm) | (iV & vm), 4u, K);
                 };
                 slot(K0, ID, I0);
                 slot(K1, I0, I1);
@@ -548,7 +578,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         }
         // (a row every predecessor of which lies wholly left of its band was found by the pre-pass)
         if (FULL && chunk > 0)
-            left_t = __shfl_sync(kFull, cedge, r - r0); // this row's cell at column 256 * chunk, from the pass before
+            left_hi = static_cast<uint32_t>(__shfl_sync(kFull, cedge, r - r0)) << 16; // this row's cell at column 256 * chunk, from the pass before
 
         // horizontal pass = prefix maximum, both halves at once
         const uint32_t P1 = __vmaxs2(S1, S0);
@@ -560,7 +590,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         {
             uint32_t e = __shfl_up_sync(kFull, tot, 1);
             if (lane == 0)
-                e = static_cast<uint32_t>(left_t) << 16;
+                e = left_hi;
             uint32_t u;
             u = __shfl_up_sync(kFull, e, 1);
             e = __vmaxs2(e, u); // lanes below the shift receive their own value: harmless for a maximum
@@ -596,28 +626,25 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             }
         }
         // move codes: a cell whose value exceeds its own candidate was reached horizontally
-        K0 += 2u * vminu2_1(out.x ^ S0);
-        K1 += 2u * vminu2_1(out.y ^ S1);
-        K2 += 2u * vminu2_1(out.z ^ S2);
-        K3 += 2u * vminu2_1(out.w ^ S3);
+        K0 = mad_u32(grew2(out.x, S0), 2u, K0);
+        K1 = mad_u32(grew2(out.y, S1), 2u, K1);
+        K2 = mad_u32(grew2(out.z, S2), 2u, K2);
+        K3 = mad_u32(grew2(out.w, S3), 2u, K3);
         POA_COUNT(!(rec.z & kRecMulti) ? "fill2.rows_1pred" : !(rec.z & kRecWide) ? "fill2.rows_2to4pred" : "fill2.rows_wide");
         if (!(rec.z & kRecWide))
         {
             // nibble k of the lane's word = cell k (low half-word: cells 0..3, high: cells 4..7)
-            const uint32_t w = K0 + 16u * K1 + 256u * K2 + 4096u * K3;
+            const uint32_t w = mad_u32(K3, 4096u, mad_u32(K2, 256u, mad_u32(K1, 16u, K0)));
             __stcg(reinterpret_cast<uint32_t*>(code_at), w);
         }
         else
         {
-            const uint32_t t01 = __byte_perm(K0, K1, 0x6240); // c0 c1 c4 c5
-            const uint32_t t23 = __byte_perm(K2, K3, 0x6240); // c2 c3 c6 c7
-            __stcg(reinterpret_cast<uint2*>(code_at + 4 * lane),
-                   make_uint2(__byte_perm(t01, t23, 0x5410), __byte_perm(t01, t23, 0x7632)));
+            store_wide_codes(code_at + 4 * lane, K0, K1, K2, K3);
         }
 
         const uint32_t rrow = static_cast<uint32_t>((r & (kRingRows - 1)) * (kFastRowWords * 4));
         sts_v4(ring_l + rrow, out);
-        const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, static_cast<uint32_t>(left_t) << 16);
+        const uint4 lead = make_uint4(static_cast<uint32_t>(bs), 0u, 0u, left_hi);
         if (lane == 0)
             sts_v4(ring + rrow, lead);
         if (rec.z & (kRecSpill | kRecSink))
@@ -645,7 +672,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 }
                 else if (read_len == 0 || c == -1)
                 {
-                    t = static_cast<int16_t>(__shfl_sync(kFull, left_t, 0));
+                    t = hi16(__shfl_sync(kFull, left_hi, 0));
                 }
                 if (t <= kNegThreshold)
                     t = kNegT;
@@ -665,7 +692,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         if (FULL && chunk + 1 < n_chunks && lane == 31)
             __stcg(edge_cell + r, hi16(out.w)); // the row's cell at column 256 * (chunk + 1)
         prev_out    = out;
-        prev_left_t = left_t;
+        prev_left   = left_hi;
         __syncwarp();
     }
     } // 32 rows

@@ -103,6 +103,7 @@ struct KernelParams
     int32_t max_reads;
     int32_t band;
     int32_t gap, mismatch, match;
+    uint32_t gap_x2;       // the gap score in both 16-bit halves (operand of the packed fill)
     int32_t spoa_accurate;
     int32_t* next_window; // zeroed before the launch; warps take window ids from it
     int32_t adaptive_max_band; // 0: static band; else the widest band the score rows can hold

@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 else if (beta == 0 &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                                P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0) == 0)
+                                                P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0, P.gap_x2) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 const int32_t beta  = fast_path_beta(st.node_count, len, kFastBand, P.gap, P.mismatch, P.match);
                 if (beta == 0 && P.smem_per_warp >= fill2_smem_bytes(len) &&
                     fill2_impl<IdT, false, true>(g, st.node_count, seq, len, area, area_bytes, P.max_nodes, P.gap, P.mismatch,
-                                                 P.match, smem, lane, start_row, start_score, 0) == 0)
+                                                 P.match, smem, lane, start_row, start_score, 0, P.gap_x2) == 0)
                     st.aln_len = kAlnPendingTraceback;
                 else
                     st.aln_len = kAlnNeedsExact;
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, 6) poa_fill_rebased_k
             beta = fast_path_rebased_beta(st.node_count, P.band, P.gap, P.mismatch, P.match);
         if (beta > 0 && fill2_impl<IdT, true>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                               P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                              P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, beta) == 0)
+                                              P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, beta, P.gap_x2) == 0)
         {
             st.aln_len   = kAlnPendingTraceback;
             st.start_row = start_row;
