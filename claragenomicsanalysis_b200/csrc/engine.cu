@@ -537,10 +537,10 @@ static int32_t blocks_cap_from_env(const char* name, int32_t fallback)
 
 template <typename Kernel>
 static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per_block, int32_t sm_count,
-                         cudaStream_t stream, int32_t blocks_cap = INT32_MAX)
+                         cudaStream_t stream, int32_t blocks_cap = INT32_MAX, size_t block_smem = 0)
 {
     const dim3 block(warps_per_block * 32);
-    const size_t smem    = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp);
+    const size_t smem    = static_cast<size_t>(warps_per_block) * static_cast<size_t>(P.smem_per_warp) + block_smem;
     const int32_t per_sm = std::min(blocks_cap, phase_blocks_per_sm(reinterpret_cast<const void*>(kernel), static_cast<int>(block.x), smem));
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
     const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
@@ -616,7 +616,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
         if (full)
         {
             // full alignment: the chunked packed fill, the exact full alignment for what it declines
-            launch_phase(poa_fill_full_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
+            launch_phase(poa_fill_full_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill, kLutBytes);
             P.next_window   = c + 2;
             P.smem_per_warp = 0;
             launch_phase(poa_exact_kernel<ScoreT, IdT, true>, P, kFillWarpsPerBlock, sm_count, stream);
@@ -624,7 +624,7 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
         }
         else
         {
-            launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill);
+            launch_phase(poa_fill_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream, cap_fill, kLutBytes);
             P.next_window   = c + 1;
             P.smem_per_warp = scratch.fill_long;
             launch_phase(poa_fill_rebased_kernel<ScoreT, IdT>, P, kFillWarpsPerBlock, sm_count, stream);

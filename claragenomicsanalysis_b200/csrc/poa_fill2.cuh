@@ -43,14 +43,36 @@ constexpr int32_t kMoveDiag      = 0;
 constexpr int32_t kMoveVert      = 1;
 constexpr int32_t kMoveHoriz     = 2;  // bit 1 set (3 also means horizontal)
 
-__host__ __device__ inline int32_t fill2_profile_stride(int32_t read_len)
+// The plain formulation keeps the profile as MATCH BITS: per distinct base of the read one bit per read position, twice
+// (copy c starts at position 4 c, so that the eight positions under a lane's cells -- band starts are multiples of 4 --
+// are one byte of one of the copies), and turns a lane's byte into its four operand registers through a 256-entry
+// table of 16 bytes that the block shares (kLutBytes behind the warps' scratch).  Bytes of one copy of one base:
+__host__ __device__ inline int32_t fill2_bits_stride(int32_t read_len)
 {
-    return (read_len + kFastBand + 8 + 15) & ~15;
+    const int32_t reach = ((read_len > kFastBand ? read_len : kFastBand) + kFastBand - 1) / kFastBand * kFastBand; // band end, full-alignment chunks included
+    return (((reach + 8 + 31) / 32) * 4 + 15) & ~15;
 }
-// Shared memory the fill needs for a read of this length: the ring, the descriptor buffer and the profile.
+constexpr int32_t kLutBytes = 256 * 16;
+// Shared memory the fill needs per warp for a read of this length: the ring, the descriptor buffer and the profile.
 __host__ __device__ inline int32_t fill2_smem_bytes(int32_t read_len)
 {
-    return kRingBytes + kDescBufBytes + kProfRows * fill2_profile_stride(read_len);
+    return kRingBytes + kDescBufBytes + kProfRows * 2 * fill2_bits_stride(read_len);
+}
+// The block's table: entry b = the operand registers Q_i = (pd(bit i), pd(bit i + 4)) of a lane whose eight positions
+// match as the bits of b say.  Every warp of the block writes all of it (the same values: no block barrier needed)
+// before its first window.
+__device__ __forceinline__ void fill2_build_lut(uint32_t lut, int32_t pd_m, int32_t pd_x, int32_t lane)
+{
+    for (int32_t b = lane; b < 256; b += 32)
+    {
+        uint32_t q[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            q[i] = (static_cast<uint32_t>(((b >> i) & 1) ? pd_m : pd_x) & 0xffffu) |
+                   (static_cast<uint32_t>(((b >> (i + 4)) & 1) ? pd_m : pd_x) << 16);
+        sts_v4(lut + 16u * static_cast<uint32_t>(b), make_uint4(q[0], q[1], q[2], q[3]));
+    }
+    __syncwarp();
 }
 // Long windows (the REBASED instance) keep a sliding window of the profile instead: kProfWindow read positions per base,
 // addressed modulo the window and refilled 256 positions at a time as the band moves right -- shared memory does not
@@ -116,12 +138,13 @@ template <typename IdT, bool REBASED, bool FULL = false>
 __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uint8_t* read, int32_t read_len,
                               uint8_t* area, int64_t area_bytes, int32_t max_nodes, int32_t gap, int32_t mismatch,
                               int32_t match, uint32_t smem, int32_t lane, int32_t& start_row, int32_t& start_score,
-                              int32_t beta_arg, uint32_t gapv)
+                              int32_t beta_arg, uint32_t gapv, uint32_t lut = 0u)
 {
+    constexpr bool BITS = !REBASED; // match-bit profile + table (plain and full); the rebased fill slides a byte profile
     const int32_t beta = REBASED ? beta_arg : 0;
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
     const int32_t pd_x = mismatch - gap; // bases differ
-    const int32_t pstride = REBASED ? kProfWindow : fill2_profile_stride(read_len);
+    const int32_t pstride = REBASED ? kProfWindow : 2 * fill2_bits_stride(read_len); // bytes per base in the profile
     if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > 65535)
         return kFastNotTaken;
     static_assert(!(FULL && REBASED), "full alignment is served by the plain formulation only");
@@ -181,8 +204,45 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 sts_u8(prof + static_cast<uint32_t>(a * pstride + at), static_cast<uint32_t>(((eq >> (8 * a)) & 1u) ? pd_m : pd_x) & 0xffu);
         }
     };
-    profile_fill(0, pstride);
     int32_t prof_loaded = pstride; // sliding window: positions below this are in the window (the last kProfWindow of them)
+    if (!BITS)
+    {
+        profile_fill(0, pstride);
+    }
+    else
+    {
+        // copy 0: one ballot per base and 32 positions; copy 1: the same bits four positions on
+        const int32_t bstride = pstride / 2;
+        const int32_t nwords  = bstride / 4;
+        for (int32_t w0 = 0; w0 < nwords; w0++)
+        {
+            const int32_t k   = 32 * w0 + lane;
+            const uint32_t b  = (k < read_len) ? read[k] : 0u;
+            const uint32_t eq = (k < read_len) ? (__vcmpeq4(alpha, b * 0x01010101u) & alpha_valid) : 0u;
+            uint32_t mine     = 0u;
+#pragma unroll
+            for (int a = 0; a < kProfRows; a++)
+            {
+                const uint32_t m = __ballot_sync(kFull, ((eq >> (8 * a)) & 1u) != 0u);
+                if (lane == a)
+                    mine = m;
+            }
+            if (lane < kProfRows)
+                sts_u32(prof + static_cast<uint32_t>(lane * pstride + 4 * w0), mine);
+        }
+        __syncwarp();
+        for (int32_t a = 0; a < kProfRows; a++)
+        {
+            const uint32_t c0 = prof + static_cast<uint32_t>(a * pstride);
+            for (int32_t wi = lane; wi < nwords; wi += 32)
+            {
+                const uint32_t lo = lds_u32(c0 + 4u * static_cast<uint32_t>(wi));
+                const uint32_t hi = (wi + 1 < nwords) ? lds_u32(c0 + 4u * static_cast<uint32_t>(wi + 1)) : 0u;
+                sts_u32(c0 + static_cast<uint32_t>(bstride) + 4u * static_cast<uint32_t>(wi), (lo >> 4) | (hi << 28));
+            }
+        }
+        __syncwarp();
+    }
 
     const int32_t max_column = read_len + 1;
     const float gradient     = band_gradient(read_len, node_count);
@@ -236,7 +296,9 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 {
                     const int32_t bs  = FULL ? 0 : band_start(r, gradient, kFastBand, max_column);
                     const int32_t bsp = FULL ? 0 : band_start(r - 1, gradient, kFastBand, max_column);
-                    uint32_t z        = zw[u] + (REBASED ? 0u : static_cast<uint32_t>(bs)); // sliding window: bs is added at use
+                    // profile address of the row: its base's bits, the copy that starts at bs mod 8, the byte of cell 0
+                    // (sliding byte window: bs is added at use)
+                    uint32_t z        = zw[u] + (REBASED ? 0u : static_cast<uint32_t>(((bs >> 2) & 1) * (pstride / 2) + (bs >> 3)));
                     if (r > 1 && static_cast<int32_t>(pr[0]) == r - 1 && bs == bsp)
                         z |= kRecChain;
                     if (pc[u] > 1u)
@@ -309,7 +371,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     }
     __syncwarp();
 
-    const uint32_t prof_l = prof + 8u * static_cast<uint32_t>(lane);
+    const uint32_t prof_l = prof + (BITS ? 1u : 8u) * static_cast<uint32_t>(lane);
     const uint32_t ring_l = ring + 16u + 16u * static_cast<uint32_t>(lane); // this lane's cell block in ring row 0
 
     const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
@@ -357,34 +419,33 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
 
         // profile registers Q_i = (pd(cell i), pd(cell i + 4)): read positions bs + 8 * lane ..
         uint32_t Q0, Q1, Q2, Q3;
+        if (BITS)
         {
-            uint32_t at_lo, at_hi;
-            if (REBASED)
+            uint32_t at = prof_l + (rec.z & 0xffffu); // the byte of match bits under this lane's cells
+            if (FULL)
+                at += static_cast<uint32_t>(chunk_bs >> 3); // the records carry band start 0
+            const uint4 q = lds_v4(lut + 16u * lds_u8(at));
+            Q0            = q.x;
+            Q1            = q.y;
+            Q2            = q.z;
+            Q3            = q.w;
+        }
+        else
+        {
+            while (bs + kFastBand > prof_loaded) // uniform; the band moved past what the window holds
             {
-                while (bs + kFastBand > prof_loaded) // uniform; the band moved past what the window holds
-                {
-                    profile_fill(prof_loaded, kFastBand);
-                    prof_loaded += kFastBand;
-                    __syncwarp();
-                }
-                const uint32_t row = prof + (rec.z & 0xffffu);
-                const uint32_t off = static_cast<uint32_t>(bs) + 8u * static_cast<uint32_t>(lane);
-                at_lo              = row + (off & (kProfWindow - 1));
-                at_hi              = row + ((off + 4u) & (kProfWindow - 1));
+                profile_fill(prof_loaded, kFastBand);
+                prof_loaded += kFastBand;
+                __syncwarp();
             }
-            else
-            {
-                at_lo = prof_l + (rec.z & 0xffffu); // profile row + band start: 4-byte aligned, not always 8
-                if (FULL)
-                    at_lo += static_cast<uint32_t>(chunk_bs); // the records carry band start 0
-                at_hi = at_lo + 4u;
-            }
-            const uint32_t lo = lds_u32(at_lo);
-            const uint32_t hi = lds_u32(at_hi);
-            Q0                = prmt(lo, hi, 0xC480u);
-            Q1                = prmt(lo, hi, 0xD591u);
-            Q2                = prmt(lo, hi, 0xE6A2u);
-            Q3                = prmt(lo, hi, 0xF7B3u);
+            const uint32_t row = prof + (rec.z & 0xffffu);
+            const uint32_t off = static_cast<uint32_t>(bs) + 8u * static_cast<uint32_t>(lane);
+            const uint32_t lo  = lds_u32(row + (off & (kProfWindow - 1)));
+            const uint32_t hi  = lds_u32(row + ((off + 4u) & (kProfWindow - 1)));
+            Q0                 = prmt(lo, hi, 0xC480u);
+            Q1                 = prmt(lo, hi, 0xD591u);
+            Q2                 = prmt(lo, hi, 0xE6A2u);
+            Q3                 = prmt(lo, hi, 0xF7B3u);
         }
 
         // One predecessor row from the ring or from its spilled copy: its cells under this lane's cells (V_i) and the

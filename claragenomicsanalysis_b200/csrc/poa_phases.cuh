@@ -25,7 +25,7 @@ constexpr int32_t kFillWarpsPerBlock  = 4;
 constexpr int32_t kGraphWarpsPerBlock = 4;
 constexpr int32_t kTileBytes          = kTileAndDescBytes; // traceback tile + its row descriptors
 #ifndef POA_FILL_MIN_BLOCKS
-#define POA_FILL_MIN_BLOCKS 6
+#define POA_FILL_MIN_BLOCKS 8
 #endif
 
 // First launch of a batch: per-window state and the backbone from read 0 (cudapoa_kernels.cuh:171-209).
@@ -64,6 +64,10 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
     asm volatile("" : "+r"(smem));
+    // the block's operand table of the match-bit profile (poa_fill2.cuh), behind the warps' scratch
+    uint32_t lut = smem_u32(smem_block) + static_cast<uint32_t>(kFillWarpsPerBlock) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lut));
+    fill2_build_lut(lut, P.match - P.gap, P.mismatch - P.gap, lane);
     const int32_t s = P.step;
 
     for (;;)
@@ -106,7 +110,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 else if (beta == 0 &&
                          fill2_impl<IdT, false>(g, st.node_count, seq, len, reinterpret_cast<uint8_t*>(scores),
                                                 P.banded_score_stride * static_cast<int64_t>(sizeof(ScoreT)), P.max_nodes,
-                                                P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0, P.gap_x2) == 0)
+                                                P.gap, P.mismatch, P.match, smem, lane, start_row, start_score, 0, P.gap_x2, lut) == 0)
                     aln_len = kAlnPendingTraceback;
                 else
                     aln_len = kAlnNeedsExact;
@@ -135,6 +139,10 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
     uint32_t smem = smem_u32(smem_block) + static_cast<uint32_t>(threadIdx.x >> 5) * static_cast<uint32_t>(P.smem_per_warp);
     asm volatile("" : "+r"(lane));
     asm volatile("" : "+r"(smem));
+    // the block's operand table of the match-bit profile (poa_fill2.cuh), behind the warps' scratch
+    uint32_t lut = smem_u32(smem_block) + static_cast<uint32_t>(kFillWarpsPerBlock) * static_cast<uint32_t>(P.smem_per_warp);
+    asm volatile("" : "+r"(lut));
+    fill2_build_lut(lut, P.match - P.gap, P.mismatch - P.gap, lane);
     const int32_t s = P.step;
     for (;;)
     {
@@ -170,7 +178,7 @@ __global__ void __launch_bounds__(kFillWarpsPerBlock * 32, POA_FILL_MIN_BLOCKS) 
                 const int32_t beta  = fast_path_beta(st.node_count, len, kFastBand, P.gap, P.mismatch, P.match);
                 if (beta == 0 && P.smem_per_warp >= fill2_smem_bytes(len) &&
                     fill2_impl<IdT, false, true>(g, st.node_count, seq, len, area, area_bytes, P.max_nodes, P.gap, P.mismatch,
-                                                 P.match, smem, lane, start_row, start_score, 0, P.gap_x2) == 0)
+                                                 P.match, smem, lane, start_row, start_score, 0, P.gap_x2, lut) == 0)
                     st.aln_len = kAlnPendingTraceback;
                 else
                     st.aln_len = kAlnNeedsExact;

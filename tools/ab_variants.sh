@@ -14,6 +14,6 @@ for v in ${VARIANTS:-A B C}; do
 done
 done
 cp /tmp/keep.so $L
-for n in ${SIZES:-17760 35520}; do
+for n in ${SIZES-17760 35520}; do
   python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-other-configs --windows $n --max-mem-gb 120 2>/dev/null | show "windows=$n"
 done

@@ -33,6 +33,12 @@ CASES = [
      dict(max_seq=2400, max_reads=6, band=256, banded=True, output="consensus"), 2),
     ("full 400x8", dict(n=2, start_index=8100, template_length=400, n_reads=8, read_error=0.15),
      dict(max_seq=512, max_reads=8, band=256, banded=False, output="consensus"), 2),
+    ("short 90x6", dict(n=3, start_index=9500, template_length=90, n_reads=6, read_error=0.15),
+     dict(max_seq=256, max_reads=6, band=256, banded=True, output="consensus"), 2),
+    ("full 700x5 (3 chunks)", dict(n=2, start_index=9600, template_length=700, n_reads=5, read_error=0.12),
+     dict(max_seq=768, max_reads=5, band=256, banded=False, output="consensus"), 2),
+    ("mixed 60..620 x 8", dict(n=6, start_index=9700, template_length=(60, 620), n_reads=8, read_error=0.15),
+     dict(max_seq=704, max_reads=8, band=256, banded=True, output="consensus"), 2),
     ("msa noisy 250x10", dict(n=2, start_index=9100, template_length=250, n_reads=10, read_error=0.2),
      dict(max_seq=384, max_reads=10, band=256, banded=True, output="msa"), 2),
 ]

@@ -29,3 +29,10 @@ for k in fill trace sort; do
 done
 fi
 ls -la gpurun_out | tail -12
+# compute-sanitizer on the smoke batch (8 windows, both schedules): memcheck and racecheck logs for profiles/
+if [ -n "$SANITIZER" ]; then
+  for tool in memcheck racecheck; do
+    timeout 900 compute-sanitizer --tool $tool --log-file gpurun_out/${TAG}_sanitizer_${tool}.log python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_sanitizer_${tool}.out 2>&1
+    echo "compute-sanitizer $tool rc=$?"; tail -3 gpurun_out/${TAG}_sanitizer_${tool}.log
+  done
+fi
