@@ -713,8 +713,13 @@ bool B200Batch::launch_split(KernelParams& P)
     // profiles/r2_other_shapes_both_schedules.txt): cfg 2 2 368 windows 35.9 against 37.3 ms, 3 552 windows 45 against
     // 68 ms (the single launch holds 16 windows per SM: a second wave); cfg 5b 2 368 windows (1 970 units) 444 against
     // 402 ms, 9 472 windows 583 against 766 ms; cfg 4 592 windows (4 190 units) 2 045 against 2 131 ms.
-    const int64_t units = num_bases_ / (static_cast<int64_t>(500) * steps);
-    if (mode == 0 && !overlapped_ && units < static_cast<int64_t>(15) * sm_count_)
+    // With the round's last fill kernel the crossover moved down for polishing-size windows, whose graphs sort out of
+    // the small shared-memory class (lone cfg 2 batches, profiles/r2s_pipeline_trace_and_crossover.txt: 592 windows 25.1
+    // against 26.5 ms, 1 184 27.0 against 29.8, 2 368 32.1 against 37.1); batches with long windows keep the old bound
+    // (cfg 5b, 2 368 windows, 1 970 units: 423 against 391 ms -- their graphs sort out of global memory).
+    const int64_t units     = num_bases_ / (static_cast<int64_t>(500) * steps);
+    const int64_t min_units = static_cast<int64_t>(batch_size_.max_sequence_size <= 1024 ? 4 : 15) * sm_count_;
+    if (mode == 0 && !overlapped_ && units < min_units)
         return false;
     if (kCountersPerStep * steps > kPhaseCounters)
         return false;

@@ -20,7 +20,10 @@
 #include <cuda_runtime_api.h>
 
 #include <algorithm>
+#include <array>
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 #include <chrono>
 #include <condition_variable>
 #include <exception>
@@ -55,6 +58,11 @@ struct cudapoa_b200_pipeline
         std::atomic<int32_t> next_chunk{0};
         bool want_msa = false;
         std::string first_error;
+        // CUDAPOA_B200_PIPELINE_TRACE=1: per chunk {worker, windows, stage start, launch start, collect start, end} in ms
+        // since the run began, printed to stderr (development: where a run's wall time goes, tools/pipeline_trace.py)
+        bool trace = false;
+        std::chrono::steady_clock::time_point t0;
+        std::vector<std::array<double, 6>> trace_rows;
     };
     std::vector<Worker> workers;
     int8_t output_mask = 1;
@@ -129,6 +137,8 @@ void work(cudapoa_b200_pipeline* p, cudapoa_b200_pipeline::Worker& wk, cudapoa_b
             while (a < b)
             {
                 int32_t added = 0;
+                auto now_ms   = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - job.t0).count(); };
+                const double t_stage = job.trace ? now_ms() : 0.0;
                 {
                     NvtxRange range("pipeline: stage");
                     wk.batch->reset();
@@ -153,10 +163,12 @@ void work(cudapoa_b200_pipeline* p, cudapoa_b200_pipeline::Worker& wk, cudapoa_b
                 }
                 if (added == 0)
                     throw std::runtime_error("pipeline: window " + std::to_string(job.order[a]) + " does not fit a batch");
+                const double t_launch = job.trace ? now_ms() : 0.0;
                 {
                     NvtxRange range("pipeline: launch");
                     wk.batch->generate_poa();
                 }
+                const double t_collect = job.trace ? now_ms() : 0.0;
                 NvtxRange range("pipeline: collect");
                 out_status.clear();
                 if (job.want_msa)
@@ -184,6 +196,12 @@ void work(cudapoa_b200_pipeline* p, cudapoa_b200_pipeline::Worker& wk, cudapoa_b
                     cudapoa_b200_stats s{};
                     src->fill_stats(&s);
                     add_stats(local, s);
+                }
+                if (job.trace)
+                {
+                    std::lock_guard<std::mutex> lock(p->mu);
+                    job.trace_rows.push_back({static_cast<double>(&wk - p->workers.data()), static_cast<double>(added), t_stage,
+                                              t_launch, t_collect, now_ms()});
                 }
                 a += added;
             }
@@ -339,6 +357,11 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
     {
         NvtxRange range("cudapoa_b200_pipeline_run");
         cudapoa_b200_pipeline::Job job;
+        const auto t_call = std::chrono::steady_clock::now();
+        {
+            const char* env = std::getenv("CUDAPOA_B200_PIPELINE_TRACE");
+            job.trace       = env != nullptr && env[0] == '1';
+        }
         job.bases          = bases;
         job.weights        = weights;
         job.read_lengths   = read_lengths;
@@ -384,6 +407,7 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
         job.chunk_end = plan_chunks(n_windows, chunk);
 
         const auto t0 = std::chrono::steady_clock::now();
+        job.t0        = t0;
         {
             std::unique_lock<std::mutex> lock(p->mu);
             p->job  = &job;
@@ -394,6 +418,16 @@ int32_t cudapoa_b200_pipeline_run(cudapoa_b200_pipeline* p, const uint8_t* bases
             p->job = nullptr;
         }
         p->wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (job.trace)
+        {
+            std::fprintf(stderr, "pipeline trace: %d windows, schedule built in %.2f ms, workers ran %.2f ms\n", n_windows,
+                         std::chrono::duration<double, std::milli>(t0 - t_call).count(), p->wall_ms);
+            std::sort(job.trace_rows.begin(), job.trace_rows.end(),
+                      [](const std::array<double, 6>& x, const std::array<double, 6>& y) { return x[2] < y[2]; });
+            for (const auto& r : job.trace_rows)
+                std::fprintf(stderr, "  worker %2d  %5d windows  stage %7.2f  launch %7.2f  collect %7.2f  end %7.2f   (stage %.2f, enqueue %.2f, wait+collect %.2f)\n",
+                             static_cast<int>(r[0]), static_cast<int>(r[1]), r[2], r[3], r[4], r[5], r[3] - r[2], r[4] - r[3], r[5] - r[4]);
+        }
         if (!job.first_error.empty())
             throw std::runtime_error(job.first_error);
         return 0;
