@@ -38,6 +38,14 @@ constexpr uint32_t kRecFar0      = 1u << 29; //           predecessor 0 / 1 / 2 
 constexpr uint32_t kRecFar1      = 1u << 30; //           ring, or row 0); predecessor 3: bit 22
 constexpr uint32_t kRecFar2      = 1u << 31;
 constexpr uint32_t kRecFar3      = 1u << 22;
+// record.z, low half: bits 0-10 the row's profile address; for predecessors 0 and 1 that sit in the ring no more than 8
+// columns to the left (every ring predecessor unless the read is much longer than the graph) the band shift in units
+// of 4 (bits 11-12, 13-14) and a flag (bit 15, bit 23) that says so: their block in the ring is precomputed in
+// record.w (bits 16-23, 24-31), and the row loop neither reads the predecessor's band start nor clamps block indices.
+constexpr uint32_t kRecProfMask  = 0x7ffu;
+constexpr int32_t kRecShift0     = 11, kRecShift1 = 13;
+constexpr uint32_t kRecFast0     = 1u << 15;
+constexpr uint32_t kRecFast1     = 1u << 23;
 constexpr int32_t kDescBufBytes  = 32 * 16;  // descriptor records of 32 rows
 constexpr int32_t kMoveDiag      = 0;
 constexpr int32_t kMoveVert      = 1;
@@ -145,7 +153,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     const int32_t pd_m = match - gap;    // diagonal step in the tilted domain, bases equal
     const int32_t pd_x = mismatch - gap; // bases differ
     const int32_t pstride = REBASED ? kProfWindow : 2 * fill2_bits_stride(read_len); // bytes per base in the profile
-    if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > 65535)
+    if (pd_m > 127 || pd_m < -128 || pd_x > 127 || pd_x < -128 || kProfRows * pstride > static_cast<int32_t>(kRecProfMask) + 1)
         return kFastNotTaken;
     static_assert(!(FULL && REBASED), "full alignment is served by the plain formulation only");
     const int32_t n_chunks    = FULL ? max((read_len + kFastBand - 1) / kFastBand, 1) : 1;
@@ -159,6 +167,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
     uint32_t* spill   = reinterpret_cast<uint32_t*>(area + code_bytes);
     uint4* records    = reinterpret_cast<uint4*>(g.rowinfo);
     uint8_t* far_mark = g.marks; // per row: a later row reads it from beyond the ring
+    uint32_t* slot_of = reinterpret_cast<uint32_t*>(g.row_bs); // ... and its spill slot (the exact path's array, free here)
 
     const uint32_t ring = smem;
     const uint32_t dbuf = ring + kRingBytes;
@@ -308,18 +317,31 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     // predecessors the ring (rows r - 8 .. r - 1) will no longer hold; row 0 is always in slot 0.
                     // min_d: the smallest band shift against a predecessor (a node without in-edges reads row 0).
                     int32_t min_d = (pc[u] == 0u) ? bs : INT32_MAX;
+                    uint32_t blocks = 0u; // record.w, high half: ring blocks of predecessors 0 and 1
 #pragma unroll
                     for (int k = 0; k < 4; k++)
                     {
                         const bool have = static_cast<uint32_t>(k) < pc[u] || k == 0;
-                        if (have && (static_cast<int32_t>(pr[k]) < r - kRingRows || pr[k] == 0u))
+                        const bool far  = static_cast<int32_t>(pr[k]) < r - kRingRows || pr[k] == 0u;
+                        if (have && far)
                         {
                             z |= (k == 0) ? kRecFar0 : (k == 1) ? kRecFar1 : (k == 2) ? kRecFar2 : kRecFar3;
                             if (pr[k] != 0u)
                                 far_mark[pr[k]] = 1;
                         }
                         if (static_cast<uint32_t>(k) < pc[u])
-                            min_d = min(min_d, bs - (FULL ? 0 : band_start(static_cast<int32_t>(pr[k]), gradient, kFastBand, max_column)));
+                        {
+                            const int32_t d = bs - (FULL ? 0 : band_start(static_cast<int32_t>(pr[k]), gradient, kFastBand, max_column));
+                            min_d           = min(min_d, d);
+                            if (k < 2 && !far && d >= 0 && d <= 8)
+                            {
+                                // block of the ring that lies under lane 0's cells: ring row, lead block, whole-block shift
+                                const uint32_t blk = (pr[k] & static_cast<uint32_t>(kRingRows - 1)) * kRowBlocks + 1u + static_cast<uint32_t>(d >> 3);
+                                z |= (k == 0) ? (kRecFast0 | (static_cast<uint32_t>(d >> 2) << kRecShift0))
+                                              : (kRecFast1 | (static_cast<uint32_t>(d >> 2) << kRecShift1));
+                                blocks |= blk << (16 + 8 * k);
+                            }
+                        }
                     }
                     for (uint32_t k = 4; k < pc[u]; k++)
                     {
@@ -329,7 +351,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                         min_d = min(min_d, bs - (FULL ? 0 : band_start(p, gradient, kFastBand, max_column)));
                     }
                     apart |= min_d > kFastBand;
-                    records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs));
+                    records[r] = make_uint4(pr[0] | (pr[1] << 16), pr[2] | (pr[3] << 16), z, static_cast<uint32_t>(bs) | blocks);
                 }
             }
         }
@@ -347,7 +369,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             {
                 const uint32_t slot = static_cast<uint32_t>(used + __popc(mask & lt));
                 records[r].z |= kRecSpill;
-                records[r].w |= slot << 16;
+                slot_of[r] = slot;
             }
             used += __popc(mask);
         }
@@ -373,6 +395,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
 
     const uint32_t prof_l = prof + (BITS ? 1u : 8u) * static_cast<uint32_t>(lane);
     const uint32_t ring_l = ring + 16u + 16u * static_cast<uint32_t>(lane); // this lane's cell block in ring row 0
+    const uint32_t ring_l0 = ring + 16u * static_cast<uint32_t>(lane);      // block `lane` of the ring
 
     const int32_t best_floor = REBASED ? INT32_MIN : INT16_MIN;
     int32_t best = best_floor, best_row = 0;
@@ -421,7 +444,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         uint32_t Q0, Q1, Q2, Q3;
         if (BITS)
         {
-            uint32_t at = prof_l + (rec.z & 0xffffu); // the byte of match bits under this lane's cells
+            uint32_t at = prof_l + (rec.z & kRecProfMask); // the byte of match bits under this lane's cells
             if (FULL)
                 at += static_cast<uint32_t>(chunk_bs >> 3); // the records carry band start 0
             const uint4 q = lds_v4(lut + 16u * lds_u8(at));
@@ -438,7 +461,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 prof_loaded += kFastBand;
                 __syncwarp();
             }
-            const uint32_t row = prof + (rec.z & 0xffffu);
+            const uint32_t row = prof + (rec.z & kRecProfMask);
             const uint32_t off = static_cast<uint32_t>(bs) + 8u * static_cast<uint32_t>(lane);
             const uint32_t lo  = lds_u32(row + (off & (kProfWindow - 1)));
             const uint32_t hi  = lds_u32(row + ((off + 4u) & (kProfWindow - 1)));
@@ -448,6 +471,42 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             Q3                 = prmt(lo, hi, 0xF7B3u);
         }
 
+        // A ring predecessor whose block and band shift the pre-pass worked out (kRecFast0 / kRecFast1): one aligned
+        // 16-byte load, plus the neighbouring block (a shift by an odd multiple of 4 cells) or the word before (the corner).
+        auto load_fast = [&](uint32_t blk, uint32_t shift4, uint32_t& V0, uint32_t& V1, uint32_t& V2, uint32_t& V3, uint32_t& D0) {
+            POA_COUNT("fill2.pred_ring_fast");
+            const uint32_t at = ring_l0 + 16u * blk;
+            const uint4 a     = lds_v4(at);
+            if (shift4 & 1u)
+            {
+                const uint4 b = lds_v4(at + 16u);
+                V0            = __byte_perm(a.x, b.x, 0x5432);
+                V1            = __byte_perm(a.y, b.y, 0x5432);
+                V2            = __byte_perm(a.z, b.z, 0x5432);
+                V3            = __byte_perm(a.w, b.w, 0x5432);
+                D0            = __byte_perm(a.w, V3, 0x5410);
+            }
+            else
+            {
+                const uint32_t wv = lds_u32(at - 4u);
+                V0                = a.x;
+                V1                = a.y;
+                V2                = a.z;
+                V3                = a.w;
+                D0                = __byte_perm(wv, V3, 0x5432);
+            }
+            if (REBASED && shift4 != 0u)
+            {
+                const int32_t bd   = min(beta * static_cast<int32_t>(4u * shift4), 8000);
+                const uint32_t fl  = pack2(kNegT + bd, kNegT + bd);
+                const uint32_t c2_ = pack2(-bd, -bd);
+                V0                 = __vadd2(__vmaxs2(V0, fl), c2_);
+                V1                 = __vadd2(__vmaxs2(V1, fl), c2_);
+                V2                 = __vadd2(__vmaxs2(V2, fl), c2_);
+                V3                 = __vadd2(__vmaxs2(V3, fl), c2_);
+                D0                 = __vadd2(__vmaxs2(D0, fl), c2_);
+            }
+        };
         // One predecessor row from the ring or from its spilled copy: its cells under this lane's cells (V_i) and the
         // corner (D0 = (corner, V3.lo)); the diagonal operands are D_i = V_{i-1}.  All branches are warp-uniform.
         // (The corner of lane 0 is the predecessor's left boundary while the bands have not moved: the maximum over the
@@ -487,7 +546,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             else // far predecessor: its spilled copy (through L2); pad blocks are implied
             {
                 POA_COUNT("fill2.pred_spilled");
-                const uint32_t slot = (prow == 0) ? 0u : (records[prow].w >> 16);
+                const uint32_t slot = (prow == 0) ? 0u : slot_of[prow];
                 const uint4* prow4  = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
                 const uint4 lead    = __ldcg(prow4);
                 d                   = bs - static_cast<int32_t>(lead.x);
@@ -562,6 +621,10 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                     X = prev_left;
                 D0        = __byte_perm(X, V3, 0x5432);
             }
+            else if (rec.z & kRecFast0)
+            {
+                load_fast((rec.w >> 16) & 0xffu, (rec.z >> kRecShift0) & 3u, V0, V1, V2, V3, D0);
+            }
             else
             {
                 load_pred(static_cast<int32_t>(rec.x & 0xffffu), (rec.z & kRecFar0) != 0u, V0, V1, V2, V3, D0); // row 0 for a source node
@@ -595,7 +658,10 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
                 uint32_t W0, W1, W2, W3, WD;
                 {
                     // predecessor 1: the slot is just "strictly better than predecessor 0"
-                    load_pred(static_cast<int32_t>(rec.x >> 16), (rec.z & kRecFar1) != 0u, W0, W1, W2, W3, WD);
+                    if (rec.z & kRecFast1)
+                        load_fast(rec.w >> 24, (rec.z >> kRecShift1) & 3u, W0, W1, W2, W3, WD);
+                    else
+                        load_pred(static_cast<int32_t>(rec.x >> 16), (rec.z & kRecFar1) != 0u, W0, W1, W2, W3, WD);
                     auto second = [&](uint32_t& bestv, uint32_t& idx, uint32_t cand) {
                         const uint32_t nb = __vmaxs2(bestv, cand);
                         idx               = grew2(nb, bestv);
@@ -713,7 +779,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             if (rec.z & kRecSpill) // a later row reads this one from beyond the ring
             {
                 POA_COUNT("fill2.rows_spilled");
-                uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(rec.w >> 16) * (kSpillRowBytes / 4));
+                uint4* dst = reinterpret_cast<uint4*>(spill + static_cast<int64_t>(slot_of[r]) * (kSpillRowBytes / 4));
                 __stcg(dst + 1 + lane, out);
                 if (lane == 0)
                     __stcg(dst, lead);
