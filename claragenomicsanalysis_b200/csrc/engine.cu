@@ -13,6 +13,7 @@
 #include <claraparabricks/genomeworks/cudapoa/utils.hpp>
 
 #include <algorithm>
+#include <cstdio>
 #include <atomic>
 #include <cstring>
 #include <iomanip>
@@ -545,6 +546,24 @@ static void launch_phase(Kernel kernel, const KernelParams& P, int32_t warps_per
     const int32_t needed = (P.n_windows + warps_per_block - 1) / warps_per_block;
     const dim3 grid(std::max(1, std::min(needed, sm_count * per_sm)));
     POA_LAUNCH(kernel, grid, block, smem, stream, P);
+#ifndef POA_EMU
+    // development: CUDAPOA_B200_DEBUG_SYNC=1 waits for every phase launch and names the one that failed
+    static const bool debug_sync = [] {
+        const char* env = std::getenv("CUDAPOA_B200_DEBUG_SYNC");
+        return env != nullptr && env[0] == '1';
+    }();
+    if (debug_sync)
+    {
+        const cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess)
+        {
+            cudaFuncAttributes attr{};
+            std::fprintf(stderr, "phase launch failed: %s; step %d, grid %u, block %u, shared memory %zu, scratch per warp %d, class %d\n",
+                         cudaGetErrorString(e), P.step, grid.x, block.x, smem, P.smem_per_warp, P.phase_class);
+            (void)attr;
+        }
+    }
+#endif
 }
 
 // Nodes a graph may have for the consensus (staging area + 6 bytes per node) to run out of `smem` bytes of scratch.

@@ -360,6 +360,8 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
         return kFastNotTaken;
     {
         int32_t used = 1; // slot 0: row 0
+        if (lane == 0)
+            slot_of[0] = 0u;
         for (int32_t r0 = 1; r0 <= node_count; r0 += 32)
         {
             const int32_t r     = r0 + lane;
@@ -546,7 +548,7 @@ __device__ int32_t fill2_impl(const Graph<IdT>& g, int32_t node_count, const uin
             else // far predecessor: its spilled copy (through L2); pad blocks are implied
             {
                 POA_COUNT("fill2.pred_spilled");
-                const uint32_t slot = (prow == 0) ? 0u : slot_of[prow];
+                const uint32_t slot = slot_of[prow]; // row 0: slot 0
                 const uint4* prow4  = reinterpret_cast<const uint4*>(spill + static_cast<int64_t>(slot) * (kSpillRowBytes / 4));
                 const uint4 lead    = __ldcg(prow4);
                 d                   = bs - static_cast<int32_t>(lead.x);
