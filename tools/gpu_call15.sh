@@ -36,3 +36,7 @@ if [ -n "$SANITIZER" ]; then
     echo "compute-sanitizer $tool rc=$?"; tail -3 gpurun_out/${TAG}_sanitizer_${tool}.log
   done
 fi
+# parity at scale against the live reference build (25 600 distinct windows, seven cases, both schedules)
+if [ -n "$PARITY_AT_SCALE" ]; then
+  timeout 1500 python tools/parity_at_scale.py gpurun_out/${TAG}_parity_at_scale.json 2>&1 | grep -v Warning | tail -12
+fi
