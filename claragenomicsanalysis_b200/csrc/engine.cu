@@ -656,7 +656,27 @@ static int32_t launch_split_typed(KernelParams& P, int32_t steps, const PhaseScr
             timeline->mark(stream, 0);
         P.next_window   = c + 3;
         P.smem_per_warp = scratch.trace;
-        if (full)
+        // traceback: one warp per window over shared-memory tiles (trace2_impl), or -- large batches -- one thread per
+        // window (trace2_lane): its launch takes as long as one walk out of L2 whatever the batch size (0.61 ms per
+        // read at cfg 2), the warp-per-window launch 0.049 ms per thousand windows, which is more from about 12 500
+        // windows (18 944 windows: 17.7 against 26.7 ms per step; CUDAPOA_B200_TRACE=warp / lane forces either)
+        static const int trace_choice = [] {
+            const char* env = std::getenv("CUDAPOA_B200_TRACE");
+            return env == nullptr ? 0 : std::strcmp(env, "warp") == 0 ? 1 : std::strcmp(env, "lane") == 0 ? 2 : 0;
+        }();
+        constexpr int32_t kTraceLanesMinWindows = 12288;
+        const int32_t trace_forced = (g_schedule_override.load() >> 2) & 3; // tests: 1 warp per window, 2 thread per window
+        const int32_t trace_mode   = trace_forced != 0 ? trace_forced : trace_choice;
+        if (trace_mode == 2 || (trace_mode == 0 && P.n_windows >= kTraceLanesMinWindows))
+        {
+            const dim3 block(kGraphWarpsPerBlock * 32);
+            const dim3 grid((P.n_windows + block.x - 1) / block.x);
+            if (full)
+                POA_LAUNCH((poa_trace_lanes_kernel<ScoreT, IdT, true>), grid, block, 0, stream, P);
+            else
+                POA_LAUNCH((poa_trace_lanes_kernel<ScoreT, IdT, false>), grid, block, 0, stream, P);
+        }
+        else if (full)
             launch_phase(poa_trace_kernel<ScoreT, IdT, true>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
         else
             launch_phase(poa_trace_kernel<ScoreT, IdT>, P, kGraphWarpsPerBlock, sm_count, stream, cap_trace);
@@ -714,7 +734,7 @@ bool B200Batch::launch_split(KernelParams& P)
         const char* env = std::getenv("CUDAPOA_B200_SCHEDULE");
         return env != nullptr && std::strcmp(env, "fused") == 0;
     }();
-    const int32_t mode = g_schedule_override.load();
+    const int32_t mode = g_schedule_override.load() & 3;
     if (plan_.size32 || mode == 1 || (mode == 0 && fused_by_env))
         return false;
     // full alignment: the chunked packed fill keeps a read's whole profile in shared memory (reads of up to 768 bases:

@@ -342,6 +342,28 @@ __global__ void __launch_bounds__(kGraphWarpsPerBlock * 32, POA_TRACE_MIN_BLOCKS
     }
 }
 
+// The traceback with one thread per window (trace2_lane): no shared memory, no window counter -- thread t of the grid
+// takes window t.
+template <typename ScoreT, typename IdT, bool FULL = false>
+__global__ void __launch_bounds__(kGraphWarpsPerBlock * 32) poa_trace_lanes_kernel(const KernelParams P)
+{
+    const int32_t w = static_cast<int32_t>(blockIdx.x * blockDim.x + threadIdx.x);
+    if (w >= P.n_windows)
+        return;
+    PhaseState* ps      = P.phase + w;
+    const PhaseState st = *ps;
+    if (st.aln_len != kAlnPendingTraceback || st.status != kStSuccess || st.finalized)
+        return;
+    const WindowDesc wd = P.windows[w];
+    const Graph<IdT> g  = make_graph<IdT>(P.arena + static_cast<int64_t>(w) * P.layout.stride, P.layout);
+    const int32_t len   = P.read_len[wd.read_off + P.step];
+    const uint8_t* area = reinterpret_cast<const uint8_t*>(
+        static_cast<ScoreT*>(P.scores) + (FULL ? wd.score_off : static_cast<int64_t>(w) * P.banded_score_stride));
+    if (FULL)
+        area += (16 - (reinterpret_cast<uintptr_t>(area) & 15)) & 15; // as poa_fill_full_kernel aligned it
+    ps->aln_len = trace2_lane<IdT, FULL>(g, st.node_count, len, area, st.start_row);
+}
+
 // Adaptive banding (extension, no counterpart in the reference; the rule is poa_window.cuh's): after the traceback of a
 // step, an alignment that scores below 3/4 of a perfect match or that runs within kAdaptiveBandMargin cells of a band
 // edge is repeated with the band doubled, while that raises the score or the path still hugs an edge, up to

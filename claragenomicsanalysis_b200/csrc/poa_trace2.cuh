@@ -182,4 +182,97 @@ __device__ int32_t trace2_impl(const Graph<IdT>& g, int32_t node_count, int32_t 
     return max(steps + j, 1);
 }
 
+// The same traceback with ONE THREAD PER WINDOW (poa_trace_lanes_kernel): a step is a serial decision whatever is done, so
+// the warp-per-window walk above keeps 31 lanes idle and at most a few dozen windows per SM in flight; here every
+// window of the batch walks at once, each thread following its own codes out of global memory (the records of
+// neighbouring rows share cache lines; the code row a few steps ahead is prefetched), the 32 threads of a warp share
+// the instruction stream of 32 walks, and only what a walk touches is read: one 32-byte sector per row instead of the
+// tile's two or three.  Moves are taken exactly as trace2_impl takes them; node ids are written as the walk goes.
+// Returns the alignment length (> 0) or -1.
+#ifndef POA_TRACE_PREFETCH
+#define POA_TRACE_PREFETCH 1 // 0: none, 1: into L2, 2: into L1
+#endif
+#ifndef POA_TRACE_AHEAD
+#define POA_TRACE_AHEAD 6
+#endif
+template <typename IdT, bool FULL = false>
+__device__ int32_t trace2_lane(const Graph<IdT>& g, int32_t node_count, int32_t read_len, const uint8_t* area,
+                               int32_t start_row)
+{
+    const uint8_t* codes = area;
+    const uint4* records = reinterpret_cast<const uint4*>(g.rowinfo);
+    // A row's band start follows from its rank (band_start, as the fill placed it): the code word's address then does
+    // not wait for the row's record, and the two loads of a step are in flight together.
+    const int32_t max_column = read_len + 1;
+    const float gradient     = band_gradient(read_len, node_count);
+    int32_t i = start_row, j = read_len;
+    int32_t steps = 0;
+    // the node id of a paired base is loaded in one step and stored in the next: the store never waits for its load
+    int32_t pend_at = -1;
+    IdT pend_id     = static_cast<IdT>(-1);
+    while (i > 0 && j > 0)
+    {
+        const int32_t chunk_lo   = FULL ? ((j - 1) & ~(kFastBand - 1)) : 0;
+        const int64_t chunk_row0 = FULL ? static_cast<int64_t>(chunk_lo / kFastBand) * (node_count + 1) : 0;
+        const int32_t bs         = FULL ? chunk_lo : band_start(i, gradient, kFastBand, max_column);
+        const int32_t cell       = j - bs - 1; // 0-based cell of the row's band
+        const bool inside        = static_cast<uint32_t>(cell) < static_cast<uint32_t>(kFastBand);
+        const uint8_t* row       = codes + (chunk_row0 + i) * kCodeRowBytes;
+        const uint4 dd           = __ldg(records + i);
+        uint32_t word            = 0xEEEEEEEEu; // outside the band: an inserted base, as the tile's padding says
+        if (inside)
+            word = __ldg(reinterpret_cast<const uint32_t*>(row) + (cell >> 3));
+#if !defined(POA_EMU) && POA_TRACE_PREFETCH > 0
+        // the walk climbs about a row per step: the record and the code sector POA_TRACE_AHEAD rows up
+        if (i > POA_TRACE_AHEAD)
+        {
+#if POA_TRACE_PREFETCH == 1
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(row - POA_TRACE_AHEAD * kCodeRowBytes + (max(cell - 4, 0) >> 1)));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(records + i - POA_TRACE_AHEAD));
+#else
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(row - POA_TRACE_AHEAD * kCodeRowBytes + (max(cell - 4, 0) >> 1)));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(records + i - POA_TRACE_AHEAD));
+#endif
+        }
+#endif
+        if (pend_at >= 0)
+        {
+            g.aln_node[pend_at] = pend_id;
+            pend_at             = -1;
+        }
+        const int32_t pc = static_cast<int32_t>((dd.z >> 16) & 0x3fu);
+        uint32_t code    = (word >> ((cell & 7) * 4)) & 0xfu;
+        if (pc > kWidePreds && inside) // rare: such rows keep a byte per cell
+            code = __ldg(row + cell);
+        steps++;
+        if (code & 2u) // horizontal: an inserted base
+        {
+            g.aln_node[j - 1] = static_cast<IdT>(-1);
+            j--;
+            continue;
+        }
+        const int32_t p = static_cast<int32_t>(code >> 2);
+        int32_t pi      = static_cast<int32_t>(dd.x & 0xffffu);
+        if (p != 0)
+        {
+            if (p >= pc)
+                return -1; // not a code the fill writes
+            pi = record_pred_row<IdT>(g, dd.x, dd.y, i, p);
+        }
+        if ((code & 1u) == 0u) // diagonal: the base pairs with this row's node
+        {
+            pend_id = g.sorted[i - 1];
+            pend_at = j - 1;
+            j--;
+        }
+        i = pi;
+    }
+    if (pend_at >= 0)
+        g.aln_node[pend_at] = pend_id;
+    // the walk reached row 0 (the remaining bases are inserted before the graph's first node) or column 0
+    for (int32_t k = 0; k < j; k++)
+        g.aln_node[k] = static_cast<IdT>(-1);
+    return max(steps + j, 1);
+}
+
 } // namespace poa_b200

@@ -238,6 +238,8 @@ double cudapoa_b200_bench_relaunch(cudapoa_b200_batch* batch, int32_t iterations
 /* Native library only (tests, A/B measurements): how banded batches are scheduled on the device from now on, process
  * wide.  0 = default (one launch per phase and read -- poa_fill_kernel / poa_graph_kernel -- unless the environment
  * says CUDAPOA_B200_SCHEDULE=fused), 1 = always the single launch (poa_window_kernel), 2 = always phase-split.
+ * Adding 4 or 8 also fixes the traceback kernel of the phase-split schedule: 4 = one warp per window
+ * (poa_trace_kernel), 8 = one thread per window (poa_trace_lanes_kernel; by default batches of 12 288 windows and more).
  * Results are identical either way. */
 void cudapoa_b200_debug_set_schedule(int32_t mode);
 

@@ -54,9 +54,10 @@ def test_emulated_msa_matches_oracle(emu, schedule):
     _check(emu, ws, dict(max_seq=256, max_reads=6, band=256, banded=True, output="msa"), output="msa", graphs=False)
 
 
-def test_emulated_noisy_reads_phase_split(emu):
+@pytest.mark.parametrize("trace", [4, 8])  # traceback by one warp / by one thread per window
+def test_emulated_noisy_reads_phase_split(emu, trace):
     """25 % errors: bubbles, far predecessors (beyond the shared-memory ring), rows with several predecessors."""
-    emu.set_schedule(2)
+    emu.set_schedule(2 + trace)
     ws = generate_windows(3, start_index=4000, template_length=300, n_reads=10, read_error=0.25, backbone_error=0.15)
     _check(emu, ws, dict(max_seq=448, max_reads=10, band=256, banded=True, output="consensus"))
 

@@ -93,6 +93,12 @@ def test_single_launch_and_phase_split_agree(lib, schedule, name):
     assert got[1]["seq_status"] == got[2]["seq_status"]
     for key in ("dp_cells", "graph_rows", "exact_path", "reads_aligned"):
         assert [s[key] for s in got[1]["stats"]] == [s[key] for s in got[2]["stats"]]
+    # the phase-split schedule's two traceback kernels (one warp / one thread per window; the second serves large batches)
+    for trace in (4, 8):
+        schedule(2 + trace)
+        t = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+        assert parity.compare(t, o, eng["output"]) == []
+        assert t["graphs"] == got[2]["graphs"]
 
 
 FULL_SPLIT_CASES = sorted(n for n in CASES if not CASES[n]["engine"].get("banded", True) and CASES[n]["engine"]["max_seq"] <= 768)
@@ -124,12 +130,13 @@ def test_full_alignment_cfg2_windows_phase_split(lib, schedule):
     schedule against the oracle, and -- when the reference build is present -- against the live reference."""
     ws = generate_windows(24, start_index=31000, template_length=500, n_reads=30)
     eng = dict(max_seq=640, max_reads=30, band=256, banded=False, output="consensus")
-    schedule(2)
-    got = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
     o = parity.run_oracle(ws, want_graphs=True, **eng)
-    assert parity.compare(got, o, "consensus") == []
-    assert got["graphs"] == o["graphs"]
-    assert sum(s["exact_path"] for s in got["stats"]) == 0
+    for mode in (2 + 4, 2 + 8):  # traceback across chunk edges by one warp / by one thread per window
+        schedule(mode)
+        got = parity.run_abi(lib, ws, want_graphs=True, max_mem=MEM, **eng)
+        assert parity.compare(got, o, "consensus") == []
+        assert got["graphs"] == o["graphs"]
+        assert sum(s["exact_path"] for s in got["stats"]) == 0
 
 
 @pytest.mark.parametrize("output", ["consensus", "msa"])
@@ -164,7 +171,7 @@ def test_phase_split_many_windows_property(lib, schedule):
     ws = base.tile(4096)
     eng = dict(max_seq=512, max_reads=24, band=256, banded=True, output="consensus")
     res = {}
-    for mode in (1, 2):
+    for mode in (1, 2, 2 + 8):  # 2 + 8: the phase-split schedule with the thread-per-window traceback
         schedule(mode)
         res[mode] = parity.run_abi(lib, ws, max_mem=16 << 30, **eng)
         r = res[mode]
@@ -172,8 +179,8 @@ def test_phase_split_many_windows_property(lib, schedule):
         for w in range(512, 4096):
             assert r["consensus"][w] == r["consensus"][w % 512]
             assert list(r["coverage"][w]) == list(r["coverage"][w % 512])
-    assert res[1]["consensus"] == res[2]["consensus"]
-    assert [list(c) for c in res[1]["coverage"]] == [list(c) for c in res[2]["coverage"]]
+    assert res[1]["consensus"] == res[2]["consensus"] == res[10]["consensus"]
+    assert [list(c) for c in res[1]["coverage"]] == [list(c) for c in res[2]["coverage"]] == [list(c) for c in res[10]["coverage"]]
 
 
 # ---- Batch API behaviour, after cudapoa/tests/Test_CudapoaBatch.cu:66-199 -----------------------------------------
