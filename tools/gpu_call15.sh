@@ -23,7 +23,7 @@ PY
 if [ -z "$NO_NCU" ]; then
 timeout 600 $B --steps 1 --warmup 0 > gpurun_out/${TAG}_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum --clock-control none -c 900 --csv --log-file gpurun_out/${TAG}_launches.csv $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_launches.log 2>&1
-for k in fill trace sort; do
+for k in ${NCU_KERNELS:-fill trace_lanes sort}; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:poa_${k}_kernel -s 14 -c 1 -f -o gpurun_out/${TAG}_${k} $B --steps 1 --warmup 0 > gpurun_out/${TAG}_ncu_${k}.log 2>&1
   echo "ncu $k rc=$?"
 done
