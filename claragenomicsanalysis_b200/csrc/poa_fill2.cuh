@@ -10,12 +10,17 @@
 //     predecessor slot), 128 B per row; rows with more than four predecessors store a byte per cell.  The score matrix
 //     itself never reaches HBM: score rows live in the 8-row shared-memory ring, and only rows that a LATER row names
 //     as a predecessor from beyond the ring (known from the descriptor pre-pass) are also spilled to global memory.
-//   * the substitution profile comes from shared memory: one int8 row per distinct base of the read (at most four,
-//     else the exact path takes the read), holding match - gap / mismatch - gap per read position; a lane fetches its
-//     eight values with two 4-byte loads and widens them with four sign-replicating byte permutes.
-//   * a row's descriptor is one 16-byte record {predecessor rows 0..3, profile offset, in-degree, flags, band start,
-//     spill slot} built by a warp-parallel pre-pass; the row loop gets it with one broadcast shared-memory load out of
-//     a 32-row buffer that the lanes refill together every 32 rows.
+//   * the substitution profile comes from shared memory as MATCH BITS: per distinct base of the read (at most four,
+//     else the exact path takes the read) one bit per read position, in two copies four positions apart, so that the
+//     eight positions under a lane's cells are one byte; a 256-entry table of 16 bytes per block turns the byte into
+//     the lane's four operand registers (the rebased fill of long windows slides a 512-position int8 profile instead).
+//   * a row's descriptor is one 16-byte record {predecessor rows 0..3, profile address, band shifts and ring blocks of
+//     predecessors 0 and 1, in-degree, flags, band start} built by a warp-parallel pre-pass, which also finds the rows
+//     the packed arithmetic cannot serve and hands out spill slots (a side array); the row loop gets the record with
+//     one broadcast shared-memory load out of a 32-row buffer that the lanes refill together every 32 rows, and
+//     branches on its flags only (chain / ring / spilled predecessor, one / several / more than four predecessors).
+//   * several predecessors cost one maximum and one slot update per cell: the candidates of a cell follow from the
+//     element-wise maximum of the predecessors' aligned rows (see the row loop).
 //   * sink selection happens as the sink rows are produced.
 // Window's score area: [code rows: (M + 1) x 256 B][spill slots: 528 B each].
 #pragma once
