@@ -1,6 +1,7 @@
 """End-to-end check of the reference (cudapoa/tests/Test_CudapoaBatchEnd2End.cu:33-85): windows cut from a genome go
 through several batches at once, the coverage-trimmed consensuses are concatenated (multi_batch.hpp:176-207) and the
-result is compared with the genome.  The reference's window file (cudapoa/data/sample-windows.txt) is not part of the
+result is compared with the genome and, window by window, with the consensus and coverage of the unmodified reference
+build.  The reference's window file (cudapoa/data/sample-windows.txt) is not part of the
 snapshot, so the windows are simulated here from a synthetic genome of the same size (33 kb): 30 reads per 500 bp
 window at 2 % error, the regime in which the reference's binding test expects consensus == truth
 (pygenomeworks/test/test_cudapoa_bindings.py:121-146)."""
@@ -53,6 +54,15 @@ def test_simulated_genome_is_reassembled(workers):
     # base after the last backbone node, which is what the coverage trimming of the assembly removes.
     exact = sum(c == genome[w * WINDOW:(w + 1) * WINDOW] for w, c in enumerate(cons))
     assert exact >= 0.6 * len(ws)
+    # ... and window by window it is what the UNMODIFIED reference build computes for these windows (when it travelled)
+    import oraclelib
+    import parity
+    if oraclelib.have_ref_cudapoa():
+        r = parity.run_abi(parity.ref_lib(), ws, max_mem=4 << 30, max_seq=640, max_reads=30, band=256, banded=True,
+                           output="consensus")
+        assert r["status"] == [0] * len(ws)
+        assert list(cons) == r["consensus"]
+        assert [list(c) for c in cov] == [list(c) for c in r["coverage"]]
     asm = assembly(cons, cov)
     assert len(asm) >= 0.97 * len(genome)
     pos = 0
