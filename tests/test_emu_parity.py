@@ -73,6 +73,27 @@ def test_emulated_long_window_rebased_rows(emu, length, reads):
     assert sum(s["exact_path"] for s in n["stats"]) == 0
 
 
+@pytest.mark.parametrize("gen,eng", [
+    # reads shorter than the band: the match-bit profile's padding, bands that never move
+    (dict(n=3, start_index=9500, template_length=90, n_reads=6, read_error=0.15),
+     dict(max_seq=256, max_reads=6, band=256, banded=True, output="consensus")),
+    # full alignment of 700-base reads: three column chunks per row, traceback across chunk edges
+    (dict(n=2, start_index=9600, template_length=700, n_reads=5, read_error=0.12),
+     dict(max_seq=768, max_reads=5, band=256, banded=False, output="consensus")),
+    # windows of 60 .. 620 bases in one batch: profile strides and band placement of every size class
+    (dict(n=6, start_index=9700, template_length=(60, 620), n_reads=8, read_error=0.15),
+     dict(max_seq=704, max_reads=8, band=256, banded=True, output="consensus")),
+])
+def test_emulated_packed_fill_edge_shapes(emu, gen, eng):
+    """Shapes at the edges of the packed fill's data layout (tools/emu_check.py runs the same and more at larger counts)."""
+    gen = dict(gen)
+    ws  = generate_windows(gen.pop("n"), **gen)
+    for mode in (2 + 4, 2 + 8):  # traceback by one warp / one thread per window
+        emu.set_schedule(mode)
+        n = _check(emu, ws, eng, graphs=False)
+        assert sum(s["exact_path"] for s in n["stats"]) == 0
+
+
 def test_emulated_cfg2_window_matches_reference_golden(emu):
     """One full-size cfg 2 window (500 bp x 30 reads) against the golden produced by the unmodified reference."""
     emu.set_schedule(2)
